@@ -1,0 +1,151 @@
+/*
+ * p2c_b200.h -- C ABI of the B200-native FK + projection + loc_2d_3d hot path.
+ *
+ * The reference (wielgosz-info/pedestrians-video-2-carla @ 410bba4) is pure Python and has
+ * no FFI; each entry point below names the reference Python interface it replaces
+ * (paths relative to src/pedestrians_video_2_carla/).  A maintainer binds these with
+ * ctypes; the in-tree binding is pedestrians_video_2_carla_b200/_lib.py.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer to contiguous row-major fp32 unless stated;
+ *     the caller (PyTorch's caching allocator) owns all buffers incl. workspaces;
+ *     the library never allocates, frees, or synchronises.
+ *   - work is enqueued on `stream` (a cudaStream_t passed as void*); pass PyTorch's
+ *     current stream so autograd ordering holds.
+ *   - rotation matrices act on ROW vectors from the right (p' = p R + t); the bone axis is
+ *     the DFS order of structure.yaml (walker_control/pose.py:41-47), parent[b] < b.
+ *   - return value: 0 = ok, < 0 = bad argument (P2C_E_*), > 0 = cudaError_t of the launch.
+ *     Never throws, never exits.  Stateless and re-entrant.
+ */
+#ifndef P2C_B200_H
+#define P2C_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define P2C_MAX_BONES 32
+#define P2C_E_BADARG (-1)
+#define P2C_E_BONES (-2)   /* n_bones outside 1..32 or parent[] not in DFS order */
+#define P2C_E_NULL (-3)    /* a required pointer is NULL */
+#define P2C_E_UNSUPPORTED (-4)
+
+/* Bone tree: walker_control/pose.py:29-47 (structure.yaml walked depth-first). */
+typedef struct {
+    int32_t n_bones;
+    int32_t parent[P2C_MAX_BONES]; /* -1 for the root */
+} p2c_tree_t;
+
+/* Pinhole camera of walker_control/p3d_pose_projection.py:37-69 (pytorch3d PerspectiveCameras,
+ * in_ndc=False): c = w R + T ; u = px - f c.x / c.z ; v = py - f c.y / c.z ; out.z = 1 / c.z */
+typedef struct {
+    float R[9];
+    float T[3];
+    float f, px, py;
+} p2c_camera_t;
+
+enum { P2C_MODE_POSE_CHANGES = 0, /* modules/layers/projection.py:170-195: rel_rot[t] = in[t] . rel_rot[t-1] */
+       P2C_MODE_RELATIVE_ROT = 1  /* modules/layers/projection.py:144-168: rel_rot[t] = in[t]               */ };
+
+/* ---- P3dPose.forward / relative_to_absolute over clips (walker_control/p3d_pose.py:98-213,
+ *      looped by modules/layers/projection.py:144-195) with the optional fused
+ *      P3dPoseProjection.forward (walker_control/p3d_pose_projection.py:115-152).           */
+typedef struct {
+    p2c_tree_t tree;
+    int32_t n_clips, clip_len;  /* N, L ; P3dPose.forward itself is L = 1                          */
+    int32_t mode;               /* P2C_MODE_*                                                       */
+    const float* pose_in;       /* (N,L,B,3,3) changes (mode 0) or relative rotations (mode 1)      */
+    const float* ref_loc;       /* (S,B,3)   relative bone locations, p3d space                     */
+    const float* ref_rot;       /* (S,B,3,3) relative bone rotations before frame 0 (mode 0 only)   */
+    const int32_t* ref_index;   /* (N) row of ref_* per clip, or NULL: row = clip index (S = N)     */
+    const float* world_loc;     /* (N,L,3)   or NULL = zeros      } absolute world transform per    */
+    const float* world_rot;     /* (N,L,3,3) or NULL = identity   } frame (utils/world.py output)   */
+    p2c_camera_t camera;
+    float* rel_rot;             /* out (N,L,B,3,3) or NULL                                          */
+    float* abs_rot;             /* out (N,L,B,3,3) or NULL                                          */
+    float* abs_loc;             /* out (N,L,B,3)   or NULL                                          */
+    float* proj;                /* out (N,L,B,3)   or NULL (then world_* and camera are unused)     */
+} p2c_fk_fwd_t;
+int p2c_fk_fwd(const p2c_fk_fwd_t* p, void* stream);
+
+/* Backward of the above (replaces torch autograd over p3d_pose.py:98-184 and
+ * p3d_pose_projection.py:115-152).  Upstream gradients may each be NULL (= zero).           */
+typedef struct {
+    p2c_tree_t tree;
+    int32_t n_clips, clip_len, mode;
+    const float* pose_in;       /* saved input                                                      */
+    const float* ref_loc;
+    const float* ref_rot;
+    const int32_t* ref_index;
+    const float* world_loc;
+    const float* world_rot;
+    p2c_camera_t camera;
+    const float* rel_rot;       /* saved output (N,L,B,3,3); NULL allowed in mode 1 (= pose_in)     */
+    const float* abs_rot;       /* saved output (N,L,B,3,3)                                         */
+    const float* abs_loc;       /* saved output (N,L,B,3); only read when g_proj != NULL            */
+    const float* g_rel_rot;     /* upstream (N,L,B,3,3) or NULL                                     */
+    const float* g_abs_rot;     /* upstream (N,L,B,3,3) or NULL                                     */
+    const float* g_abs_loc;     /* upstream (N,L,B,3)   or NULL                                     */
+    const float* g_proj;        /* upstream (N,L,B,3)   or NULL                                     */
+    float* g_pose_in;           /* out (N,L,B,3,3)                                                  */
+    float* g_ref_rot;           /* out (N,B,3,3) or NULL; needs ref_index == NULL, mode 0           */
+    float* g_ref_loc;           /* out (N,B,3)   or NULL; needs ref_index == NULL                   */
+    float* g_world_loc;         /* out (N,L,3)   or NULL                                            */
+    float* g_world_rot;         /* out (N,L,3,3) or NULL                                            */
+} p2c_fk_bwd_t;
+int p2c_fk_bwd(const p2c_fk_bwd_t* p, void* stream);
+
+/* ---- P3dPoseProjection.forward alone (walker_control/p3d_pose_projection.py:115-152):
+ *      x (M,J,3), loc (M,3), rot (M,3,3) -> out (M,J,3).                                    */
+int p2c_project_fwd(const float* x, const float* loc, const float* rot, const p2c_camera_t* cam,
+                    float* out, int64_t m, int32_t j, void* stream);
+int p2c_project_bwd(const float* x, const float* loc, const float* rot, const p2c_camera_t* cam,
+                    const float* g_out, float* g_x, float* g_loc, float* g_rot,
+                    int64_t m, int32_t j, void* stream);
+
+/* ---- utils/world.py:16-63 calculate_world_from_changes: cumulative world transform per clip.
+ *      init_* (N,3)/(N,3,3) may be NULL (zeros / identity).                                 */
+int p2c_world_scan_fwd(const float* loc_change, const float* rot_change, const float* init_loc,
+                       const float* init_rot, float* world_loc, float* world_rot,
+                       int32_t n_clips, int32_t clip_len, void* stream);
+int p2c_world_scan_bwd(const float* rot_change, const float* world_rot, const float* init_rot,
+                       const float* g_world_loc, const float* g_world_rot,
+                       float* g_loc_change, float* g_rot_change,
+                       int32_t n_clips, int32_t clip_len, void* stream);
+
+/* ---- pytorch3d rotation conversions at the reference's call sites
+ *      (modules/movements/movements.py:113-116; walker_control/p3d_pose.py:54,78,259).      */
+int p2c_rot6d_to_matrix_fwd(const float* d6, float* out, int64_t n, void* stream);
+int p2c_rot6d_to_matrix_bwd(const float* d6, const float* g_out, float* g_d6, int64_t n, void* stream);
+int p2c_euler_xyz_to_matrix(const float* euler, float* out, int64_t n, void* stream);
+int p2c_matrix_to_euler_xyz(const float* mat, float* euler, int64_t n, void* stream);
+
+/* ---- Normalizer(HipsNeckExtractor) (transforms/pose/normalization/normalizer.py:20-41,
+ *      extractor.py:23-36, hips_neck_extractor.py:6-13): sample (M,J,C), C in {2,3}.        */
+int p2c_hips_neck_normalize_fwd(const float* sample, float* out, int64_t m, int32_t j, int32_t c,
+                                int32_t hips, int32_t neck, float near_zero, void* stream);
+int p2c_hips_neck_normalize_bwd(const float* sample, const float* g_out, float* g_sample, int64_t m,
+                                int32_t j, int32_t c, int32_t hips, int32_t neck, float near_zero,
+                                void* stream);
+
+/* ---- nn.MSELoss(reduction='mean') over the first `c_used` channels with the missing-joints
+ *      mask of utils/tensors.py:29-40 (loss/base_pose_loss.py:36-66, loss/loc_2d.py:69-89,
+ *      loss/loc_3d.py:12-40).  pred (M,J,c_pred), gt (M,J,c_gt).  mask_hips < 0: no mask.
+ *      Deterministic two-stage reduction: `partials` is a caller-owned workspace of
+ *      p2c_mse_workspace_floats(m) floats; `out` receives [loss, sum_sq, count].            */
+int64_t p2c_mse_workspace_floats(int64_t m);
+int p2c_masked_mse_fwd(const float* pred, const float* gt, int64_t m, int32_t j, int32_t c_pred,
+                       int32_t c_gt, int32_t c_used, int32_t mask_hips, float* partials, float* out,
+                       void* stream);
+int p2c_masked_mse_bwd(const float* pred, const float* gt, const float* out, const float* g_loss,
+                       float* g_pred, int64_t m, int32_t j, int32_t c_pred, int32_t c_gt,
+                       int32_t c_used, int32_t mask_hips, void* stream);
+
+const char* p2c_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* P2C_B200_H */

@@ -1,0 +1,189 @@
+// Shared device helpers for the p2c_b200 kernels (sm_100a, CUDA cores only: 3x3 / 1x3.3x3 work).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "p2c_b200.h"
+
+#define P2C_LAUNCH_CHECK()                        \
+    do {                                          \
+        cudaError_t e__ = cudaGetLastError();     \
+        if (e__ != cudaSuccess) return (int)e__;  \
+    } while (0)
+
+#define FULL_MASK 0xffffffffu
+
+// 3x3 row-major matrix in registers.
+struct M3 {
+    float m[9];
+};
+struct V3 {
+    float x, y, z;
+};
+
+__device__ __forceinline__ M3 m3_identity() {
+    M3 r;
+    r.m[0] = 1.f; r.m[1] = 0.f; r.m[2] = 0.f;
+    r.m[3] = 0.f; r.m[4] = 1.f; r.m[5] = 0.f;
+    r.m[6] = 0.f; r.m[7] = 0.f; r.m[8] = 1.f;
+    return r;
+}
+__device__ __forceinline__ M3 m3_zero() {
+    M3 r;
+#pragma unroll
+    for (int i = 0; i < 9; ++i) r.m[i] = 0.f;
+    return r;
+}
+// C = A . B
+__device__ __forceinline__ M3 m3_mul(const M3& a, const M3& b) {
+    M3 c;
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+            c.m[i * 3 + j] = fmaf(a.m[i * 3 + 2], b.m[6 + j], fmaf(a.m[i * 3 + 1], b.m[3 + j], a.m[i * 3] * b.m[j]));
+    return c;
+}
+// C = A . B^T
+__device__ __forceinline__ M3 m3_mul_bt(const M3& a, const M3& b) {
+    M3 c;
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+            c.m[i * 3 + j] =
+                fmaf(a.m[i * 3 + 2], b.m[j * 3 + 2], fmaf(a.m[i * 3 + 1], b.m[j * 3 + 1], a.m[i * 3] * b.m[j * 3]));
+    return c;
+}
+// C = A^T . B
+__device__ __forceinline__ M3 m3_mul_at(const M3& a, const M3& b) {
+    M3 c;
+#pragma unroll
+    for (int i = 0; i < 3; ++i)
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+            c.m[i * 3 + j] = fmaf(a.m[6 + i], b.m[6 + j], fmaf(a.m[3 + i], b.m[3 + j], a.m[i] * b.m[j]));
+    return c;
+}
+__device__ __forceinline__ void m3_acc(M3& a, const M3& b) {
+#pragma unroll
+    for (int i = 0; i < 9; ++i) a.m[i] += b.m[i];
+}
+// v . A  (row vector times matrix)
+__device__ __forceinline__ V3 v3_mul_m(const V3& v, const M3& a) {
+    V3 r;
+    r.x = fmaf(v.z, a.m[6], fmaf(v.y, a.m[3], v.x * a.m[0]));
+    r.y = fmaf(v.z, a.m[7], fmaf(v.y, a.m[4], v.x * a.m[1]));
+    r.z = fmaf(v.z, a.m[8], fmaf(v.y, a.m[5], v.x * a.m[2]));
+    return r;
+}
+// v . A^T
+__device__ __forceinline__ V3 v3_mul_mt(const V3& v, const M3& a) {
+    V3 r;
+    r.x = fmaf(v.z, a.m[2], fmaf(v.y, a.m[1], v.x * a.m[0]));
+    r.y = fmaf(v.z, a.m[5], fmaf(v.y, a.m[4], v.x * a.m[3]));
+    r.z = fmaf(v.z, a.m[8], fmaf(v.y, a.m[7], v.x * a.m[6]));
+    return r;
+}
+// a += u^T (x) v   (outer product, 3x1 . 1x3)
+__device__ __forceinline__ void m3_acc_outer(M3& a, const V3& u, const V3& v) {
+    a.m[0] = fmaf(u.x, v.x, a.m[0]); a.m[1] = fmaf(u.x, v.y, a.m[1]); a.m[2] = fmaf(u.x, v.z, a.m[2]);
+    a.m[3] = fmaf(u.y, v.x, a.m[3]); a.m[4] = fmaf(u.y, v.y, a.m[4]); a.m[5] = fmaf(u.y, v.z, a.m[5]);
+    a.m[6] = fmaf(u.z, v.x, a.m[6]); a.m[7] = fmaf(u.z, v.y, a.m[7]); a.m[8] = fmaf(u.z, v.z, a.m[8]);
+}
+__device__ __forceinline__ M3 m3_shfl(const M3& a, int src) {
+    M3 r;
+#pragma unroll
+    for (int i = 0; i < 9; ++i) r.m[i] = __shfl_sync(FULL_MASK, a.m[i], src);
+    return r;
+}
+__device__ __forceinline__ V3 v3_shfl(const V3& a, int src) {
+    V3 r;
+    r.x = __shfl_sync(FULL_MASK, a.x, src);
+    r.y = __shfl_sync(FULL_MASK, a.y, src);
+    r.z = __shfl_sync(FULL_MASK, a.z, src);
+    return r;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(FULL_MASK, v, o);
+    return v;
+}
+
+// torch.nan_to_num(x, nan=0, posinf=0, neginf=0)  (utils/tensors.py:43-53)
+__device__ __forceinline__ float nan_to_zero(float x) { return (fabsf(x) <= 3.402823466e38f) ? x : 0.f; }
+
+// ---- warp-cooperative tile movement -------------------------------------------------------------
+// Per-pose records are 8-byte but not 16-byte multiples (B*9*4 = 936, B*3*4 = 312 for B = 26), so the
+// widest vector that is aligned for every pose is float2 when the record has an even float count.
+// Lanes move consecutive words => full-sector coalescing; the lane<->bone redistribution goes through
+// a per-warp shared-memory tile (stride 9 or 3 words per lane: odd => bank-conflict free).
+__device__ __forceinline__ void warp_tile_load(float* __restrict__ s, const float* __restrict__ g, int nfloats,
+                                               int lane) {
+    if (((nfloats & 1) == 0) && ((reinterpret_cast<uintptr_t>(g) & 7) == 0)) {
+        const float2* g2 = reinterpret_cast<const float2*>(g);
+        float2* s2 = reinterpret_cast<float2*>(s);
+        for (int i = lane; i < (nfloats >> 1); i += 32) s2[i] = __ldg(g2 + i);
+    } else {
+        for (int i = lane; i < nfloats; i += 32) s[i] = __ldg(g + i);
+    }
+}
+__device__ __forceinline__ void warp_tile_store(float* __restrict__ g, const float* __restrict__ s, int nfloats,
+                                                int lane) {
+    if (((nfloats & 1) == 0) && ((reinterpret_cast<uintptr_t>(g) & 7) == 0)) {
+        float2* g2 = reinterpret_cast<float2*>(g);
+        const float2* s2 = reinterpret_cast<const float2*>(s);
+        for (int i = lane; i < (nfloats >> 1); i += 32) g2[i] = s2[i];
+    } else {
+        for (int i = lane; i < nfloats; i += 32) g[i] = s[i];
+    }
+}
+__device__ __forceinline__ M3 m3_from(const float* s) {
+    M3 r;
+#pragma unroll
+    for (int i = 0; i < 9; ++i) r.m[i] = s[i];
+    return r;
+}
+__device__ __forceinline__ void m3_to(float* s, const M3& a) {
+#pragma unroll
+    for (int i = 0; i < 9; ++i) s[i] = a.m[i];
+}
+
+// Host-side tree preprocessing shared by the launchers.
+struct TreeDev {
+    int n_bones;
+    int max_depth;
+    int max_children;
+    int8_t parent[P2C_MAX_BONES];
+    int8_t depth[P2C_MAX_BONES];
+    int8_t child[P2C_MAX_BONES][4];  // up to 4 children per bone are handled by the shuffle gather
+};
+
+static inline int build_tree(const p2c_tree_t& t, TreeDev& d) {
+    if (t.n_bones < 1 || t.n_bones > P2C_MAX_BONES) return P2C_E_BONES;
+    d.n_bones = t.n_bones;
+    d.max_depth = 0;
+    d.max_children = 0;
+    int nchild[P2C_MAX_BONES];
+    for (int b = 0; b < P2C_MAX_BONES; ++b) {
+        d.parent[b] = -1;
+        d.depth[b] = 0;
+        nchild[b] = 0;
+        for (int k = 0; k < 4; ++k) d.child[b][k] = -1;
+    }
+    for (int b = 0; b < t.n_bones; ++b) {
+        int p = t.parent[b];
+        if (b == 0) {
+            if (p != -1) return P2C_E_BONES;
+            continue;
+        }
+        if (p < 0 || p >= b) return P2C_E_BONES;  // DFS order: a parent precedes its children
+        d.parent[b] = (int8_t)p;
+        d.depth[b] = (int8_t)(d.depth[p] + 1);
+        if (d.depth[b] > d.max_depth) d.max_depth = d.depth[b];
+        if (nchild[p] >= 4) return P2C_E_UNSUPPORTED;
+        d.child[p][nchild[p]++] = (int8_t)b;
+        if (nchild[p] > d.max_children) d.max_children = nchild[p];
+    }
+    return 0;
+}
