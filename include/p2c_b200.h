@@ -143,6 +143,44 @@ int p2c_masked_mse_bwd(const float* pred, const float* gt, const float* out, con
                        float* g_pred, int64_t m, int32_t j, int32_t c_pred, int32_t c_gt,
                        int32_t c_used, int32_t mask_hips, void* stream);
 
+/* ---- One pose_lifting step of the hot path, fused: ProjectionModule.forward
+ *      (modules/layers/projection.py:73-123) -> Normalizer (modules/flow/pose_lifting.py:167-170) ->
+ *      loc_2d, loc_3d, loc_2d_3d (modules/flow/base.py:440-469; loss/loc_2d.py, loc_3d.py, loc_2d_3d.py)
+ *      AND the gradient of  weight_2d*loc_2d + weight_3d*loc_3d  w.r.t. pose_in, so that
+ *      loss.backward() only has to scale g_pose_in by the upstream scalar.
+ *      losses[8] = { loc_2d, loc_3d, weight_2d*loc_2d + weight_3d*loc_3d, sum_sq_2d, count_2d,
+ *                    sum_sq_3d, count_3d, 0 }  (means are LOCAL to this call: DDP semantics).     */
+typedef struct {
+    p2c_tree_t tree;
+    int32_t hips, neck;          /* joints used by HipsNeckExtractor and never masked               */
+    int32_t n_clips, clip_len;
+    int32_t mode;                /* P2C_MODE_*                                                       */
+    int32_t input_6d;            /* 1: pose_in / g_pose_in are (N,L,B,6) rotation_6d (movements.py:113-116) */
+    int32_t normalize;           /* 1: hips/neck normalise the projection before loc_2d              */
+    int32_t mask_missing_joints; /* utils/tensors.py:29-40                                           */
+    const float* pose_in;
+    const float* ref_loc;
+    const float* ref_rot;
+    const int32_t* ref_index;
+    const float* world_loc;      /* (N,L,3) or NULL                                                  */
+    const float* world_rot;      /* (N,L,3,3) or NULL                                                */
+    p2c_camera_t camera;
+    const float* gt_2d;          /* targets['projection_2d(_transformed)'] (N,L,B,gt_2d_channels)    */
+    int32_t gt_2d_channels;      /* >= 2                                                             */
+    const float* gt_3d;          /* targets['absolute_pose_loc'] (N,L,B,3)                           */
+    float weight_2d, weight_3d;
+    float* rel_rot;              /* out (N,L,B,3,3)                                                  */
+    float* abs_rot;              /* out (N,L,B,3,3)                                                  */
+    float* abs_loc;              /* out (N,L,B,3)                                                    */
+    float* proj;                 /* out (N,L,B,3)                                                    */
+    float* proj_norm;            /* out (N,L,B,3) normalised projection or NULL                      */
+    float* g_pose_in;            /* out, same shape as pose_in                                       */
+    float* workspace;            /* p2c_fused_step_workspace_floats(N*L, B, input_6d) floats         */
+    float* losses;               /* out, 8 floats                                                    */
+} p2c_fused_step_t;
+int64_t p2c_fused_step_workspace_floats(int64_t n_poses, int32_t n_bones, int32_t input_6d);
+int p2c_fused_step(const p2c_fused_step_t* p, void* stream);
+
 const char* p2c_version(void);
 
 #ifdef __cplusplus

@@ -1,0 +1,282 @@
+"""torch.autograd.Function wrappers over the C ABI (include/p2c_b200.h).
+
+PyTorch here is plumbing only (device memory, streams, autograd graph); every forward and
+backward below is a hand-written sm_100a kernel.  There is no CPU fallback: CPU tensors raise.
+"""
+import torch
+
+from . import _lib
+from ._lib import check, ptr, stream
+
+
+def _f32c(t, name):
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError('p2c_b200: %s must be a CUDA tensor (no CPU fallback); got %s' % (name, t.device))
+    if t.dtype != torch.float32:
+        t = t.float()
+    return t.contiguous()
+
+
+class _Rot6dToMatrix(torch.autograd.Function):
+    """pytorch3d rotation_6d_to_matrix at modules/movements/movements.py:113-116."""
+
+    @staticmethod
+    def forward(ctx, d6):
+        d6 = _f32c(d6, 'd6')
+        out = torch.empty(d6.shape[:-1] + (3, 3), device=d6.device, dtype=torch.float32)
+        n = d6.numel() // 6
+        check(_lib.load().p2c_rot6d_to_matrix_fwd(ptr(d6), ptr(out), n, stream()), 'rot6d_to_matrix_fwd')
+        ctx.save_for_backward(d6)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        (d6,) = ctx.saved_tensors
+        g = _f32c(g, 'grad')
+        gd = torch.empty_like(d6)
+        check(_lib.load().p2c_rot6d_to_matrix_bwd(ptr(d6), ptr(g), ptr(gd), d6.numel() // 6, stream()),
+              'rot6d_to_matrix_bwd')
+        return gd
+
+
+def rotation_6d_to_matrix(d6):
+    if d6.shape[-1] != 6:
+        raise RuntimeError('rotation_6d_to_matrix expects (..., 6)')
+    return _Rot6dToMatrix.apply(d6)
+
+
+def matrix_to_rotation_6d(matrix):
+    """pytorch3d matrix_to_rotation_6d (modules/movements/seq2seq.py:330): first two rows; a view + copy."""
+    return matrix[..., :2, :].clone().reshape(matrix.shape[:-2] + (6,))
+
+
+def euler_angles_to_matrix(euler, convention='XYZ'):
+    """pytorch3d euler_angles_to_matrix for the only convention the reference uses ("XYZ")."""
+    if convention != 'XYZ':
+        raise RuntimeError('only the "XYZ" convention is implemented (the only one the reference uses)')
+    e = _f32c(euler.detach(), 'euler')
+    out = torch.empty(e.shape[:-1] + (3, 3), device=e.device, dtype=torch.float32)
+    check(_lib.load().p2c_euler_xyz_to_matrix(ptr(e), ptr(out), e.numel() // 3, stream()), 'euler_xyz_to_matrix')
+    return out
+
+
+def matrix_to_euler_angles(matrix, convention='XYZ'):
+    if convention != 'XYZ':
+        raise RuntimeError('only the "XYZ" convention is implemented (the only one the reference uses)')
+    m = _f32c(matrix.detach(), 'matrix')
+    out = torch.empty(m.shape[:-2] + (3,), device=m.device, dtype=torch.float32)
+    check(_lib.load().p2c_matrix_to_euler_xyz(ptr(m), ptr(out), m.numel() // 9, stream()), 'matrix_to_euler_xyz')
+    return out
+
+
+class _FkClip(torch.autograd.Function):
+    """P3dPose.forward / relative_to_absolute over (N, L) with optional fused projection."""
+
+    @staticmethod
+    def forward(ctx, pose_in, ref_loc, ref_rot, ref_index, world_loc, world_rot, tree, camera, mode, want_proj):
+        pose_in = _f32c(pose_in, 'pose_in')
+        ref_loc = _f32c(ref_loc, 'ref_loc')
+        ref_rot = _f32c(ref_rot, 'ref_rot')
+        world_loc = _f32c(world_loc, 'world_loc')
+        world_rot = _f32c(world_rot, 'world_rot')
+        N, L, B = pose_in.shape[:3]
+        dev = pose_in.device
+        rel_rot = torch.empty((N, L, B, 3, 3), device=dev) if mode == _lib.MODE_POSE_CHANGES else None
+        abs_rot = torch.empty((N, L, B, 3, 3), device=dev)
+        abs_loc = torch.empty((N, L, B, 3), device=dev)
+        proj = torch.empty((N, L, B, 3), device=dev) if want_proj else None
+        a = _lib.FkFwd()
+        a.tree, a.n_clips, a.clip_len, a.mode = tree, N, L, mode
+        a.pose_in, a.ref_loc, a.ref_rot, a.ref_index = ptr(pose_in), ptr(ref_loc), ptr(ref_rot), ptr(ref_index)
+        a.world_loc, a.world_rot = ptr(world_loc), ptr(world_rot)
+        if camera is not None:
+            a.camera = camera
+        a.rel_rot, a.abs_rot, a.abs_loc, a.proj = ptr(rel_rot), ptr(abs_rot), ptr(abs_loc), ptr(proj)
+        check(_lib.load().p2c_fk_fwd(a, stream()), 'fk_fwd')
+        ctx.save_for_backward(pose_in, ref_loc, ref_rot, ref_index, world_loc, world_rot, rel_rot, abs_rot, abs_loc)
+        ctx.tree, ctx.camera, ctx.mode, ctx.want_proj = tree, camera, mode, want_proj
+        if rel_rot is None:
+            rel_rot = pose_in.new_empty(0)
+        if proj is None:
+            proj = pose_in.new_empty(0)
+        ctx.mark_non_differentiable(*[t for t, w in ((rel_rot, mode != _lib.MODE_POSE_CHANGES), (proj, not want_proj)) if w])
+        return rel_rot, abs_rot, abs_loc, proj
+
+    @staticmethod
+    def backward(ctx, g_rel_rot, g_abs_rot, g_abs_loc, g_proj):
+        pose_in, ref_loc, ref_rot, ref_index, world_loc, world_rot, rel_rot, abs_rot, abs_loc = ctx.saved_tensors
+        N, L, B = pose_in.shape[:3]
+        dev = pose_in.device
+        need = ctx.needs_input_grad
+        if ctx.mode != _lib.MODE_POSE_CHANGES:
+            g_rel_rot = None
+        if not ctx.want_proj:
+            g_proj = None
+        a = _lib.FkBwd()
+        a.tree, a.n_clips, a.clip_len, a.mode = ctx.tree, N, L, ctx.mode
+        a.pose_in, a.ref_loc, a.ref_rot, a.ref_index = ptr(pose_in), ptr(ref_loc), ptr(ref_rot), ptr(ref_index)
+        a.world_loc, a.world_rot = ptr(world_loc), ptr(world_rot)
+        if ctx.camera is not None:
+            a.camera = ctx.camera
+        a.rel_rot, a.abs_rot, a.abs_loc = ptr(rel_rot), ptr(abs_rot), ptr(abs_loc)
+        g_rel_rot, g_abs_rot = _f32c(g_rel_rot, 'g_rel_rot'), _f32c(g_abs_rot, 'g_abs_rot')
+        g_abs_loc, g_proj = _f32c(g_abs_loc, 'g_abs_loc'), _f32c(g_proj, 'g_proj')
+        a.g_rel_rot, a.g_abs_rot, a.g_abs_loc, a.g_proj = ptr(g_rel_rot), ptr(g_abs_rot), ptr(g_abs_loc), ptr(g_proj)
+        g_in = torch.empty_like(pose_in)
+        a.g_pose_in = ptr(g_in)
+        g_ref_loc = g_ref_rot = g_wl = g_wr = None
+        if need[1]:
+            if ref_index is not None:
+                raise RuntimeError('gradient w.r.t. an indexed reference table is not supported')
+            g_ref_loc = torch.empty_like(ref_loc)
+            a.g_ref_loc = ptr(g_ref_loc)
+        if need[2] and ref_rot is not None and ctx.mode == _lib.MODE_POSE_CHANGES:
+            if ref_index is not None:
+                raise RuntimeError('gradient w.r.t. an indexed reference table is not supported')
+            g_ref_rot = torch.empty_like(ref_rot)
+            a.g_ref_rot = ptr(g_ref_rot)
+        if g_proj is not None and world_loc is not None and need[4]:
+            g_wl = torch.empty_like(world_loc)
+            a.g_world_loc = ptr(g_wl)
+        if g_proj is not None and world_rot is not None and need[5]:
+            g_wr = torch.empty_like(world_rot)
+            a.g_world_rot = ptr(g_wr)
+        check(_lib.load().p2c_fk_bwd(a, stream()), 'fk_bwd')
+        return g_in, g_ref_loc, g_ref_rot, None, g_wl, g_wr, None, None, None, None
+
+
+def fk_clip(pose_in, ref_loc, ref_rot, ref_index, world_loc, world_rot, tree, camera, mode, want_proj):
+    rel_rot, abs_rot, abs_loc, proj = _FkClip.apply(pose_in, ref_loc, ref_rot, ref_index, world_loc, world_rot, tree,
+                                                    camera, mode, want_proj)
+    return (rel_rot if mode == _lib.MODE_POSE_CHANGES else None), abs_rot, abs_loc, (proj if want_proj else None)
+
+
+class _Project(torch.autograd.Function):
+    """P3dPoseProjection.forward (walker_control/p3d_pose_projection.py:115-152)."""
+
+    @staticmethod
+    def forward(ctx, x, loc, rot, camera):
+        x, loc, rot = _f32c(x, 'x'), _f32c(loc, 'loc'), _f32c(rot, 'rot')
+        out = torch.empty_like(x)
+        m, j = x.shape[0], x.shape[1]
+        check(_lib.load().p2c_project_fwd(ptr(x), ptr(loc), ptr(rot), camera, ptr(out), m, j, stream()), 'project_fwd')
+        ctx.save_for_backward(x, loc, rot)
+        ctx.camera = camera
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        x, loc, rot = ctx.saved_tensors
+        g = _f32c(g, 'grad')
+        need = ctx.needs_input_grad
+        gx = torch.empty_like(x) if need[0] else None
+        gl = torch.empty_like(loc) if need[1] else None
+        gr = torch.empty_like(rot) if need[2] else None
+        check(_lib.load().p2c_project_bwd(ptr(x), ptr(loc), ptr(rot), ctx.camera, ptr(g), ptr(gx), ptr(gl), ptr(gr),
+                                          x.shape[0], x.shape[1], stream()), 'project_bwd')
+        return gx, gl, gr, None
+
+
+def project(x, loc, rot, camera):
+    return _Project.apply(x, loc, rot, camera)
+
+
+class _WorldScan(torch.autograd.Function):
+    """utils/world.py:16-63 (the cumulative part)."""
+
+    @staticmethod
+    def forward(ctx, loc_change, rot_change, init_loc, init_rot):
+        loc_change, rot_change = _f32c(loc_change, 'world_loc_change'), _f32c(rot_change, 'world_rot_change')
+        init_loc, init_rot = _f32c(init_loc, 'initial_world_loc'), _f32c(init_rot, 'initial_world_rot')
+        n, l = loc_change.shape[:2]
+        wl = torch.empty((n, l, 3), device=loc_change.device)
+        wr = torch.empty((n, l, 3, 3), device=loc_change.device)
+        check(_lib.load().p2c_world_scan_fwd(ptr(loc_change), ptr(rot_change), ptr(init_loc), ptr(init_rot), ptr(wl),
+                                             ptr(wr), n, l, stream()), 'world_scan_fwd')
+        ctx.save_for_backward(rot_change, wr, init_rot)
+        return wl, wr
+
+    @staticmethod
+    def backward(ctx, g_wl, g_wr):
+        rot_change, wr, init_rot = ctx.saved_tensors
+        n, l = rot_change.shape[:2]
+        need = ctx.needs_input_grad
+        g_wl, g_wr = _f32c(g_wl, 'g_world_loc'), _f32c(g_wr, 'g_world_rot')
+        g_dl = torch.empty((n, l, 3), device=wr.device) if need[0] else None
+        g_dr = torch.empty_like(rot_change) if need[1] else None
+        check(_lib.load().p2c_world_scan_bwd(ptr(rot_change), ptr(wr), ptr(init_rot), ptr(g_wl), ptr(g_wr), ptr(g_dl),
+                                             ptr(g_dr), n, l, stream()), 'world_scan_bwd')
+        return g_dl, g_dr, None, None
+
+
+def world_scan(loc_change, rot_change, init_loc=None, init_rot=None):
+    return _WorldScan.apply(loc_change, rot_change, init_loc, init_rot)
+
+
+class _HipsNeckNormalize(torch.autograd.Function):
+    """Normalizer(HipsNeckExtractor) (transforms/pose/normalization/normalizer.py:20-41)."""
+
+    @staticmethod
+    def forward(ctx, sample, hips, neck, near_zero):
+        s = _f32c(sample, 'sample')
+        out = torch.empty_like(s)
+        j, c = s.shape[-2], s.shape[-1]
+        m = s.numel() // (j * c)
+        check(_lib.load().p2c_hips_neck_normalize_fwd(ptr(s), ptr(out), m, j, c, hips, neck, near_zero, stream()),
+              'hips_neck_normalize_fwd')
+        ctx.save_for_backward(s)
+        ctx.cfg = (hips, neck, near_zero)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        (s,) = ctx.saved_tensors
+        g = _f32c(g, 'grad')
+        hips, neck, near_zero = ctx.cfg
+        gs = torch.empty_like(s)
+        j, c = s.shape[-2], s.shape[-1]
+        check(_lib.load().p2c_hips_neck_normalize_bwd(ptr(s), ptr(g), ptr(gs), s.numel() // (j * c), j, c, hips, neck,
+                                                      near_zero, stream()), 'hips_neck_normalize_bwd')
+        return gs, None, None, None
+
+
+def hips_neck_normalize(sample, hips, neck, near_zero=1e-5):
+    return _HipsNeckNormalize.apply(sample, hips, neck, near_zero)
+
+
+class _MaskedMSE(torch.autograd.Function):
+    """nn.MSELoss('mean') over [..., :c_used] of the joints kept by utils/tensors.py:29-40."""
+
+    @staticmethod
+    def forward(ctx, pred, gt, c_used, mask_hips):
+        pred, gt = _f32c(pred, 'pred'), _f32c(gt.detach(), 'gt')
+        j, cp, cg = pred.shape[-2], pred.shape[-1], gt.shape[-1]
+        m = pred.numel() // (j * cp)
+        if gt.numel() // (j * cg) != m or gt.shape[-2] != j:
+            raise RuntimeError('pred %s and gt %s do not match' % (tuple(pred.shape), tuple(gt.shape)))
+        lib = _lib.load()
+        ws = torch.empty(lib.p2c_mse_workspace_floats(m), device=pred.device)
+        out = torch.empty(3, device=pred.device)
+        check(lib.p2c_masked_mse_fwd(ptr(pred), ptr(gt), m, j, cp, cg, c_used, mask_hips, ptr(ws), ptr(out), stream()),
+              'masked_mse_fwd')
+        ctx.save_for_backward(pred, gt, out)
+        ctx.cfg = (c_used, mask_hips)
+        return out[0]
+
+    @staticmethod
+    def backward(ctx, g):
+        pred, gt, out = ctx.saved_tensors
+        c_used, mask_hips = ctx.cfg
+        g = _f32c(g, 'grad').reshape(1)
+        gp = torch.empty_like(pred)
+        j, cp, cg = pred.shape[-2], pred.shape[-1], gt.shape[-1]
+        check(_lib.load().p2c_masked_mse_bwd(ptr(pred), ptr(gt), ptr(out), ptr(g), ptr(gp), pred.numel() // (j * cp), j,
+                                             cp, cg, c_used, mask_hips, stream()), 'masked_mse_bwd')
+        return gp, None, None, None
+
+
+def masked_mse(pred, gt, c_used, mask_hips=-1):
+    """mask_hips < 0: plain MSE; otherwise joints whose gt[..., :c_used] has a zero are dropped, hips kept."""
+    return _MaskedMSE.apply(pred, gt, c_used, mask_hips)
