@@ -180,6 +180,8 @@ typedef struct {
 } p2c_fused_step_t;
 int64_t p2c_fused_step_workspace_floats(int64_t n_poses, int32_t n_bones, int32_t input_6d);
 int p2c_fused_step(const p2c_fused_step_t* p, void* stream);
+/* number of kernels p2c_fused_step(p) enqueues (for launch accounting; < 0 = bad argument) */
+int p2c_fused_step_launches(const p2c_fused_step_t* p);
 
 const char* p2c_version(void);
 

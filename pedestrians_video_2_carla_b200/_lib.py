@@ -70,6 +70,7 @@ _SIGS = {
                                      C.c_int32, _P]),
     'p2c_fused_step_workspace_floats': (C.c_int64, [C.c_int64, C.c_int32, C.c_int32]),
     'p2c_fused_step': (C.c_int, [C.POINTER(FusedStep), _P]),
+    'p2c_fused_step_launches': (C.c_int, [C.POINTER(FusedStep)]),
     'p2c_version': (C.c_char_p, []),
 }
 

@@ -10,3 +10,7 @@ extern "C" int p2c_fused_carla(const p2c_fused_step_t* p, void* stream) {
     (void)p; (void)stream;
     return P2C_E_UNSUPPORTED;
 }
+extern "C" int p2c_fused_carla_launches(const p2c_fused_step_t* p) {
+    (void)p;
+    return 0;
+}

@@ -194,6 +194,15 @@ extern "C" int64_t p2c_fused_step_workspace_floats(int64_t n_poses, int32_t n_bo
     return w;
 }
 
+extern "C" int p2c_fused_carla_launches(const p2c_fused_step_t* p);
+
+extern "C" int p2c_fused_step_launches(const p2c_fused_step_t* p) {
+    if (!p) return P2C_E_NULL;
+    if (p->n_clips == 0) return 0;
+    if (p2c_fused_carla_supported(p)) return p2c_fused_carla_launches(p);
+    return 5 + (p->input_6d ? 2 : 0);  // fk_fwd, loss_fwd, finalize, loss_bwd, fk_bwd (+ rot6d fwd/bwd)
+}
+
 extern "C" int p2c_fused_step(const p2c_fused_step_t* p, void* stream) {
     if (!p) return P2C_E_NULL;
     if (p->tree.n_bones < 1 || p->tree.n_bones > P2C_MAX_BONES) return P2C_E_BONES;

@@ -280,3 +280,91 @@ class _MaskedMSE(torch.autograd.Function):
 def masked_mse(pred, gt, c_used, mask_hips=-1):
     """mask_hips < 0: plain MSE; otherwise joints whose gt[..., :c_used] has a zero are dropped, hips kept."""
     return _MaskedMSE.apply(pred, gt, c_used, mask_hips)
+
+
+class FusedStepResult(object):
+    """Outputs of one fused pose_lifting step (see fused_step)."""
+    __slots__ = ('loc_2d', 'loc_3d', 'loc_2d_3d', 'losses', 'relative_pose_rot', 'absolute_pose_rot',
+                 'absolute_pose_loc', 'projection_2d', 'projection_2d_transformed')
+
+
+class _FusedStep(torch.autograd.Function):
+    """ProjectionModule.forward -> Normalizer -> loc_2d / loc_3d / loc_2d_3d with the gradient w.r.t. the pose
+    input produced in the SAME launch sequence (modules/flow/pose_lifting.py:121-195, flow/base.py:440-469).
+    forward returns the three losses; backward only scales the stored gradient by the upstream scalars."""
+
+    @staticmethod
+    def forward(ctx, pose_in, cfg):
+        lib = _lib.load()
+        pose_in = _f32c(pose_in, 'pose_in')
+        N, L, B = pose_in.shape[:3]
+        dev = pose_in.device
+        a = _lib.FusedStep()
+        a.tree, a.hips, a.neck = cfg['tree'], cfg['hips'], cfg['neck']
+        a.n_clips, a.clip_len, a.mode = N, L, cfg['mode']
+        a.input_6d = 1 if pose_in.shape[-1] == 6 and pose_in.dim() == 4 else 0
+        a.normalize = 1 if cfg['normalize'] else 0
+        a.mask_missing_joints = 1 if cfg['mask_missing_joints'] else 0
+        gt2, gt3 = _f32c(cfg['gt_2d'], 'gt_2d'), _f32c(cfg['gt_3d'], 'gt_3d')
+        ref_loc, ref_rot = _f32c(cfg['ref_loc'], 'ref_loc'), _f32c(cfg['ref_rot'], 'ref_rot')
+        world_loc, world_rot = _f32c(cfg.get('world_loc'), 'world_loc'), _f32c(cfg.get('world_rot'), 'world_rot')
+        ref_index = cfg.get('ref_index')
+        a.pose_in, a.ref_loc, a.ref_rot, a.ref_index = ptr(pose_in), ptr(ref_loc), ptr(ref_rot), ptr(ref_index)
+        a.world_loc, a.world_rot, a.camera = ptr(world_loc), ptr(world_rot), cfg['camera']
+        a.gt_2d, a.gt_2d_channels, a.gt_3d = ptr(gt2), gt2.shape[-1], ptr(gt3)
+        a.weight_2d, a.weight_3d = float(cfg.get('weight_2d', 1.0)), float(cfg.get('weight_3d', 1.0))
+        out = cfg.get('out') or {}
+        rel_rot = out.get('rel_rot') if out.get('rel_rot') is not None else torch.empty((N, L, B, 3, 3), device=dev)
+        abs_rot = out.get('abs_rot') if out.get('abs_rot') is not None else torch.empty((N, L, B, 3, 3), device=dev)
+        abs_loc = out.get('abs_loc') if out.get('abs_loc') is not None else torch.empty((N, L, B, 3), device=dev)
+        proj = out.get('proj') if out.get('proj') is not None else torch.empty((N, L, B, 3), device=dev)
+        proj_norm = None
+        if cfg.get('want_transformed', True) and cfg['normalize']:
+            proj_norm = out.get('proj_norm') if out.get('proj_norm') is not None else torch.empty((N, L, B, 3), device=dev)
+        g_in = out.get('g_pose_in') if out.get('g_pose_in') is not None else torch.empty_like(pose_in)
+        nws = lib.p2c_fused_step_workspace_floats(N * L, B, a.input_6d)
+        ws = out.get('workspace')
+        if ws is None or ws.numel() < nws:
+            ws = torch.empty(max(int(nws), 1), device=dev)
+        losses = out.get('losses') if out.get('losses') is not None else torch.empty(8, device=dev)
+        a.rel_rot, a.abs_rot, a.abs_loc, a.proj, a.proj_norm = (ptr(rel_rot), ptr(abs_rot), ptr(abs_loc), ptr(proj),
+                                                                ptr(proj_norm))
+        a.g_pose_in, a.workspace, a.losses = ptr(g_in), ptr(ws), ptr(losses)
+        check(lib.p2c_fused_step(a, stream()), 'fused_step')
+        ctx.save_for_backward(g_in)
+        ctx.weights = (a.weight_2d, a.weight_3d)
+        res = cfg.setdefault('_result', FusedStepResult())
+        res.losses = losses
+        res.relative_pose_rot, res.absolute_pose_rot, res.absolute_pose_loc = rel_rot, abs_rot, abs_loc
+        res.projection_2d, res.projection_2d_transformed = proj, proj_norm
+        return losses[0].clone(), losses[1].clone(), losses[2].clone()
+
+    @staticmethod
+    def backward(ctx, g2d, g3d, g23):
+        # g_pose_in holds d(w2*loc_2d + w3*loc_3d)/d pose_in.  The common case (loss = loc_2d_3d or the weighted
+        # sum) is a pure scale; separate upstream weights on loc_2d / loc_3d alone are not representable from the
+        # single stored gradient and raise instead of silently returning something wrong.
+        (g_in,) = ctx.saved_tensors
+        for g in (g2d, g3d):
+            if g is not None and bool((g != 0).any()):
+                raise RuntimeError('fused_step: backpropagate through loc_2d_3d (the fused sum); for loc_2d or '
+                                   'loc_3d alone call fused_step with weight_3d=0 or weight_2d=0')
+        if g23 is None:
+            return None, None
+        return g_in * g23, None
+
+
+def fused_step(pose_in, tree, camera, ref_loc, ref_rot, gt_2d, gt_3d, ref_index=None, world_loc=None, world_rot=None,
+               mode=_lib.MODE_POSE_CHANGES, hips=1, neck=8, normalize=True, mask_missing_joints=True, weight_2d=1.0,
+               weight_3d=1.0, want_transformed=True, out=None):
+    """One pose_lifting step of the hot path in one call.  pose_in: (N,L,B,6) rotation_6d model output or
+    (N,L,B,3,3) matrices.  Returns FusedStepResult; .loc_2d_3d (= weight_2d*loc_2d + weight_3d*loc_3d) carries
+    the autograd edge back to pose_in.  `out` may hold preallocated buffers (CUDA-graph friendly)."""
+    cfg = dict(tree=tree, camera=camera, ref_loc=ref_loc, ref_rot=ref_rot, gt_2d=gt_2d, gt_3d=gt_3d,
+               ref_index=ref_index, world_loc=world_loc, world_rot=world_rot, mode=mode, hips=hips, neck=neck,
+               normalize=normalize, mask_missing_joints=mask_missing_joints, weight_2d=weight_2d,
+               weight_3d=weight_3d, want_transformed=want_transformed, out=out)
+    l2, l3, l23 = _FusedStep.apply(pose_in, cfg)
+    res = cfg['_result']
+    res.loc_2d, res.loc_3d, res.loc_2d_3d = l2.detach(), l3.detach(), l23
+    return res

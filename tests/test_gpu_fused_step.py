@@ -1,0 +1,185 @@
+"""GPU parity of p2c_fused_step (ProjectionModule -> Normalizer -> loc_2d/loc_3d/loc_2d_3d fwd + bwd) against the
+oracle, the committed golden fixture (outputs of the reference's own code), and size-independent properties at
+BASELINE.json's full sizes."""
+import numpy as np
+import pytest
+import torch
+
+import oracle as O
+from _util import assert_close, make_case, make_targets, oracle_step, smpl_parents
+
+pytestmark = pytest.mark.gpu
+
+DEV = 'cuda:0'
+
+
+@pytest.fixture(scope='module')
+def ops():
+    from pedestrians_video_2_carla_b200 import ops as _ops
+    return _ops
+
+
+@pytest.fixture(scope='module')
+def lib():
+    from pedestrians_video_2_carla_b200 import _lib
+    _lib.load()
+    return _lib
+
+
+def cu(t):
+    return None if t is None else t.float().to(DEV)
+
+
+def run_cuda(ops, lib, c, pose, gt2, gt3, mode, normalize, mask, w2=1.0, w3=1.0):
+    cam = c['cam']
+    wl = wr = None
+    if c['wl'] is not None:
+        wl, wr = O.calculate_world_from_changes((c['n'], c['l']), c['wl'], c['wr'], dtype=torch.float64)
+    x = cu(pose).requires_grad_(True)
+    res = ops.fused_step(x, lib.make_tree(c['par']), lib.make_camera(cam.R.tolist(), cam.T.tolist(), cam.f, cam.px, cam.py),
+                         cu(c['loc']), cu(c['rot']), cu(gt2), cu(gt3), ref_index=c['sid'].int().to(DEV),
+                         world_loc=cu(wl), world_rot=cu(wr),
+                         mode=lib.MODE_POSE_CHANGES if mode == 'pose_changes' else lib.MODE_RELATIVE_ROT,
+                         hips=c['hips'], neck=c['neck'], normalize=normalize, mask_missing_joints=mask,
+                         weight_2d=w2, weight_3d=w3)
+    res.loc_2d_3d.backward()
+    return res, x.grad
+
+
+def compare(res, grad, want, ref_grad, normalize=True):
+    assert_close('relative_pose_rot', res.relative_pose_rot, want['relative_pose_rot'])
+    assert_close('absolute_pose_rot', res.absolute_pose_rot, want['absolute_pose_rot'])
+    assert_close('absolute_pose_loc', res.absolute_pose_loc, want['absolute_pose_loc'])
+    assert_close('projection_2d', res.projection_2d, want['projection_2d'])
+    if normalize:
+        assert_close('projection_2d_transformed', res.projection_2d_transformed, want['projection_2d_transformed'])
+    assert_close('loc_2d', res.loc_2d, want['loc_2d'])
+    assert_close('loc_3d', res.loc_3d, want['loc_3d'])
+    assert_close('loc_2d_3d', res.loc_2d_3d, want['loc_2d_3d'])
+    assert_close('grad', grad, ref_grad)
+
+
+@pytest.mark.parametrize('mode', ['pose_changes', 'relative_rot'])
+@pytest.mark.parametrize('six_d', [True, False])
+@pytest.mark.parametrize('normalize,mask', [(True, True), (False, False), (True, False)])
+def test_fused_step_carla(ops, lib, mode, six_d, normalize, mask):
+    c = make_case(12, 16, 100 + 7 * six_d + normalize + 2 * mask)
+    gt2, gt3 = make_targets(c, mode, normalize)
+    d6 = c['d6'].clone().requires_grad_(True)
+    mats = O.rotation_6d_to_matrix(d6)
+    mats.retain_grad()
+    want = oracle_step(c, mats, mode, normalize, mask, gt=(gt2, gt3))
+    want['loc_2d_3d'].backward()
+    if six_d:
+        res, grad = run_cuda(ops, lib, c, c['d6'], gt2, gt3, mode, normalize, mask)
+        compare(res, grad, want, d6.grad, normalize)
+    else:
+        res, grad = run_cuda(ops, lib, c, mats.detach(), gt2, gt3, mode, normalize, mask)
+        compare(res, grad, want, mats.grad, normalize)
+
+
+@pytest.mark.parametrize('n,l', [(1, 1), (3, 1), (2, 64), (33, 5), (64, 16)])
+def test_fused_step_shapes(ops, lib, n, l):
+    """Ragged / extreme clip shapes incl. C1 (64x16, reference tests/walker_control batch)."""
+    c = make_case(n, l, 7 * n + l, world=(n % 2 == 1))
+    gt2, gt3 = make_targets(c)
+    d6 = c['d6'].clone().requires_grad_(True)
+    want = oracle_step(c, O.rotation_6d_to_matrix(d6), gt=(gt2, gt3))
+    want['loc_2d_3d'].backward()
+    res, grad = run_cuda(ops, lib, c, c['d6'], gt2, gt3, 'pose_changes', True, True)
+    compare(res, grad, want, d6.grad)
+
+
+def test_fused_step_weights(ops, lib):
+    c = make_case(6, 4, 5)
+    gt2, gt3 = make_targets(c)
+    d6 = c['d6'].clone().requires_grad_(True)
+    want = oracle_step(c, O.rotation_6d_to_matrix(d6), gt=(gt2, gt3))
+    (0.25 * want['loc_2d'] + 3.0 * want['loc_3d']).backward()
+    res, grad = run_cuda(ops, lib, c, c['d6'], gt2, gt3, 'pose_changes', True, True, w2=0.25, w3=3.0)
+    assert_close('weighted loss', res.loc_2d_3d, 0.25 * want['loc_2d'] + 3.0 * want['loc_3d'])
+    assert_close('weighted grad', grad, d6.grad)
+
+
+def test_fused_step_smpl_tree(ops, lib):
+    """data/smpl/utils.py:106 drives P3dPose with the 22-bone SMPL tree: the path must accept arbitrary trees."""
+    c = make_case(5, 8, 77, par=smpl_parents())
+    gt2, gt3 = make_targets(c)
+    d6 = c['d6'].clone().requires_grad_(True)
+    want = oracle_step(c, O.rotation_6d_to_matrix(d6), gt=(gt2, gt3))
+    want['loc_2d_3d'].backward()
+    res, grad = run_cuda(ops, lib, c, c['d6'], gt2, gt3, 'pose_changes', True, True)
+    compare(res, grad, want, d6.grad)
+
+
+def test_fused_step_non_orthonormal_matrices(ops, lib):
+    """Matrix input is not assumed to be a rotation (reference tests/walker_control/test_p3d_pose.py:93-95)."""
+    c = make_case(4, 6, 31)
+    gt2, gt3 = make_targets(c)
+    mats = (O.rotation_6d_to_matrix(c['d6']) + 0.1 * torch.randn((4, 6, 26, 3, 3), generator=c['gen'],
+                                                                dtype=torch.float64)).requires_grad_(True)
+    want = oracle_step(c, mats, gt=(gt2, gt3))
+    want['loc_2d_3d'].backward()
+    res, grad = run_cuda(ops, lib, c, mats.detach(), gt2, gt3, 'pose_changes', True, True)
+    compare(res, grad, want, mats.grad)
+
+
+@pytest.mark.parametrize('mode', ['pose_changes', 'relative_rot'])
+def test_fused_step_golden_fixture(ops, lib, golden, mode):
+    """tests/golden/reference_run.npz: outputs of the reference's OWN code for the full step."""
+    k = mode + '/'
+    loc, rot, _, par = O.reference_tensors(torch.float64)
+    n, l = golden[k + 'd6'].shape[:2]
+    c = dict(n=n, l=l, b=26, par=par, loc=loc, rot=rot, sid=torch.as_tensor(golden['skeleton_id']).long(),
+             wl=torch.as_tensor(golden[k + 'world_loc_change']).double(),
+             wr=torch.as_tensor(golden[k + 'world_rot_change']).double(), cam=O.training_camera(), hips=O.HIPS,
+             neck=O.NECK)
+    res, grad = run_cuda(ops, lib, c, torch.as_tensor(golden[k + 'd6']).double(),
+                         torch.as_tensor(golden[k + 'gt_projection_2d_transformed']).double(),
+                         torch.as_tensor(golden[k + 'gt_absolute_pose_loc']).double(), mode, True, True)
+    for key, got in (('relative_pose_rot', res.relative_pose_rot), ('absolute_pose_loc', res.absolute_pose_loc),
+                     ('absolute_pose_rot', res.absolute_pose_rot), ('projection_2d', res.projection_2d),
+                     ('projection_2d_transformed', res.projection_2d_transformed), ('loc_2d', res.loc_2d),
+                     ('loc_3d', res.loc_3d), ('loc_2d_3d', res.loc_2d_3d)):
+        assert_close('golden ' + key, got, torch.as_tensor(np.asarray(golden[k + key])), tol=2e-4)
+    assert_close('golden grad_d6', grad, torch.as_tensor(golden[k + 'grad_d6']), tol=1e-3)
+
+
+@pytest.mark.parametrize('n,l', [(256, 16), (4096, 64)])
+def test_full_size_properties(ops, lib, n, l):
+    """BASELINE configs C2 (256x16) and C4 (4096x64): properties that need no oracle run at full size.
+    (1) identity changes => rel_rot == reference rot, every clip of one skeleton type equal
+        (reference tests/walker_control/test_p3d_pose.py:58-91);
+    (2) clip independence: a slice of the batch run alone gives bit-identical outputs;
+    (3) targets == own outputs => loss 0 and gradient 0."""
+    g = torch.Generator().manual_seed(n + l)
+    loc, rot, _, par = O.reference_tensors(torch.float32)
+    cam = O.training_camera()
+    tree, cams = lib.make_tree(par), lib.make_camera(cam.R.tolist(), cam.T.tolist(), cam.f, cam.px, cam.py)
+    sid = torch.randint(0, 4, (n,), generator=g).int().to(DEV)
+    loc, rot = loc.to(DEV), rot.to(DEV)
+    ident = torch.tensor([1., 0, 0, 0, 1, 0]).expand(n, l, 26, 6).contiguous().to(DEV)
+    zeros = torch.zeros((n, l, 26, 3), device=DEV)
+    r = ops.fused_step(ident, tree, cams, loc, rot, zeros, zeros, ref_index=sid)
+    assert torch.equal(r.relative_pose_rot, rot[sid.long()].unsqueeze(1).expand(n, l, 26, 3, 3))
+    first = [int((sid == k).nonzero()[0]) for k in range(4)]
+    for k in range(4):
+        same = r.absolute_pose_loc[sid == k]
+        assert torch.equal(same, same[:1].expand_as(same))
+        assert torch.equal(r.projection_2d[first[k], 0], r.projection_2d[first[k], l - 1])
+
+    d6 = (torch.randn((n, l, 26, 6), generator=g) * 0.3 + torch.tensor([1., 0, 0, 0, 1, 0])).to(DEV)
+    full = ops.fused_step(d6, tree, cams, loc, rot, zeros, zeros, ref_index=sid)
+    lo, hi = n // 3, n // 3 + 17
+    part = ops.fused_step(d6[lo:hi].contiguous(), tree, cams, loc, rot, zeros[lo:hi].contiguous(),
+                          zeros[lo:hi].contiguous(), ref_index=sid[lo:hi].contiguous())
+    assert torch.equal(part.absolute_pose_loc, full.absolute_pose_loc[lo:hi])
+    assert torch.equal(part.projection_2d, full.projection_2d[lo:hi])
+    assert torch.equal(part.relative_pose_rot, full.relative_pose_rot[lo:hi])
+
+    x = d6.clone().requires_grad_(True)
+    again = ops.fused_step(x, tree, cams, loc, rot, full.projection_2d_transformed, full.absolute_pose_loc,
+                           ref_index=sid, mask_missing_joints=False)
+    again.loc_2d_3d.backward()
+    assert float(again.loc_2d_3d) == 0.0
+    assert float(x.grad.abs().max()) == 0.0
