@@ -424,9 +424,9 @@ extern "C" int p2c_fk_fwd(const p2c_fk_fwd_t* p, void* stream) {
     if (rc) return rc;
     if (p->n_clips < 0 || p->clip_len < 1) return P2C_E_BADARG;
     if (p->mode != P2C_MODE_POSE_CHANGES && p->mode != P2C_MODE_RELATIVE_ROT) return P2C_E_BADARG;
+    if (p->n_clips == 0) return 0;  // empty batch: nothing to read or write (empty tensors have NULL storage)
     if (!p->pose_in || !p->ref_loc) return P2C_E_NULL;
     if (p->mode == P2C_MODE_POSE_CHANGES && !p->ref_rot) return P2C_E_NULL;
-    if (p->n_clips == 0) return 0;
     a.N = p->n_clips; a.L = p->clip_len;
     a.pose_in = p->pose_in; a.ref_loc = p->ref_loc; a.ref_rot = p->ref_rot; a.ref_index = p->ref_index;
     a.world_loc = p->world_loc; a.world_rot = p->world_rot; a.cam = p->camera;
@@ -447,6 +447,7 @@ extern "C" int p2c_fk_bwd(const p2c_fk_bwd_t* p, void* stream) {
     if (rc) return rc;
     if (p->n_clips < 0 || p->clip_len < 1) return P2C_E_BADARG;
     if (p->mode != P2C_MODE_POSE_CHANGES && p->mode != P2C_MODE_RELATIVE_ROT) return P2C_E_BADARG;
+    if (p->n_clips == 0) return 0;
     if (!p->pose_in || !p->ref_loc || !p->abs_rot || !p->g_pose_in) return P2C_E_NULL;
     if (p->mode == P2C_MODE_POSE_CHANGES && (!p->ref_rot || !p->rel_rot)) return P2C_E_NULL;
     if (p->g_proj && !p->abs_loc) return P2C_E_NULL;

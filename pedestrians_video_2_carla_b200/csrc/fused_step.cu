@@ -209,9 +209,9 @@ extern "C" int p2c_fused_step(const p2c_fused_step_t* p, void* stream) {
     const int B = p->tree.n_bones;
     if (p->n_clips < 0 || p->clip_len < 1 || p->gt_2d_channels < 2) return P2C_E_BADARG;
     if (p->hips < 0 || p->hips >= B || p->neck < 0 || p->neck >= B) return P2C_E_BADARG;
+    if (p->n_clips == 0) return 0;
     if (!p->pose_in || !p->ref_loc || !p->gt_2d || !p->gt_3d || !p->g_pose_in || !p->workspace || !p->losses)
         return P2C_E_NULL;
-    if (p->n_clips == 0) return 0;
     if (p2c_fused_carla_supported(p)) return p2c_fused_carla(p, stream);
 
     if (!p->rel_rot && p->mode == P2C_MODE_POSE_CHANGES) return P2C_E_NULL;

@@ -170,7 +170,15 @@ def test_world_scan(ops):
     ul = torch.randn((n, l, 3), generator=g, dtype=torch.float64)
     ur = torch.randn((n, l, 3, 3), generator=g, dtype=torch.float64)
     a, b = dl.clone().requires_grad_(True), dr.clone().requires_grad_(True)
-    wl, wr = O.calculate_world_from_changes((n, l), a, b, il, ir, dtype=torch.float64)
+    # functional restatement of utils/world.py:56-61 (the reference writes slices in place, which torch autograd
+    # refuses once rot_change requires grad); values are checked against the oracle below
+    rots, locs = [ir], [il]
+    for i in range(l):
+        rots.append(torch.bmm(rots[-1], b[:, i]))
+        locs.append(locs[-1] + a[:, i])
+    wl, wr = torch.stack(locs[1:], 1), torch.stack(rots[1:], 1)
+    owl, owr = O.calculate_world_from_changes((n, l), dl, dr, il, ir, dtype=torch.float64)
+    assert torch.equal(owl, wl.detach()) and torch.equal(owr, wr.detach())
     ((wl * ul).sum() + (wr * ur).sum()).backward()
     ca, cb = cu(dl).requires_grad_(True), cu(dr).requires_grad_(True)
     cwl, cwr = ops.world_scan(ca, cb, cu(il), cu(ir))
