@@ -141,7 +141,7 @@ class Shard(object):
             s['args'] = self._args(s)
             self.sets.append(s)
         nws = self.cdll.p2c_fused_step_workspace_floats(self.poses, B, 1)
-        ws = torch.empty(max(int(nws), 1), device=dev)   # scratch, shared by all sets (steps are stream-ordered)
+        ws = torch.zeros(max(int(nws), 1), device=dev)   # scratch, shared by all sets (steps are stream-ordered)
         for s in self.sets:
             s['ws'] = ws
             s['args'].workspace = _lib.ptr(ws)

@@ -175,7 +175,9 @@ typedef struct {
     float* proj;                 /* out (N,L,B,3)                                                    */
     float* proj_norm;            /* out (N,L,B,3) normalised projection or NULL                      */
     float* g_pose_in;            /* out, same shape as pose_in                                       */
-    float* workspace;            /* p2c_fused_step_workspace_floats(N*L, B, input_6d) floats         */
+    float* workspace;            /* p2c_fused_step_workspace_floats(N*L, B, input_6d) floats; its first 16 floats
+                                    are self-resetting counters: zero them ONCE before the first call, every call
+                                    leaves them zero again; do not share one workspace between concurrent streams */
     float* losses;               /* out, 8 floats                                                    */
 } p2c_fused_step_t;
 int64_t p2c_fused_step_workspace_floats(int64_t n_poses, int32_t n_bones, int32_t input_6d);

@@ -1,0 +1,587 @@
+// p2c_fused_fast: the single-pass fused step for rotation_6d input (the pose_lifting training path):
+//   rotation_6d_to_matrix (movements.py:113-116) -> relative-rotation scan over frames (layers/projection.py:170-195,
+//   p3d_pose.py:98-114) -> FK over the bone tree (p3d_pose.py:116-184) -> P3dPoseProjection.forward
+//   (p3d_pose_projection.py:115-152) -> Normalizer(HipsNeckExtractor) (normalizer.py:20-41) -> loc_2d / loc_3d /
+//   loc_2d_3d (loss/loc_2d.py, loc_3d.py, loc_2d_3d.py) AND d(w2*loc_2d + w3*loc_3d)/d(6-D input), in ONE kernel
+//   (plus a tiny mask-count pre-pass when mask_missing_joints is on).
+//
+// Mapping: one CTA per clip (persistent loop over clips), one warp per frame, lane b = bone b.
+//   phase A  every warp: 6-D -> C[t] (Gram-Schmidt)                        -> smem Rs[t]
+//   phase B  26 threads: R[t] = C[t] . R[t-1] serial over the clip's frames (in place), then rel_rot leaves as one
+//            coalesced block copy
+//   phase C  every warp, its frames: FK by pointer jumping over warp shuffles (ceil(log2(depth+1)) rounds instead
+//            of one round per tree level), projection, normaliser, loss terms, loss gradient, and the tree
+//            backward as a prefix sum over the DFS-ordered lanes                -> smem Ys[t] = R[t]^T dL/dR[t]
+//   phase D  suffix sum of Ys over the frames (the reverse-time scan reduces to additions, see below)
+//   phase E  every warp: dL/dC[t] = R[t] Z[t] R[t-1]^T, Gram-Schmidt backward -> grad wrt 6-D, coalesced store
+//
+// The backward uses that every matrix on this path is a rotation (C[t] comes out of Gram-Schmidt, the reference
+// rotations out of Euler angles, products of rotations are rotations):
+//   dL/dA_b   = A_b . M_b,   M_b = sum_{d in subtree(b)} (t_d - t_b)^T (x) g_d        (g_d = dL/d abs_loc[d])
+//   Y_b[t]   := R_b[t]^T dL/dR_b[t]|direct = A_p . M_b . A_p^T                         (p = parent of b)
+//   dL/dR[t]  (with the contributions of later frames) = R[t] . sum_{s >= t} Y[s]
+// so subtree sums are differences of an inclusive prefix scan over lanes (the bone axis is a DFS pre-order, every
+// subtree is a contiguous lane range) and the reverse-time product scan is a plain suffix sum.  Arbitrary
+// (non-rotation) 3x3 input takes the exact generic path in fk_kernels.cu / fused_step.cu instead.
+#include <stdlib.h>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int MAX_ROUNDS = 5;
+constexpr int IDENT_LANE = 31;  // holds the identity transform for lanes without an ancestor at the jump distance
+constexpr int COUNT_BLOCKS = 296;
+
+struct FastArgs {
+    int N, L, GL, B, slot;  // clips, frames per clip, frames per CTA group, bones, B*9
+    int scan;               // 1: pose_changes, 0: relative_rot
+    int hips, neck, normalize, mask, gt_c, nrounds;
+    int8_t parent[P2C_MAX_BONES];
+    int8_t sub_end[P2C_MAX_BONES];
+    int32_t anc_packed[P2C_MAX_BONES];  // 5 bits per round: lane of the 2^k-th ancestor, IDENT_LANE if none
+    const float* d6;
+    const float* ref_loc;
+    const float* ref_rot;
+    const int32_t* ref_index;
+    const float* world_loc;
+    const float* world_rot;
+    p2c_camera_t cam;
+    const float* gt2;
+    const float* gt3;
+    float w2, w3;
+    float* rel_rot;
+    float* abs_rot;
+    float* abs_loc;
+    float* proj;
+    float* proj_norm;
+    float* g_d6;
+    float* partials;       // gridDim.x x 2
+    unsigned int* ticket;  // self-resetting
+    int* count2;           // self-resetting, filled by count_kernel when mask is on
+    float* losses;
+    double count3;
+};
+
+struct GS {
+    V3 b1, b2, b3, a2;
+    float inv1, inv2, s;
+    bool deg1, deg2;
+};
+
+__device__ __forceinline__ float dot3(const V3& a, const V3& b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
+__device__ __forceinline__ V3 cross3(const V3& a, const V3& b) {
+    return V3{a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x};
+}
+
+// pytorch3d rotation_6d_to_matrix; F.normalize(v) = v / max(|v|, 1e-12) written as v * rsqrt(max(|v|^2, 1e-24))
+__device__ __forceinline__ GS gram_schmidt(const float* a) {
+    GS r;
+    const V3 a1{a[0], a[1], a[2]};
+    r.a2 = V3{a[3], a[4], a[5]};
+    const float n1 = dot3(a1, a1);
+    r.deg1 = !(n1 > 1e-24f);
+    r.inv1 = rsqrtf(fmaxf(n1, 1e-24f));
+    r.b1 = V3{a1.x * r.inv1, a1.y * r.inv1, a1.z * r.inv1};
+    r.s = dot3(r.b1, r.a2);
+    const V3 u{fmaf(-r.s, r.b1.x, r.a2.x), fmaf(-r.s, r.b1.y, r.a2.y), fmaf(-r.s, r.b1.z, r.a2.z)};
+    const float n2 = dot3(u, u);
+    r.deg2 = !(n2 > 1e-24f);
+    r.inv2 = rsqrtf(fmaxf(n2, 1e-24f));
+    r.b2 = V3{u.x * r.inv2, u.y * r.inv2, u.z * r.inv2};
+    r.b3 = cross3(r.b1, r.b2);
+    return r;
+}
+
+// backward of gram_schmidt: g = dL/d(rows b1, b2, b3) -> dL/d(a1, a2)
+__device__ __forceinline__ void gram_schmidt_bwd(const GS& r, const M3& g, float* out) {
+    const V3 g1{g.m[0], g.m[1], g.m[2]}, g2{g.m[3], g.m[4], g.m[5]}, g3{g.m[6], g.m[7], g.m[8]};
+    V3 c = cross3(r.b2, g3);
+    V3 gb1{g1.x + c.x, g1.y + c.y, g1.z + c.z};
+    c = cross3(g3, r.b1);
+    const V3 gb2{g2.x + c.x, g2.y + c.y, g2.z + c.z};
+    const float d2 = r.deg2 ? 0.f : dot3(r.b2, gb2);
+    const V3 gu{(gb2.x - r.b2.x * d2) * r.inv2, (gb2.y - r.b2.y * d2) * r.inv2, (gb2.z - r.b2.z * d2) * r.inv2};
+    const float du = dot3(r.b1, gu);
+    out[3] = fmaf(-du, r.b1.x, gu.x);
+    out[4] = fmaf(-du, r.b1.y, gu.y);
+    out[5] = fmaf(-du, r.b1.z, gu.z);
+    gb1.x -= fmaf(r.s, gu.x, du * r.a2.x);
+    gb1.y -= fmaf(r.s, gu.y, du * r.a2.y);
+    gb1.z -= fmaf(r.s, gu.z, du * r.a2.z);
+    const float d1 = r.deg1 ? 0.f : dot3(r.b1, gb1);
+    out[0] = (gb1.x - r.b1.x * d1) * r.inv1;
+    out[1] = (gb1.y - r.b1.y * d1) * r.inv1;
+    out[2] = (gb1.z - r.b1.z * d1) * r.inv1;
+}
+
+__device__ __forceinline__ void load6(const float* __restrict__ p, float* a) {
+    const float2* p2 = reinterpret_cast<const float2*>(p);  // 24-byte records: always 8-byte aligned
+    const float2 x = __ldg(p2), y = __ldg(p2 + 1), z = __ldg(p2 + 2);
+    a[0] = x.x; a[1] = x.y; a[2] = y.x; a[3] = y.y; a[4] = z.x; a[5] = z.y;
+}
+
+// coalesced smem -> global copies; the widest vector both sides are aligned for
+__device__ __forceinline__ void copy_out(float* __restrict__ g, const float* __restrict__ s, int n, int tid, int nthr) {
+    const uintptr_t both = reinterpret_cast<uintptr_t>(g) | (uintptr_t)__cvta_generic_to_shared(s);
+    if (((both & 15) == 0) && ((n & 3) == 0)) {
+        float4* g4 = reinterpret_cast<float4*>(g);
+        const float4* s4 = reinterpret_cast<const float4*>(s);
+        for (int i = tid; i < (n >> 2); i += nthr) g4[i] = s4[i];
+    } else if (((both & 7) == 0) && ((n & 1) == 0)) {
+        float2* g2 = reinterpret_cast<float2*>(g);
+        const float2* s2 = reinterpret_cast<const float2*>(s);
+        for (int i = tid; i < (n >> 1); i += nthr) g2[i] = s2[i];
+    } else {
+        for (int i = tid; i < n; i += nthr) g[i] = s[i];
+    }
+}
+
+// utils/tensors.py:29-40 count of kept (joint, channel) pairs of the 2-D targets (integer => order independent)
+__global__ void __launch_bounds__(256) count_kernel(const float* __restrict__ gt2, long total, int B, int gt_c, int hips,
+                                                   int* __restrict__ count) {
+    int c = 0;
+    for (long i = (long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long)gridDim.x * 256) {
+        const float* g = gt2 + i * gt_c;
+        const int j = (int)(i % B);
+        if (j == hips || (__ldg(g) != 0.f && __ldg(g + 1) != 0.f)) c += 2;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(FULL_MASK, c, o);
+    __shared__ int sh[8];
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = c;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int t = 0;
+        for (int w = 0; w < 8; ++w) t += sh[w];
+        if (t) atomicAdd(count, t);
+    }
+}
+
+__device__ __forceinline__ int round4(int x) { return (x + 3) & ~3; }
+
+template <int WARPS>
+__global__ void __launch_bounds__(WARPS * 32, (WARPS == 8 ? 2 : 1)) fast_kernel(const FastArgs a) {
+    extern __shared__ __align__(16) float smem[];
+    constexpr int NT = WARPS * 32;
+    const int tid = threadIdx.x, lane = tid & 31, wib = tid >> 5;
+    const int B = a.B, slot = a.slot;
+    const bool act = lane < B;
+    float* Rs = smem;                               // [GL][slot]  C[t], then R[t] (= the rel_rot records of the group)
+    float* Ys = Rs + round4(a.GL * slot);           // [GL][slot]  abs_rot staging, then Y[t], then its suffix sum
+    float* WB = Ys + round4(a.GL * slot) + wib * round4(B * 6);  // per-warp staging of the 3- and 6-float records
+    float* red = Ys + round4(a.GL * slot) + WARPS * round4(B * 6);
+
+    const int par = act ? a.parent[lane] : -1;
+    const int psrc = par < 0 ? IDENT_LANE : par;
+    const int sub_end = act ? a.sub_end[lane] : lane;
+    const int ancp = act ? a.anc_packed[lane] : 0x1ffffff;  // all rounds -> IDENT_LANE
+    const long total_poses = (long)a.N * a.L;
+    const long groups = a.scan ? (long)a.N : (total_poses + a.GL - 1) / a.GL;
+    const float k2 = a.w2 * 2.0f / (a.mask ? (float)__ldcg(a.count2) : (float)(total_poses * B * 2));
+    const float k3 = a.w3 * 2.0f / (float)a.count3;
+    const M3 camR = m3_from(a.cam.R);
+    float s2 = 0.f, s3 = 0.f;
+
+    for (long grp = blockIdx.x; grp < groups; grp += gridDim.x) {
+        const long m0 = grp * a.GL;
+        const int nf = (int)min((long)a.GL, total_poses - m0);
+
+        // ---- phase A: 6-D -> C[t]
+        for (int f = wib; f < nf; f += WARPS) {
+            if (act) {
+                float d[6];
+                load6(a.d6 + ((m0 + f) * B + lane) * 6, d);
+                const GS r = gram_schmidt(d);
+                float* o = Rs + f * slot + lane * 9;
+                o[0] = r.b1.x; o[1] = r.b1.y; o[2] = r.b1.z;
+                o[3] = r.b2.x; o[4] = r.b2.y; o[5] = r.b2.z;
+                o[6] = r.b3.x; o[7] = r.b3.y; o[8] = r.b3.z;
+            }
+        }
+        __syncthreads();
+        // ---- phase B: R[t] = C[t] . R[t-1] per bone (p3d_pose.py:98-114 looped by layers/projection.py:190-193)
+        if (a.scan) {
+            if (tid < B) {
+                const long row = a.ref_index ? (long)__ldg(a.ref_index + grp) : grp;
+                M3 prev;
+                const float* rr = a.ref_rot + (row * B + tid) * 9;
+#pragma unroll
+                for (int i = 0; i < 9; ++i) prev.m[i] = __ldg(rr + i);
+                for (int f = 0; f < nf; ++f) {
+                    float* o = Rs + f * slot + tid * 9;
+                    prev = m3_mul(m3_from(o), prev);
+                    m3_to(o, prev);
+                }
+            }
+            __syncthreads();
+        }
+        if (a.rel_rot) copy_out(a.rel_rot + m0 * slot, Rs, nf * slot, tid, NT);
+
+        // ---- phase C: per frame FK + projection + loss + tree backward
+        for (int f = wib; f < nf; f += WARPS) {
+            const long m = m0 + f;
+            const long clip = a.scan ? grp : m / a.L;
+            const long row = a.ref_index ? (long)__ldg(a.ref_index + clip) : clip;
+            V3 l{0.f, 0.f, 0.f}, g3{0.f, 0.f, 0.f};
+            float g2x = 0.f, g2y = 0.f;
+            M3 A = m3_identity();
+            if (act) {
+                const float* rl = a.ref_loc + (row * B + lane) * 3;
+                l = V3{__ldg(rl), __ldg(rl + 1), __ldg(rl + 2)};
+                const float* q3 = a.gt3 + (m * B + lane) * 3;
+                g3 = V3{__ldg(q3), __ldg(q3 + 1), __ldg(q3 + 2)};
+                const float* q2 = a.gt2 + (m * B + lane) * a.gt_c;
+                g2x = __ldg(q2); g2y = __ldg(q2 + 1);
+                A = m3_from(Rs + f * slot + lane * 9);
+            }
+            // FK by pointer jumping: (A, t) <- (A, t) o (A, t)[2^k-th ancestor]; abs = rel o parent o ... o root
+            V3 t = l;
+            for (int k = 0; k < a.nrounds; ++k) {
+                const int src = (ancp >> (5 * k)) & 31;
+                const M3 Am = m3_shfl(A, src);
+                const V3 tm = v3_shfl(t, src);
+                const V3 q = v3_mul_m(t, Am);
+                t = V3{q.x + tm.x, q.y + tm.y, q.z + tm.z};
+                A = m3_mul(A, Am);
+            }
+            float* ys = Ys + f * slot;
+            if (a.abs_rot) {
+                if (act) m3_to(ys + lane * 9, A);
+                __syncwarp();
+                copy_out(a.abs_rot + m * slot, ys, slot, lane, 32);
+            }
+            // projection (p3d_pose_projection.py:137-152)
+            V3 c;
+            {
+                V3 wp{t.y, -t.x, t.z};
+                if (a.world_rot) wp = v3_mul_m(wp, m3_from(a.world_rot + m * 9));
+                if (a.world_loc) { wp.x += __ldg(a.world_loc + m * 3); wp.y += __ldg(a.world_loc + m * 3 + 1); wp.z += __ldg(a.world_loc + m * 3 + 2); }
+                c = v3_mul_m(wp, camR);
+                c.x += a.cam.T[0]; c.y += a.cam.T[1]; c.z += a.cam.T[2];
+            }
+            const float iz = 1.0f / c.z;
+            const V3 p{a.cam.px - a.cam.f * c.x * iz, a.cam.py - a.cam.f * c.y * iz, iz};
+            if (act) {
+                WB[lane * 3] = t.x; WB[lane * 3 + 1] = t.y; WB[lane * 3 + 2] = t.z;
+                WB[B * 3 + lane * 3] = p.x; WB[B * 3 + lane * 3 + 1] = p.y; WB[B * 3 + lane * 3 + 2] = p.z;
+            }
+            __syncwarp();
+            if (a.abs_loc) copy_out(a.abs_loc + m * B * 3, WB, B * 3, lane, 32);
+            if (a.proj) copy_out(a.proj + m * B * 3, WB + B * 3, B * 3, lane, 32);
+            __syncwarp();
+
+            // Normalizer(HipsNeckExtractor) + loc_2d + loc_3d and their gradient wrt (proj, abs_loc)
+            const float sx = __shfl_sync(FULL_MASK, p.x, a.hips), sy = __shfl_sync(FULL_MASK, p.y, a.hips);
+            const float dx = __shfl_sync(FULL_MASK, p.x, a.neck) - sx, dy = __shfl_sync(FULL_MASK, p.y, a.neck) - sy;
+            const float scale = sqrtf(dx * dx + dy * dy);
+            const bool okn = scale > 0.f && scale <= 3.402823466e38f;
+            float x = p.x, y = p.y, q = p.z;
+            bool lx = true, ly = true;
+            if (a.normalize) {
+                const float rx = (p.x - sx) / scale, ry = (p.y - sy) / scale;
+                lx = fabsf(rx) <= 3.402823466e38f;
+                ly = fabsf(ry) <= 3.402823466e38f;
+                x = lx ? rx : 0.f;
+                y = ly ? ry : 0.f;
+                q = nan_to_zero(q);
+                if (!(q >= 1e-5f)) { x = 0.f; y = 0.f; lx = ly = false; }
+                if (a.proj_norm) {
+                    if (act) { WB[lane * 3] = x; WB[lane * 3 + 1] = y; WB[lane * 3 + 2] = q; }
+                    __syncwarp();
+                    copy_out(a.proj_norm + m * B * 3, WB, B * 3, lane, 32);
+                    __syncwarp();
+                }
+            }
+            const bool kept = act && (!a.mask || lane == a.hips || (g2x != 0.f && g2y != 0.f));
+            float gx = 0.f, gy = 0.f;
+            if (kept) {
+                const float ex = x - g2x, ey = y - g2y;
+                s2 = fmaf(ex, ex, fmaf(ey, ey, s2));
+                gx = lx ? k2 * ex : 0.f;
+                gy = ly ? k2 * ey : 0.f;
+            }
+            if (a.normalize) {
+                if (!okn) { gx = 0.f; gy = 0.f; }
+                const float sgx = warp_sum(gx), sgy = warp_sum(gy), sgn = warp_sum(gx * x + gy * y);
+                gx = okn ? gx / scale : 0.f;
+                gy = okn ? gy / scale : 0.f;
+                if (okn) {
+                    const float gscale = -sgn / scale, ux = dx / scale, uy = dy / scale;
+                    float hx = -sgx / scale - gscale * ux, hy = -sgy / scale - gscale * uy;
+                    float kx = gscale * ux, ky = gscale * uy;
+                    if (a.hips == a.neck) { hx += kx; hy += ky; kx = 0.f; ky = 0.f; }
+                    if (lane == a.hips) { gx += hx; gy += hy; }
+                    if (lane == a.neck) { gx += kx; gy += ky; }
+                }
+            }
+            V3 g{0.f, 0.f, 0.f};  // dL / d abs_loc[lane]
+            if (act) {
+                const V3 e{t.x - g3.x, t.y - g3.y, t.z - g3.z};
+                s3 = fmaf(e.x, e.x, fmaf(e.y, e.y, fmaf(e.z, e.z, s3)));
+                // backward of the projection: (gx, gy, 0) -> camera point -> world point -> p3d point
+                V3 gc{-a.cam.f * gx * iz, -a.cam.f * gy * iz, a.cam.f * (gx * c.x + gy * c.y) * iz * iz};
+                V3 gw = v3_mul_mt(gc, camR);
+                if (a.world_rot) gw = v3_mul_mt(gw, m3_from(a.world_rot + m * 9));
+                g = V3{fmaf(k3, e.x, -gw.y), fmaf(k3, e.y, gw.x), fmaf(k3, e.z, gw.z)};
+            }
+            // tree backward: subtree sums of (t^T (x) g, g) as an inclusive prefix scan over the DFS-ordered lanes
+            float w[12] = {t.x * g.x, t.x * g.y, t.x * g.z, t.y * g.x, t.y * g.y, t.y * g.z,
+                           t.z * g.x, t.z * g.y, t.z * g.z, g.x, g.y, g.z};
+            float own[12];
+#pragma unroll
+            for (int i = 0; i < 12; ++i) own[i] = w[i];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+#pragma unroll
+                for (int i = 0; i < 12; ++i) {
+                    const float v = __shfl_up_sync(FULL_MASK, w[i], o);
+                    if (lane >= o) w[i] += v;
+                }
+            }
+            M3 Msub;
+            V3 Gs;
+            {
+                float s[12];
+#pragma unroll
+                for (int i = 0; i < 12; ++i) s[i] = __shfl_sync(FULL_MASK, w[i], sub_end) - (w[i] - own[i]);
+                Gs = V3{s[9], s[10], s[11]};
+                Msub.m[0] = fmaf(-t.x, Gs.x, s[0]); Msub.m[1] = fmaf(-t.x, Gs.y, s[1]); Msub.m[2] = fmaf(-t.x, Gs.z, s[2]);
+                Msub.m[3] = fmaf(-t.y, Gs.x, s[3]); Msub.m[4] = fmaf(-t.y, Gs.y, s[4]); Msub.m[5] = fmaf(-t.y, Gs.z, s[5]);
+                Msub.m[6] = fmaf(-t.z, Gs.x, s[6]); Msub.m[7] = fmaf(-t.z, Gs.y, s[7]); Msub.m[8] = fmaf(-t.z, Gs.z, s[8]);
+            }
+            const M3 Ap = m3_shfl(A, psrc);                 // IDENT_LANE keeps the identity for the root
+            const M3 Y = m3_mul_bt(m3_mul(Ap, Msub), Ap);   // R^T dL/dR = A_p M A_p^T
+            __syncwarp();                                   // abs_rot staging in ys has been copied out
+            if (act) m3_to(ys + lane * 9, Y);
+        }
+        __syncthreads();
+        // ---- phase D: Z[t] = sum_{s >= t} Y[s]
+        if (a.scan) {
+            for (int col = tid; col < slot; col += NT) {
+                float acc = 0.f;
+                for (int f = nf - 1; f >= 0; --f) {
+                    acc += Ys[f * slot + col];
+                    Ys[f * slot + col] = acc;
+                }
+            }
+            __syncthreads();
+        }
+        // ---- phase E: dL/dC[t] = R[t] Z[t] R[t-1]^T, then the Gram-Schmidt backward
+        for (int f = wib; f < nf; f += WARPS) {
+            const long m = m0 + f;
+            if (act) {
+                const M3 Z = m3_from(Ys + f * slot + lane * 9);
+                M3 G = m3_mul(m3_from(Rs + f * slot + lane * 9), Z);
+                if (a.scan) {
+                    M3 prev;
+                    if (f > 0) {
+                        prev = m3_from(Rs + (f - 1) * slot + lane * 9);
+                    } else {
+                        const long row = a.ref_index ? (long)__ldg(a.ref_index + grp) : grp;
+                        const float* rr = a.ref_rot + (row * B + lane) * 9;
+#pragma unroll
+                        for (int i = 0; i < 9; ++i) prev.m[i] = __ldg(rr + i);
+                    }
+                    G = m3_mul_bt(G, prev);
+                }
+                float d[6], o[6];
+                load6(a.d6 + (m * B + lane) * 6, d);
+                gram_schmidt_bwd(gram_schmidt(d), G, o);
+#pragma unroll
+                for (int i = 0; i < 6; ++i) WB[lane * 6 + i] = o[i];
+            }
+            __syncwarp();
+            copy_out(a.g_d6 + m * B * 6, WB, B * 6, lane, 32);
+            __syncwarp();
+        }
+        __syncthreads();
+    }
+
+    // ---- loss sums: fixed-order reduction, the last CTA to finish folds the per-CTA partials
+    s2 = warp_sum(s2);
+    s3 = warp_sum(s3);
+    if (lane == 0) { red[wib * 2] = s2; red[wib * 2 + 1] = s3; }
+    __syncthreads();
+    __shared__ bool last;
+    if (tid == 0) {
+        float x = 0.f, y = 0.f;
+        for (int w = 0; w < WARPS; ++w) { x += red[w * 2]; y += red[w * 2 + 1]; }
+        a.partials[blockIdx.x * 2] = x;
+        a.partials[blockIdx.x * 2 + 1] = y;
+        __threadfence();
+        last = (atomicAdd(a.ticket, 1u) == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (last && wib == 0) {
+        __threadfence();
+        double d2 = 0.0, d3 = 0.0;
+        for (int i = lane; i < (int)gridDim.x; i += 32) {
+            d2 += (double)__ldcg(a.partials + i * 2);
+            d3 += (double)__ldcg(a.partials + i * 2 + 1);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            d2 += __shfl_xor_sync(FULL_MASK, d2, o);
+            d3 += __shfl_xor_sync(FULL_MASK, d3, o);
+        }
+        if (lane == 0) {
+            const double c2 = a.mask ? (double)*a.count2 : (double)total_poses * B * 2;
+            const float l2 = (float)(d2 / c2), l3 = (float)(d3 / a.count3);
+            a.losses[0] = l2; a.losses[1] = l3; a.losses[2] = a.w2 * l2 + a.w3 * l3;
+            a.losses[3] = (float)d2; a.losses[4] = (float)c2; a.losses[5] = (float)d3; a.losses[6] = (float)a.count3;
+            a.losses[7] = 0.f;
+            *a.ticket = 0u;   // self-resetting workspace header: ready for the next launch
+            *a.count2 = 0;
+        }
+    }
+}
+
+struct Plan {
+    int ok, warps, grid, gl;
+    size_t smem;
+};
+
+int g_sms = 0;
+int sm_count() {
+    if (!g_sms) {
+        int dev = 0, n = 0;
+        if (cudaGetDevice(&dev) == cudaSuccess &&
+            cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
+            g_sms = n;
+        else
+            g_sms = 148;
+    }
+    return g_sms;
+}
+
+size_t smem_bytes(int gl, int B, int warps) {
+    const int slot = B * 9;
+    return (size_t)(2 * ((gl * slot + 3) & ~3) + warps * ((B * 6 + 3) & ~3) + warps * 2 + 4) * sizeof(float);
+}
+
+// the bone axis must be a DFS pre-order (every subtree a contiguous index range): pose.py:41-47 produces one
+bool preorder_tables(const p2c_tree_t& t, FastArgs& a) {
+    const int B = t.n_bones;
+    if (B < 1 || B >= IDENT_LANE + 1) return false;  // lane 31 is reserved for the identity
+    int depth[P2C_MAX_BONES], size[P2C_MAX_BONES], stack[P2C_MAX_BONES], top = 0, maxd = 0;
+    if (t.parent[0] != -1) return false;
+    stack[top++] = 0;
+    depth[0] = 0;
+    for (int b = 1; b < B; ++b) {
+        const int p = t.parent[b];
+        if (p < 0 || p >= b) return false;
+        while (top > 0 && stack[top - 1] != p) --top;
+        if (top == 0) return false;
+        stack[top++] = b;
+        depth[b] = depth[p] + 1;
+        if (depth[b] > maxd) maxd = depth[b];
+    }
+    for (int b = 0; b < B; ++b) size[b] = 1;
+    for (int b = B - 1; b > 0; --b) size[t.parent[b]] += size[b];
+    int rounds = 0;
+    while ((1 << rounds) < maxd + 1) ++rounds;
+    if (rounds > MAX_ROUNDS) return false;
+    a.nrounds = rounds;
+    for (int b = 0; b < P2C_MAX_BONES; ++b) {
+        a.parent[b] = (int8_t)(b < B ? t.parent[b] : -1);
+        a.sub_end[b] = (int8_t)(b < B ? b + size[b] - 1 : b);
+        int packed = 0;
+        for (int k = 0; k < MAX_ROUNDS; ++k) {
+            int anc = b < B ? b : -1;
+            for (int s = 0; s < (1 << k) && anc >= 0; ++s) anc = t.parent[anc];
+            packed |= ((anc >= 0 && b < B) ? anc : IDENT_LANE) << (5 * k);
+        }
+        a.anc_packed[b] = packed;
+    }
+    return true;
+}
+
+Plan make_plan(const p2c_fused_step_t* p) {
+    Plan pl{};
+    const int B = p->tree.n_bones;
+    const long total = (long)p->n_clips * p->clip_len;
+    pl.gl = p->mode == P2C_MODE_POSE_CHANGES ? p->clip_len : (int)(total < 16 ? total : 16);
+    const size_t cap = 227 * 1024, s8 = smem_bytes(pl.gl, B, 8), s16 = smem_bytes(pl.gl, B, 16);
+    if (2 * (s8 + 1024) <= cap || pl.gl <= 8) {
+        pl.warps = 8;
+        pl.smem = s8;
+    } else {
+        pl.warps = 16;
+        pl.smem = s16;
+    }
+    if (pl.smem + 1024 > cap) return pl;
+    const long groups = p->mode == P2C_MODE_POSE_CHANGES ? p->n_clips : (total + pl.gl - 1) / pl.gl;
+    int per_sm = pl.warps == 8 ? (int)(cap / (pl.smem + 1024)) : 1;
+    if (per_sm > 2) per_sm = 2;   // __launch_bounds__(256, 2): 128 registers per thread
+    if (per_sm < 1) per_sm = 1;
+    const long slots = (long)sm_count() * per_sm;
+    pl.grid = (int)(groups < slots ? groups : slots);
+    pl.ok = 1;
+    return pl;
+}
+
+}  // namespace
+
+extern "C" int p2c_fused_fast_supported(const p2c_fused_step_t* p) {
+    const char* off = getenv("P2C_DISABLE_FAST");  // test hook: force the exact generic composite
+    if (off && off[0] == '1') return 0;
+    if (!p->input_6d) return 0;  // arbitrary 3x3 input is not assumed to be a rotation: exact generic path
+    if (p->mode != P2C_MODE_POSE_CHANGES && p->mode != P2C_MODE_RELATIVE_ROT) return 0;
+    if (p->mode == P2C_MODE_POSE_CHANGES && !p->ref_rot) return 0;
+    FastArgs a{};
+    if (!preorder_tables(p->tree, a)) return 0;
+    return make_plan(p).ok;
+}
+
+extern "C" int p2c_fused_fast_launches(const p2c_fused_step_t* p) { return p->mask_missing_joints ? 2 : 1; }
+
+extern "C" long p2c_fused_fast_workspace_floats(void) { return 16 + 2L * 148 * 4; }
+
+extern "C" int p2c_fused_fast(const p2c_fused_step_t* p, void* stream) {
+    FastArgs args{};
+    if (!preorder_tables(p->tree, args)) return P2C_E_UNSUPPORTED;
+    const Plan pl = make_plan(p);
+    if (!pl.ok) return P2C_E_UNSUPPORTED;
+    const int B = p->tree.n_bones;
+    args.N = p->n_clips; args.L = p->clip_len; args.GL = pl.gl; args.B = B; args.slot = B * 9;
+    args.scan = p->mode == P2C_MODE_POSE_CHANGES;
+    args.hips = p->hips; args.neck = p->neck; args.normalize = p->normalize; args.mask = p->mask_missing_joints;
+    args.gt_c = p->gt_2d_channels;
+    args.d6 = p->pose_in; args.ref_loc = p->ref_loc; args.ref_rot = p->ref_rot; args.ref_index = p->ref_index;
+    args.world_loc = p->world_loc; args.world_rot = p->world_rot; args.cam = p->camera;
+    args.gt2 = p->gt_2d; args.gt3 = p->gt_3d; args.w2 = p->weight_2d; args.w3 = p->weight_3d;
+    args.rel_rot = p->rel_rot; args.abs_rot = p->abs_rot; args.abs_loc = p->abs_loc; args.proj = p->proj;
+    args.proj_norm = p->proj_norm; args.g_d6 = p->g_pose_in;
+    args.ticket = reinterpret_cast<unsigned int*>(p->workspace);
+    args.count2 = reinterpret_cast<int*>(p->workspace) + 1;
+    args.partials = p->workspace + 16;
+    args.losses = p->losses;
+    const long total = (long)p->n_clips * p->clip_len;
+    args.count3 = (double)total * B * 3;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (args.mask) {
+        long blocks = (total * B + 255) / 256;
+        if (blocks > COUNT_BLOCKS) blocks = COUNT_BLOCKS;
+        count_kernel<<<(int)blocks, 256, 0, st>>>(p->gt_2d, total * B, B, p->gt_2d_channels, p->hips, args.count2);
+        P2C_LAUNCH_CHECK();
+    }
+    static bool attr8 = false, attr16 = false;
+    if (pl.warps == 8) {
+        if (!attr8) {
+            cudaError_t e = cudaFuncSetAttribute(fast_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
+            if (e != cudaSuccess) return (int)e;
+            attr8 = true;
+        }
+        fast_kernel<8><<<pl.grid, 256, pl.smem, st>>>(args);
+    } else {
+        if (!attr16) {
+            cudaError_t e = cudaFuncSetAttribute(fast_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
+            if (e != cudaSuccess) return (int)e;
+            attr16 = true;
+        }
+        fast_kernel<16><<<pl.grid, 512, pl.smem, st>>>(args);
+    }
+    P2C_LAUNCH_CHECK();
+    return 0;
+}

@@ -4,11 +4,12 @@
 //
 // Generic-tree path (this file): FK forward kernel -> loss kernel (normalise + masked MSE partials) ->
 // finalize (fixed-order double reduction) -> loss-gradient kernel -> FK backward kernel.
-// The CARLA-specialised single-pass kernel lives in fused_carla.cu and is dispatched from here.
+// The single-pass kernel for rotation_6d input lives in fused_fast.cu and is dispatched from here.
 #include "common.cuh"
 
-extern "C" int p2c_fused_carla_supported(const p2c_fused_step_t* p);
-extern "C" int p2c_fused_carla(const p2c_fused_step_t* p, void* stream);
+extern "C" int p2c_fused_fast_supported(const p2c_fused_step_t* p);
+extern "C" long p2c_fused_fast_workspace_floats(void);
+extern "C" int p2c_fused_fast(const p2c_fused_step_t* p, void* stream);
 
 namespace {
 
@@ -188,18 +189,19 @@ inline long align4(long x) { return (x + 3) & ~3L; }
 }  // namespace
 
 extern "C" int64_t p2c_fused_step_workspace_floats(int64_t n_poses, int32_t n_bones, int32_t input_6d) {
-    long w = LOSS_BLOCKS * 4;                               // loss partials
+    long w = 16 + p2c_fused_fast_workspace_floats();        // zero-invariant header + fast-path partials
+    w += LOSS_BLOCKS * 4;                                   // loss partials (generic path)
     w += 2 * align4((long)n_poses * n_bones * 3);           // g_proj, g_abs_loc (generic path)
     if (input_6d) w += 2 * align4((long)n_poses * n_bones * 9);  // matrices, g_matrices
     return w;
 }
 
-extern "C" int p2c_fused_carla_launches(const p2c_fused_step_t* p);
+extern "C" int p2c_fused_fast_launches(const p2c_fused_step_t* p);
 
 extern "C" int p2c_fused_step_launches(const p2c_fused_step_t* p) {
     if (!p) return P2C_E_NULL;
     if (p->n_clips == 0) return 0;
-    if (p2c_fused_carla_supported(p)) return p2c_fused_carla_launches(p);
+    if (p2c_fused_fast_supported(p)) return p2c_fused_fast_launches(p);
     return 5 + (p->input_6d ? 2 : 0);  // fk_fwd, loss_fwd, finalize, loss_bwd, fk_bwd (+ rot6d fwd/bwd)
 }
 
@@ -212,13 +214,13 @@ extern "C" int p2c_fused_step(const p2c_fused_step_t* p, void* stream) {
     if (p->n_clips == 0) return 0;
     if (!p->pose_in || !p->ref_loc || !p->gt_2d || !p->gt_3d || !p->g_pose_in || !p->workspace || !p->losses)
         return P2C_E_NULL;
-    if (p2c_fused_carla_supported(p)) return p2c_fused_carla(p, stream);
+    if (p2c_fused_fast_supported(p)) return p2c_fused_fast(p, stream);
 
     if (!p->rel_rot && p->mode == P2C_MODE_POSE_CHANGES) return P2C_E_NULL;
     if (!p->abs_rot || !p->abs_loc || !p->proj) return P2C_E_NULL;
     cudaStream_t st = (cudaStream_t)stream;
     const long M = (long)p->n_clips * p->clip_len;
-    float* ws = p->workspace;
+    float* ws = p->workspace + 16 + p2c_fused_fast_workspace_floats();  // the header stays zero (fast path's counters)
     float* partials = ws; ws += LOSS_BLOCKS * 4;
     float* g_proj = ws; ws += align4(M * B * 3);
     float* g_abs_loc = ws; ws += align4(M * B * 3);

@@ -282,6 +282,21 @@ def masked_mse(pred, gt, c_used, mask_hips=-1):
     return _MaskedMSE.apply(pred, gt, c_used, mask_hips)
 
 
+_WS = {}
+
+
+def _workspace(dev, nfloats):
+    """Per-device scratch for p2c_fused_step.  Its first 16 floats are counters that must be zero before the first
+    call and that every call leaves zero again (include/p2c_b200.h), so the buffer is zero-filled once and reused.
+    Calls on one device are stream-ordered by PyTorch's current stream."""
+    key = (dev.type, dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    ws = _WS.get(key)
+    if ws is None or ws.numel() < nfloats:
+        ws = torch.zeros(max(nfloats, 1), device=dev)
+        _WS[key] = ws
+    return ws
+
+
 class FusedStepResult(object):
     """Outputs of one fused pose_lifting step (see fused_step)."""
     __slots__ = ('loc_2d', 'loc_3d', 'loc_2d_3d', 'losses', 'relative_pose_rot', 'absolute_pose_rot',
@@ -325,7 +340,7 @@ class _FusedStep(torch.autograd.Function):
         nws = lib.p2c_fused_step_workspace_floats(N * L, B, a.input_6d)
         ws = out.get('workspace')
         if ws is None or ws.numel() < nws:
-            ws = torch.empty(max(int(nws), 1), device=dev)
+            ws = _workspace(dev, int(nws))
         losses = out.get('losses') if out.get('losses') is not None else torch.empty(8, device=dev)
         a.rel_rot, a.abs_rot, a.abs_loc, a.proj, a.proj_norm = (ptr(rel_rot), ptr(abs_rot), ptr(abs_loc), ptr(proj),
                                                                 ptr(proj_norm))

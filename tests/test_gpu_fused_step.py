@@ -6,7 +6,8 @@ import pytest
 import torch
 
 import oracle as O
-from _util import assert_close, make_case, make_targets, oracle_step, smpl_parents
+from _util import (assert_close, assert_close_fp32_aware, cast_case, make_case, make_targets, oracle_step,
+                   smpl_parents)
 
 pytestmark = pytest.mark.gpu
 
@@ -46,7 +47,17 @@ def run_cuda(ops, lib, c, pose, gt2, gt3, mode, normalize, mask, w2=1.0, w3=1.0)
     return res, x.grad
 
 
-def compare(res, grad, want, ref_grad, normalize=True):
+def oracle_grad32(c, gt2, gt3, mode='pose_changes', normalize=True, mask=True, pose=None, w2=1.0, w3=1.0):
+    """The same step evaluated by the oracle in float32 (= the reference PyTorch path's own precision)."""
+    c32 = cast_case(c, torch.float32)
+    x = (c32['d6'] if pose is None else pose.float()).clone().requires_grad_(True)
+    mats = O.rotation_6d_to_matrix(x) if x.shape[-1] == 6 and x.dim() == 4 else x
+    out = oracle_step(c32, mats, mode, normalize, mask, gt=(gt2.float(), gt3.float()))
+    (w2 * out['loc_2d'] + w3 * out['loc_3d']).backward()
+    return x.grad
+
+
+def compare(res, grad, want, ref_grad, normalize=True, ref_grad32=None):
     assert_close('relative_pose_rot', res.relative_pose_rot, want['relative_pose_rot'])
     assert_close('absolute_pose_rot', res.absolute_pose_rot, want['absolute_pose_rot'])
     assert_close('absolute_pose_loc', res.absolute_pose_loc, want['absolute_pose_loc'])
@@ -56,7 +67,10 @@ def compare(res, grad, want, ref_grad, normalize=True):
     assert_close('loc_2d', res.loc_2d, want['loc_2d'])
     assert_close('loc_3d', res.loc_3d, want['loc_3d'])
     assert_close('loc_2d_3d', res.loc_2d_3d, want['loc_2d_3d'])
-    assert_close('grad', grad, ref_grad)
+    if ref_grad32 is None:
+        assert_close('grad', grad, ref_grad)
+    else:
+        assert_close_fp32_aware('grad', grad, ref_grad, ref_grad32)
 
 
 @pytest.mark.parametrize('mode', ['pose_changes', 'relative_rot'])
@@ -72,10 +86,11 @@ def test_fused_step_carla(ops, lib, mode, six_d, normalize, mask):
     want['loc_2d_3d'].backward()
     if six_d:
         res, grad = run_cuda(ops, lib, c, c['d6'], gt2, gt3, mode, normalize, mask)
-        compare(res, grad, want, d6.grad, normalize)
+        compare(res, grad, want, d6.grad, normalize, oracle_grad32(c, gt2, gt3, mode, normalize, mask))
     else:
         res, grad = run_cuda(ops, lib, c, mats.detach(), gt2, gt3, mode, normalize, mask)
-        compare(res, grad, want, mats.grad, normalize)
+        compare(res, grad, want, mats.grad, normalize,
+                oracle_grad32(c, gt2, gt3, mode, normalize, mask, pose=mats.detach()))
 
 
 @pytest.mark.parametrize('n,l', [(1, 1), (3, 1), (2, 64), (33, 5), (64, 16)])
@@ -87,7 +102,7 @@ def test_fused_step_shapes(ops, lib, n, l):
     want = oracle_step(c, O.rotation_6d_to_matrix(d6), gt=(gt2, gt3))
     want['loc_2d_3d'].backward()
     res, grad = run_cuda(ops, lib, c, c['d6'], gt2, gt3, 'pose_changes', True, True)
-    compare(res, grad, want, d6.grad)
+    compare(res, grad, want, d6.grad, ref_grad32=oracle_grad32(c, gt2, gt3))
 
 
 def test_fused_step_weights(ops, lib):
@@ -98,7 +113,7 @@ def test_fused_step_weights(ops, lib):
     (0.25 * want['loc_2d'] + 3.0 * want['loc_3d']).backward()
     res, grad = run_cuda(ops, lib, c, c['d6'], gt2, gt3, 'pose_changes', True, True, w2=0.25, w3=3.0)
     assert_close('weighted loss', res.loc_2d_3d, 0.25 * want['loc_2d'] + 3.0 * want['loc_3d'])
-    assert_close('weighted grad', grad, d6.grad)
+    assert_close_fp32_aware('weighted grad', grad, d6.grad, oracle_grad32(c, gt2, gt3, w2=0.25, w3=3.0))
 
 
 def test_fused_step_smpl_tree(ops, lib):
@@ -109,7 +124,7 @@ def test_fused_step_smpl_tree(ops, lib):
     want = oracle_step(c, O.rotation_6d_to_matrix(d6), gt=(gt2, gt3))
     want['loc_2d_3d'].backward()
     res, grad = run_cuda(ops, lib, c, c['d6'], gt2, gt3, 'pose_changes', True, True)
-    compare(res, grad, want, d6.grad)
+    compare(res, grad, want, d6.grad, ref_grad32=oracle_grad32(c, gt2, gt3))
 
 
 def test_fused_step_non_orthonormal_matrices(ops, lib):
@@ -121,7 +136,7 @@ def test_fused_step_non_orthonormal_matrices(ops, lib):
     want = oracle_step(c, mats, gt=(gt2, gt3))
     want['loc_2d_3d'].backward()
     res, grad = run_cuda(ops, lib, c, mats.detach(), gt2, gt3, 'pose_changes', True, True)
-    compare(res, grad, want, mats.grad)
+    compare(res, grad, want, mats.grad, ref_grad32=oracle_grad32(c, gt2, gt3, pose=mats.detach()))
 
 
 @pytest.mark.parametrize('mode', ['pose_changes', 'relative_rot'])
