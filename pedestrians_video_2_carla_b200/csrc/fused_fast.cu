@@ -93,26 +93,20 @@ __device__ __forceinline__ GS gram_schmidt(const float* a) {
     return r;
 }
 
-// backward of gram_schmidt: g = dL/d(rows b1, b2, b3) -> dL/d(a1, a2)
-__device__ __forceinline__ void gram_schmidt_bwd(const GS& r, const M3& g, float* out) {
-    const V3 g1{g.m[0], g.m[1], g.m[2]}, g2{g.m[3], g.m[4], g.m[5]}, g3{g.m[6], g.m[7], g.m[8]};
-    V3 c = cross3(r.b2, g3);
-    V3 gb1{g1.x + c.x, g1.y + c.y, g1.z + c.z};
-    c = cross3(g3, r.b1);
-    const V3 gb2{g2.x + c.x, g2.y + c.y, g2.z + c.z};
-    const float d2 = r.deg2 ? 0.f : dot3(r.b2, gb2);
-    const V3 gu{(gb2.x - r.b2.x * d2) * r.inv2, (gb2.y - r.b2.y * d2) * r.inv2, (gb2.z - r.b2.z * d2) * r.inv2};
-    const float du = dot3(r.b1, gu);
-    out[3] = fmaf(-du, r.b1.x, gu.x);
-    out[4] = fmaf(-du, r.b1.y, gu.y);
-    out[5] = fmaf(-du, r.b1.z, gu.z);
-    gb1.x -= fmaf(r.s, gu.x, du * r.a2.x);
-    gb1.y -= fmaf(r.s, gu.y, du * r.a2.y);
-    gb1.z -= fmaf(r.s, gu.z, du * r.a2.z);
-    const float d1 = r.deg1 ? 0.f : dot3(r.b1, gb1);
-    out[0] = (gb1.x - r.b1.x * d1) * r.inv1;
-    out[1] = (gb1.y - r.b1.y * d1) * r.inv1;
-    out[2] = (gb1.z - r.b1.z * d1) * r.inv1;
+
+// Backward of gram_schmidt in tangent form.  C(d6) is a rotation for every d6, so only the component of dL/dC
+// along the tangent space {[k]x C} matters: omega = vee(dL/dC . C^T), dL = omega . k, and the Gram-Schmidt
+// differential gives  k1 = -(da2.b3 - s da1.b3 / n1) / n2,  k2 = da1.b3 / n1,  k3 = -da1.b2 / n1.
+// (Degenerate inputs |a1| or |u| < 1e-12, where F.normalize stops normalising and C is no rotation, get the same
+// formula; the exact generic path covers arbitrary matrices.)
+__device__ __forceinline__ void gram_schmidt_bwd_tangent(const GS& r, const V3& w, float* out) {
+    const float c3 = fmaf(w.x * r.s, r.inv2, w.y) * r.inv1, c2 = -w.z * r.inv1, e3 = -w.x * r.inv2;
+    out[0] = fmaf(c3, r.b3.x, c2 * r.b2.x);
+    out[1] = fmaf(c3, r.b3.y, c2 * r.b2.y);
+    out[2] = fmaf(c3, r.b3.z, c2 * r.b2.z);
+    out[3] = e3 * r.b3.x;
+    out[4] = e3 * r.b3.y;
+    out[5] = e3 * r.b3.z;
 }
 
 __device__ __forceinline__ void load6(const float* __restrict__ p, float* a) {
@@ -121,35 +115,41 @@ __device__ __forceinline__ void load6(const float* __restrict__ p, float* a) {
     a[0] = x.x; a[1] = x.y; a[2] = y.x; a[3] = y.y; a[4] = z.x; a[5] = z.y;
 }
 
-// coalesced smem -> global copies; the widest vector both sides are aligned for
-__device__ __forceinline__ void copy_out(float* __restrict__ g, const float* __restrict__ s, int n, int tid, int nthr) {
+// CTA-wide coalesced smem -> global copy of a flat staging region; the widest vector both sides are aligned for
+template <int NT>
+__device__ __forceinline__ void block_copy_out(float* __restrict__ g, const float* __restrict__ s, int n, int tid) {
     const uintptr_t both = reinterpret_cast<uintptr_t>(g) | (uintptr_t)__cvta_generic_to_shared(s);
     if (((both & 15) == 0) && ((n & 3) == 0)) {
         float4* g4 = reinterpret_cast<float4*>(g);
         const float4* s4 = reinterpret_cast<const float4*>(s);
-        for (int i = tid; i < (n >> 2); i += nthr) g4[i] = s4[i];
+        const int n4 = n >> 2;
+#pragma unroll 4
+        for (int i = tid; i < n4; i += NT) __stcs(g4 + i, s4[i]);
     } else if (((both & 7) == 0) && ((n & 1) == 0)) {
         float2* g2 = reinterpret_cast<float2*>(g);
         const float2* s2 = reinterpret_cast<const float2*>(s);
-        for (int i = tid; i < (n >> 1); i += nthr) g2[i] = s2[i];
+        const int n2 = n >> 1;
+#pragma unroll 4
+        for (int i = tid; i < n2; i += NT) __stcs(g2 + i, s2[i]);
     } else {
-        for (int i = tid; i < n; i += nthr) g[i] = s[i];
+        for (int i = tid; i < n; i += NT) g[i] = s[i];
     }
 }
 
 // utils/tensors.py:29-40 count of kept (joint, channel) pairs of the 2-D targets (integer => order independent)
-__global__ void __launch_bounds__(256) count_kernel(const float* __restrict__ gt2, long total, int B, int gt_c, int hips,
+__global__ void __launch_bounds__(256) count_kernel(const float* __restrict__ gt2, long poses, int B, int gt_c, int hips,
                                                    int* __restrict__ count) {
     int c = 0;
-    for (long i = (long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long)gridDim.x * 256) {
-        const float* g = gt2 + i * gt_c;
-        const int j = (int)(i % B);
-        if (j == hips || (__ldg(g) != 0.f && __ldg(g + 1) != 0.f)) c += 2;
+    const int lane = threadIdx.x & 31;
+    for (long p = (long)blockIdx.x * 8 + (threadIdx.x >> 5); p < poses; p += (long)gridDim.x * 8) {
+        const float* g = gt2 + p * B * gt_c;
+        for (int j = lane; j < B; j += 32)
+            if (j == hips || (__ldg(g + j * gt_c) != 0.f && __ldg(g + j * gt_c + 1) != 0.f)) c += 2;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(FULL_MASK, c, o);
     __shared__ int sh[8];
-    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = c;
+    if (lane == 0) sh[threadIdx.x >> 5] = c;
     __syncthreads();
     if (threadIdx.x == 0) {
         int t = 0;
@@ -158,19 +158,47 @@ __global__ void __launch_bounds__(256) count_kernel(const float* __restrict__ gt
     }
 }
 
-__device__ __forceinline__ int round4(int x) { return (x + 3) & ~3; }
+__device__ __host__ __forceinline__ int round4(int x) { return (x + 3) & ~3; }
 
-template <int WARPS>
+// shared-memory plan of one CTA (floats); every region starts 16-byte aligned
+struct Smem {
+    int rs, as, ts, ps, ns, ys, ident, red, total;
+};
+__device__ __host__ __forceinline__ Smem smem_plan(int gl, int B, int warps, int want_norm) {
+    Smem s;
+    int o = 0;
+    s.rs = o; o += round4(gl * B * 9);   // C[t] -> R[t]: the rel_rot records of the group
+    s.as = o; o += round4(gl * B * 9);   // abs_rot records
+    s.ts = o; o += round4(gl * B * 3);   // abs_loc records   } after their copy-out the two regions together hold
+    s.ps = o; o += round4(gl * B * 3);   // projection records } the grad-wrt-6-D records (gl * B * 6)
+    s.ns = o; o += want_norm ? round4(gl * B * 3) : 0;
+    s.ys = o; o += round4(gl * B * 3);   // y[t] (torque in the parent frame), then its suffix sum over frames
+    s.ident = o; o += 12;
+    s.red = o; o += round4(warps * 2);
+    s.total = o;
+    return s;
+}
+
+template <int WARPS, int BT>
 __global__ void __launch_bounds__(WARPS * 32, (WARPS == 8 ? 2 : 1)) fast_kernel(const FastArgs a) {
     extern __shared__ __align__(16) float smem[];
     constexpr int NT = WARPS * 32;
     const int tid = threadIdx.x, lane = tid & 31, wib = tid >> 5;
-    const int B = a.B, slot = a.slot;
+    const int B = BT ? BT : a.B;
+    const int B3 = B * 3, B6 = B * 6, slot = B * 9;
     const bool act = lane < B;
-    float* Rs = smem;                               // [GL][slot]  C[t], then R[t] (= the rel_rot records of the group)
-    float* Ys = Rs + round4(a.GL * slot);           // [GL][slot]  abs_rot staging, then Y[t], then its suffix sum
-    float* WB = Ys + round4(a.GL * slot) + wib * round4(B * 6);  // per-warp staging of the 3- and 6-float records
-    float* red = Ys + round4(a.GL * slot) + WARPS * round4(B * 6);
+    const int lb = act ? lane : B - 1;   // clamped bone index: inactive lanes load valid memory and are ignored
+    const Smem sm = smem_plan(a.GL, B, WARPS, a.proj_norm != nullptr);
+    float* Rs = smem + sm.rs;
+    float* As = smem + sm.as;
+    float* Ts = smem + sm.ts;
+    float* Ps = smem + sm.ps;
+    float* Ns = smem + sm.ns;
+    float* Ys = smem + sm.ys;
+    float* Gd = smem + sm.ts;            // grad wrt 6-D records; reuses Ts+Ps once those have been copied out
+    float* ident = smem + sm.ident;
+    float* red = smem + sm.red;
+    if (tid < 12) ident[tid] = (tid == 0 || tid == 4 || tid == 8) ? 1.f : 0.f;
 
     const int par = act ? a.parent[lane] : -1;
     const int psrc = par < 0 ? IDENT_LANE : par;
@@ -181,18 +209,19 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 8 ? 2 : 1)) fast_kernel(
     const float k2 = a.w2 * 2.0f / (a.mask ? (float)__ldcg(a.count2) : (float)(total_poses * B * 2));
     const float k3 = a.w3 * 2.0f / (float)a.count3;
     const M3 camR = m3_from(a.cam.R);
+    const float camf = a.cam.f;
     float s2 = 0.f, s3 = 0.f;
 
     for (long grp = blockIdx.x; grp < groups; grp += gridDim.x) {
         const long m0 = grp * a.GL;
         const int nf = (int)min((long)a.GL, total_poses - m0);
 
-        // ---- phase A: 6-D -> C[t]
+        // ---- phase A: 6-D -> C[t] (rotation_6d_to_matrix)
         for (int f = wib; f < nf; f += WARPS) {
+            float d[6];
+            load6(a.d6 + ((m0 + f) * B + lb) * 6, d);
+            const GS r = gram_schmidt(d);
             if (act) {
-                float d[6];
-                load6(a.d6 + ((m0 + f) * B + lane) * 6, d);
-                const GS r = gram_schmidt(d);
                 float* o = Rs + f * slot + lane * 9;
                 o[0] = r.b1.x; o[1] = r.b1.y; o[2] = r.b1.z;
                 o[3] = r.b2.x; o[4] = r.b2.y; o[5] = r.b2.z;
@@ -208,35 +237,35 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 8 ? 2 : 1)) fast_kernel(
                 const float* rr = a.ref_rot + (row * B + tid) * 9;
 #pragma unroll
                 for (int i = 0; i < 9; ++i) prev.m[i] = __ldg(rr + i);
+                float* o = Rs + tid * 9;
+                M3 cur = m3_from(o);
                 for (int f = 0; f < nf; ++f) {
-                    float* o = Rs + f * slot + tid * 9;
-                    prev = m3_mul(m3_from(o), prev);
+                    M3 nxt;
+                    if (f + 1 < nf) nxt = m3_from(o + slot);  // next C[t] in flight while this product runs
+                    prev = m3_mul(cur, prev);
                     m3_to(o, prev);
+                    cur = nxt;
+                    o += slot;
                 }
             }
             __syncthreads();
         }
-        if (a.rel_rot) copy_out(a.rel_rot + m0 * slot, Rs, nf * slot, tid, NT);
+        if (a.rel_rot) block_copy_out<NT>(a.rel_rot + m0 * slot, Rs, nf * slot, tid);
 
-        // ---- phase C: per frame FK + projection + loss + tree backward
+        // ---- phase C: per frame FK + projection + loss + torque backward
         for (int f = wib; f < nf; f += WARPS) {
             const long m = m0 + f;
             const long clip = a.scan ? grp : m / a.L;
             const long row = a.ref_index ? (long)__ldg(a.ref_index + clip) : clip;
-            V3 l{0.f, 0.f, 0.f}, g3{0.f, 0.f, 0.f};
-            float g2x = 0.f, g2y = 0.f;
-            M3 A = m3_identity();
-            if (act) {
-                const float* rl = a.ref_loc + (row * B + lane) * 3;
-                l = V3{__ldg(rl), __ldg(rl + 1), __ldg(rl + 2)};
-                const float* q3 = a.gt3 + (m * B + lane) * 3;
-                g3 = V3{__ldg(q3), __ldg(q3 + 1), __ldg(q3 + 2)};
-                const float* q2 = a.gt2 + (m * B + lane) * a.gt_c;
-                g2x = __ldg(q2); g2y = __ldg(q2 + 1);
-                A = m3_from(Rs + f * slot + lane * 9);
-            }
+            const float* q3 = a.gt3 + (m * B + lb) * 3;
+            const V3 g3{__ldg(q3), __ldg(q3 + 1), __ldg(q3 + 2)};
+            const float* q2 = a.gt2 + (m * B + lb) * a.gt_c;
+            const float g2x = __ldg(q2), g2y = __ldg(q2 + 1);
+            const float* rl = a.ref_loc + (row * B + lb) * 3;
+            V3 t{__ldg(rl), __ldg(rl + 1), __ldg(rl + 2)};
+            if (!act) t = V3{0.f, 0.f, 0.f};
+            M3 A = m3_from(act ? Rs + f * slot + lane * 9 : ident);
             // FK by pointer jumping: (A, t) <- (A, t) o (A, t)[2^k-th ancestor]; abs = rel o parent o ... o root
-            V3 t = l;
             for (int k = 0; k < a.nrounds; ++k) {
                 const int src = (ancp >> (5 * k)) & 31;
                 const M3 Am = m3_shfl(A, src);
@@ -244,12 +273,6 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 8 ? 2 : 1)) fast_kernel(
                 const V3 q = v3_mul_m(t, Am);
                 t = V3{q.x + tm.x, q.y + tm.y, q.z + tm.z};
                 A = m3_mul(A, Am);
-            }
-            float* ys = Ys + f * slot;
-            if (a.abs_rot) {
-                if (act) m3_to(ys + lane * 9, A);
-                __syncwarp();
-                copy_out(a.abs_rot + m * slot, ys, slot, lane, 32);
             }
             // projection (p3d_pose_projection.py:137-152)
             V3 c;
@@ -260,37 +283,37 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 8 ? 2 : 1)) fast_kernel(
                 c = v3_mul_m(wp, camR);
                 c.x += a.cam.T[0]; c.y += a.cam.T[1]; c.z += a.cam.T[2];
             }
-            const float iz = 1.0f / c.z;
-            const V3 p{a.cam.px - a.cam.f * c.x * iz, a.cam.py - a.cam.f * c.y * iz, iz};
+            const float iz = __fdividef(1.0f, c.z);
+            const V3 p{fmaf(-camf * c.x, iz, a.cam.px), fmaf(-camf * c.y, iz, a.cam.py), iz};
             if (act) {
-                WB[lane * 3] = t.x; WB[lane * 3 + 1] = t.y; WB[lane * 3 + 2] = t.z;
-                WB[B * 3 + lane * 3] = p.x; WB[B * 3 + lane * 3 + 1] = p.y; WB[B * 3 + lane * 3 + 2] = p.z;
+                m3_to(As + f * slot + lane * 9, A);
+                float* o = Ts + f * B3 + lane * 3;
+                o[0] = t.x; o[1] = t.y; o[2] = t.z;
+                o = Ps + f * B3 + lane * 3;
+                o[0] = p.x; o[1] = p.y; o[2] = p.z;
             }
-            __syncwarp();
-            if (a.abs_loc) copy_out(a.abs_loc + m * B * 3, WB, B * 3, lane, 32);
-            if (a.proj) copy_out(a.proj + m * B * 3, WB + B * 3, B * 3, lane, 32);
-            __syncwarp();
-
             // Normalizer(HipsNeckExtractor) + loc_2d + loc_3d and their gradient wrt (proj, abs_loc)
-            const float sx = __shfl_sync(FULL_MASK, p.x, a.hips), sy = __shfl_sync(FULL_MASK, p.y, a.hips);
-            const float dx = __shfl_sync(FULL_MASK, p.x, a.neck) - sx, dy = __shfl_sync(FULL_MASK, p.y, a.neck) - sy;
-            const float scale = sqrtf(dx * dx + dy * dy);
-            const bool okn = scale > 0.f && scale <= 3.402823466e38f;
-            float x = p.x, y = p.y, q = p.z;
+            float x = p.x, y = p.y;
             bool lx = true, ly = true;
+            float inv = 1.f, dx = 0.f, dy = 0.f;
+            bool okn = true;
             if (a.normalize) {
-                const float rx = (p.x - sx) / scale, ry = (p.y - sy) / scale;
+                const float sx = __shfl_sync(FULL_MASK, p.x, a.hips), sy = __shfl_sync(FULL_MASK, p.y, a.hips);
+                dx = __shfl_sync(FULL_MASK, p.x, a.neck) - sx;
+                dy = __shfl_sync(FULL_MASK, p.y, a.neck) - sy;
+                const float scale = sqrtf(fmaf(dx, dx, dy * dy));
+                okn = scale > 0.f && scale <= 3.402823466e38f;
+                inv = __fdividef(1.0f, scale);
+                const float rx = (p.x - sx) * inv, ry = (p.y - sy) * inv;
                 lx = fabsf(rx) <= 3.402823466e38f;
                 ly = fabsf(ry) <= 3.402823466e38f;
                 x = lx ? rx : 0.f;
                 y = ly ? ry : 0.f;
-                q = nan_to_zero(q);
+                const float q = nan_to_zero(p.z);
                 if (!(q >= 1e-5f)) { x = 0.f; y = 0.f; lx = ly = false; }
-                if (a.proj_norm) {
-                    if (act) { WB[lane * 3] = x; WB[lane * 3 + 1] = y; WB[lane * 3 + 2] = q; }
-                    __syncwarp();
-                    copy_out(a.proj_norm + m * B * 3, WB, B * 3, lane, 32);
-                    __syncwarp();
+                if (a.proj_norm && act) {
+                    float* o = Ns + f * B3 + lane * 3;
+                    o[0] = x; o[1] = y; o[2] = q;
                 }
             }
             const bool kept = act && (!a.mask || lane == a.hips || (g2x != 0.f && g2y != 0.f));
@@ -302,100 +325,86 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 8 ? 2 : 1)) fast_kernel(
                 gy = ly ? k2 * ey : 0.f;
             }
             if (a.normalize) {
-                if (!okn) { gx = 0.f; gy = 0.f; }
-                const float sgx = warp_sum(gx), sgy = warp_sum(gy), sgn = warp_sum(gx * x + gy * y);
-                gx = okn ? gx / scale : 0.f;
-                gy = okn ? gy / scale : 0.f;
-                if (okn) {
-                    const float gscale = -sgn / scale, ux = dx / scale, uy = dy / scale;
-                    float hx = -sgx / scale - gscale * ux, hy = -sgy / scale - gscale * uy;
-                    float kx = gscale * ux, ky = gscale * uy;
-                    if (a.hips == a.neck) { hx += kx; hy += ky; kx = 0.f; ky = 0.f; }
-                    if (lane == a.hips) { gx += hx; gy += hy; }
-                    if (lane == a.neck) { gx += kx; gy += ky; }
-                }
+                if (!okn) { gx = 0.f; gy = 0.f; inv = 0.f; }
+                const float sgx = warp_sum(gx), sgy = warp_sum(gy), sgn = warp_sum(fmaf(gx, x, gy * y));
+                gx *= inv;
+                gy *= inv;
+                // d/d(hips, neck) through shift and scale: scale = |neck - hips|, u = (neck - hips) / scale
+                const float gs = -sgn * inv * inv;   // dL/dscale . (1/scale)
+                const float kx = gs * dx, ky = gs * dy;
+                if (lane == a.neck) { gx += kx; gy += ky; }
+                if (lane == a.hips) { gx -= fmaf(sgx, inv, kx); gy -= fmaf(sgy, inv, ky); }
             }
-            V3 g{0.f, 0.f, 0.f};  // dL / d abs_loc[lane]
-            if (act) {
+            V3 g;  // dL / d abs_loc[lane]
+            {
                 const V3 e{t.x - g3.x, t.y - g3.y, t.z - g3.z};
-                s3 = fmaf(e.x, e.x, fmaf(e.y, e.y, fmaf(e.z, e.z, s3)));
+                if (act) s3 = fmaf(e.x, e.x, fmaf(e.y, e.y, fmaf(e.z, e.z, s3)));
                 // backward of the projection: (gx, gy, 0) -> camera point -> world point -> p3d point
-                V3 gc{-a.cam.f * gx * iz, -a.cam.f * gy * iz, a.cam.f * (gx * c.x + gy * c.y) * iz * iz};
+                const float fgx = camf * gx * iz, fgy = camf * gy * iz;
+                const V3 gc{-fgx, -fgy, fmaf(fgx, c.x, fgy * c.y) * iz};
                 V3 gw = v3_mul_mt(gc, camR);
                 if (a.world_rot) gw = v3_mul_mt(gw, m3_from(a.world_rot + m * 9));
                 g = V3{fmaf(k3, e.x, -gw.y), fmaf(k3, e.y, gw.x), fmaf(k3, e.z, gw.z)};
+                if (!act) g = V3{0.f, 0.f, 0.f};
             }
-            // tree backward: subtree sums of (t^T (x) g, g) as an inclusive prefix scan over the DFS-ordered lanes
-            float w[12] = {t.x * g.x, t.x * g.y, t.x * g.z, t.y * g.x, t.y * g.y, t.y * g.z,
-                           t.z * g.x, t.z * g.y, t.z * g.z, g.x, g.y, g.z};
-            float own[12];
+            // torque backward: m_b = sum_{d in subtree(b)} g_d x (t_d - t_b); subtree sums of (g x t, g) are
+            // differences of an inclusive prefix scan over the DFS-ordered lanes
+            float w[6] = {g.y * t.z - g.z * t.y, g.z * t.x - g.x * t.z, g.x * t.y - g.y * t.x, g.x, g.y, g.z};
+            float ex_[6];
 #pragma unroll
-            for (int i = 0; i < 12; ++i) own[i] = w[i];
+            for (int i = 0; i < 6; ++i) ex_[i] = w[i];
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
 #pragma unroll
-                for (int i = 0; i < 12; ++i) {
+                for (int i = 0; i < 6; ++i) {
                     const float v = __shfl_up_sync(FULL_MASK, w[i], o);
                     if (lane >= o) w[i] += v;
                 }
             }
-            M3 Msub;
-            V3 Gs;
-            {
-                float s[12];
+            float s[6];
 #pragma unroll
-                for (int i = 0; i < 12; ++i) s[i] = __shfl_sync(FULL_MASK, w[i], sub_end) - (w[i] - own[i]);
-                Gs = V3{s[9], s[10], s[11]};
-                Msub.m[0] = fmaf(-t.x, Gs.x, s[0]); Msub.m[1] = fmaf(-t.x, Gs.y, s[1]); Msub.m[2] = fmaf(-t.x, Gs.z, s[2]);
-                Msub.m[3] = fmaf(-t.y, Gs.x, s[3]); Msub.m[4] = fmaf(-t.y, Gs.y, s[4]); Msub.m[5] = fmaf(-t.y, Gs.z, s[5]);
-                Msub.m[6] = fmaf(-t.z, Gs.x, s[6]); Msub.m[7] = fmaf(-t.z, Gs.y, s[7]); Msub.m[8] = fmaf(-t.z, Gs.z, s[8]);
+            for (int i = 0; i < 6; ++i) s[i] = __shfl_sync(FULL_MASK, w[i], sub_end) - (w[i] - ex_[i]);
+            const V3 mv{s[0] - (s[4] * t.z - s[5] * t.y), s[1] - (s[5] * t.x - s[3] * t.z), s[2] - (s[3] * t.y - s[4] * t.x)};
+            const M3 Ap = m3_shfl(A, psrc);       // IDENT_LANE keeps the identity for the root
+            const V3 yv = v3_mul_mt(mv, Ap);      // torque rotated into the parent frame
+            if (act) {
+                float* o = Ys + f * B3 + lane * 3;
+                o[0] = yv.x; o[1] = yv.y; o[2] = yv.z;
             }
-            const M3 Ap = m3_shfl(A, psrc);                 // IDENT_LANE keeps the identity for the root
-            const M3 Y = m3_mul_bt(m3_mul(Ap, Msub), Ap);   // R^T dL/dR = A_p M A_p^T
-            __syncwarp();                                   // abs_rot staging in ys has been copied out
-            if (act) m3_to(ys + lane * 9, Y);
         }
         __syncthreads();
-        // ---- phase D: Z[t] = sum_{s >= t} Y[s]
+        if (a.abs_rot) block_copy_out<NT>(a.abs_rot + m0 * slot, As, nf * slot, tid);
+        if (a.abs_loc) block_copy_out<NT>(a.abs_loc + m0 * B3, Ts, nf * B3, tid);
+        if (a.proj) block_copy_out<NT>(a.proj + m0 * B3, Ps, nf * B3, tid);
+        if (a.proj_norm) block_copy_out<NT>(a.proj_norm + m0 * B3, Ns, nf * B3, tid);
+        // ---- phase D: z[t] = sum_{s >= t} y[s]  (the reverse-time scan in tangent form is a plain suffix sum)
         if (a.scan) {
-            for (int col = tid; col < slot; col += NT) {
+            for (int col = tid; col < B3; col += NT) {
                 float acc = 0.f;
                 for (int f = nf - 1; f >= 0; --f) {
-                    acc += Ys[f * slot + col];
-                    Ys[f * slot + col] = acc;
+                    acc += Ys[f * B3 + col];
+                    Ys[f * B3 + col] = acc;
                 }
             }
-            __syncthreads();
-        }
-        // ---- phase E: dL/dC[t] = R[t] Z[t] R[t-1]^T, then the Gram-Schmidt backward
-        for (int f = wib; f < nf; f += WARPS) {
-            const long m = m0 + f;
-            if (act) {
-                const M3 Z = m3_from(Ys + f * slot + lane * 9);
-                M3 G = m3_mul(m3_from(Rs + f * slot + lane * 9), Z);
-                if (a.scan) {
-                    M3 prev;
-                    if (f > 0) {
-                        prev = m3_from(Rs + (f - 1) * slot + lane * 9);
-                    } else {
-                        const long row = a.ref_index ? (long)__ldg(a.ref_index + grp) : grp;
-                        const float* rr = a.ref_rot + (row * B + lane) * 9;
-#pragma unroll
-                        for (int i = 0; i < 9; ++i) prev.m[i] = __ldg(rr + i);
-                    }
-                    G = m3_mul_bt(G, prev);
-                }
-                float d[6], o[6];
-                load6(a.d6 + (m * B + lane) * 6, d);
-                gram_schmidt_bwd(gram_schmidt(d), G, o);
-#pragma unroll
-                for (int i = 0; i < 6; ++i) WB[lane * 6 + i] = o[i];
-            }
-            __syncwarp();
-            copy_out(a.g_d6 + m * B * 6, WB, B * 6, lane, 32);
-            __syncwarp();
         }
         __syncthreads();
+        // ---- phase E: omega[t] = R[t] z[t]; tangent-form Gram-Schmidt backward -> grad wrt the 6-D input
+        for (int f = wib; f < nf; f += WARPS) {
+            float d[6], o6[6];
+            load6(a.d6 + ((m0 + f) * B + lb) * 6, d);
+            const float* zp = Ys + f * B3 + lb * 3;
+            const V3 z{zp[0], zp[1], zp[2]};
+            const V3 om = v3_mul_mt(z, m3_from(Rs + f * slot + lb * 9));
+            gram_schmidt_bwd_tangent(gram_schmidt(d), om, o6);
+            if (act) {
+                float* o = Gd + f * B6 + lane * 6;
+#pragma unroll
+                for (int i = 0; i < 6; ++i) o[i] = o6[i];
+            }
+        }
+        __syncthreads();
+        block_copy_out<NT>(a.g_d6 + m0 * B6, Gd, nf * B6, tid);
+        // (the next group's phase A writes Rs only; Gd/Ts/Ps are next written in phase C, two barriers later)
     }
 
     // ---- loss sums: fixed-order reduction, the last CTA to finish folds the per-CTA partials
@@ -436,7 +445,6 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 8 ? 2 : 1)) fast_kernel(
         }
     }
 }
-
 struct Plan {
     int ok, warps, grid, gl;
     size_t smem;
@@ -455,9 +463,8 @@ int sm_count() {
     return g_sms;
 }
 
-size_t smem_bytes(int gl, int B, int warps) {
-    const int slot = B * 9;
-    return (size_t)(2 * ((gl * slot + 3) & ~3) + warps * ((B * 6 + 3) & ~3) + warps * 2 + 4) * sizeof(float);
+size_t smem_bytes(int gl, int B, int warps, int want_norm) {
+    return (size_t)smem_plan(gl, B, warps, want_norm).total * sizeof(float);
 }
 
 // the bone axis must be a DFS pre-order (every subtree a contiguous index range): pose.py:41-47 produces one
@@ -502,7 +509,8 @@ Plan make_plan(const p2c_fused_step_t* p) {
     const int B = p->tree.n_bones;
     const long total = (long)p->n_clips * p->clip_len;
     pl.gl = p->mode == P2C_MODE_POSE_CHANGES ? p->clip_len : (int)(total < 16 ? total : 16);
-    const size_t cap = 227 * 1024, s8 = smem_bytes(pl.gl, B, 8), s16 = smem_bytes(pl.gl, B, 16);
+    const size_t cap = 227 * 1024, s8 = smem_bytes(pl.gl, B, 8, p->proj_norm != nullptr),
+                 s16 = smem_bytes(pl.gl, B, 16, p->proj_norm != nullptr);
     if (2 * (s8 + 1024) <= cap || pl.gl <= 8) {
         pl.warps = 8;
         pl.smem = s8;
@@ -561,27 +569,23 @@ extern "C" int p2c_fused_fast(const p2c_fused_step_t* p, void* stream) {
     args.count3 = (double)total * B * 3;
     cudaStream_t st = (cudaStream_t)stream;
     if (args.mask) {
-        long blocks = (total * B + 255) / 256;
+        long blocks = (total + 7) / 8;
         if (blocks > COUNT_BLOCKS) blocks = COUNT_BLOCKS;
-        count_kernel<<<(int)blocks, 256, 0, st>>>(p->gt_2d, total * B, B, p->gt_2d_channels, p->hips, args.count2);
+        count_kernel<<<(int)blocks, 256, 0, st>>>(p->gt_2d, total, B, p->gt_2d_channels, p->hips, args.count2);
         P2C_LAUNCH_CHECK();
     }
-    static bool attr8 = false, attr16 = false;
-    if (pl.warps == 8) {
-        if (!attr8) {
-            cudaError_t e = cudaFuncSetAttribute(fast_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
-            if (e != cudaSuccess) return (int)e;
-            attr8 = true;
-        }
-        fast_kernel<8><<<pl.grid, 256, pl.smem, st>>>(args);
-    } else {
-        if (!attr16) {
-            cudaError_t e = cudaFuncSetAttribute(fast_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
-            if (e != cudaSuccess) return (int)e;
-            attr16 = true;
-        }
-        fast_kernel<16><<<pl.grid, 512, pl.smem, st>>>(args);
+    typedef void (*kern_t)(const FastArgs);
+    const bool carla = (B == 26);   // CARLA_SKELETON: bone count known at compile time (unrolled copies, immediates)
+    kern_t k = pl.warps == 8 ? (carla ? fast_kernel<8, 26> : fast_kernel<8, 0>)
+                             : (carla ? fast_kernel<16, 26> : fast_kernel<16, 0>);
+    static kern_t configured[4] = {nullptr, nullptr, nullptr, nullptr};
+    const int ki = (pl.warps == 8 ? 0 : 2) + (carla ? 0 : 1);
+    if (configured[ki] != k) {
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
+        if (e != cudaSuccess) return (int)e;
+        configured[ki] = k;
     }
+    k<<<pl.grid, pl.warps * 32, pl.smem, st>>>(args);
     P2C_LAUNCH_CHECK();
     return 0;
 }
