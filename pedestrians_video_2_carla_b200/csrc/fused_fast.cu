@@ -445,8 +445,411 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 8 ? 2 : 1)) fast_kernel(
         }
     }
 }
+// ------------------------------------------------------------------------------------------------------------------
+// Staged variant (the default when a clip group fits): the same phases, but every HBM access is a TMA bulk copy.
+//   inputs  : cp.async.bulk global -> shared for the NEXT clip group (6-D records, 3-D targets, 2-D targets), double
+//             buffered and signalled through an mbarrier, issued by one thread while the CTA works on the current group
+//   outputs : cp.async.bulk shared -> global of the flat staging regions (rel_rot, abs_rot, abs_loc, projection,
+//             normalised projection, grad wrt 6-D), issued by one thread after the barrier that completes the region
+// so no warp ever waits on a global load and the LSU only sees shared-memory traffic.
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_s2g(void* dst, const void* src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+struct SmemStaged {
+    int in_g3, in_g2, stage;  // input stage k starts at k * stage: 6-D records at +0, 3-D targets, 2-D targets
+    int rs, as, ts, ps, ns, gd, ys, ident, red, bars, total;
+};
+__device__ __host__ __forceinline__ SmemStaged staged_plan(int gl, int B, int gt_c, int warps, int want_norm) {
+    SmemStaged s;
+    int o = 0;
+    s.in_g3 = round4(gl * B * 6);
+    s.in_g2 = s.in_g3 + round4(gl * B * 3);
+    s.stage = s.in_g2 + round4(gl * B * gt_c);
+    o = 2 * s.stage;
+    s.rs = o; o += round4(gl * B * 9);
+    s.as = o; o += round4(gl * B * 9);
+    s.ts = o; o += round4(gl * B * 3);
+    s.ps = o; o += round4(gl * B * 3);
+    s.ns = o; o += want_norm ? round4(gl * B * 3) : 0;
+    s.gd = o; o += round4(gl * B * 6);
+    s.ys = o; o += round4(gl * B * 3);
+    s.ident = o; o += 12;
+    s.red = o; o += round4(warps * 2);
+    s.bars = o; o += 4;  // two 8-byte mbarriers
+    s.total = o;
+    return s;
+}
+
+// one flat region: TMA when source, destination and size are 16-byte multiples, else a cooperative copy by all threads
+__device__ __forceinline__ bool bulk_ok(const void* g, long off_floats, int n_floats) {
+    return (((reinterpret_cast<uintptr_t>(g) + (uintptr_t)off_floats * 4) & 15) == 0) && ((n_floats & 3) == 0);
+}
+
+template <int WARPS, int BT>
+__global__ void __launch_bounds__(WARPS * 32, (WARPS == 8 ? 2 : 1)) staged_kernel(const FastArgs a) {
+    extern __shared__ __align__(16) float smem[];
+    constexpr int NT = WARPS * 32;
+    const int tid = threadIdx.x, lane = tid & 31, wib = tid >> 5;
+    const int B = BT ? BT : a.B;
+    const int B3 = B * 3, B6 = B * 6, slot = B * 9, Bc = B * a.gt_c;
+    const bool act = lane < B;
+    const int lb = act ? lane : B - 1;
+    const SmemStaged sm = staged_plan(a.GL, B, a.gt_c, WARPS, a.proj_norm != nullptr);
+    float* Rs = smem + sm.rs;
+    float* As = smem + sm.as;
+    float* Ts = smem + sm.ts;
+    float* Ps = smem + sm.ps;
+    float* Ns = smem + sm.ns;
+    float* Gd = smem + sm.gd;
+    float* Ys = smem + sm.ys;
+    float* ident = smem + sm.ident;
+    float* red = smem + sm.red;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + sm.bars);
+    if (tid < 12) ident[tid] = (tid == 0 || tid == 4 || tid == 8) ? 1.f : 0.f;
+    if (tid == 0) {
+        mbar_init(bars, 1);
+        mbar_init(bars + 1, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    const int par = act ? a.parent[lane] : -1;
+    const int psrc = par < 0 ? IDENT_LANE : par;
+    const int sub_end = act ? a.sub_end[lane] : lane;
+    const int ancp = act ? a.anc_packed[lane] : 0x1ffffff;
+    const long total_poses = (long)a.N * a.L;
+    const long groups = a.scan ? (long)a.N : (total_poses + a.GL - 1) / a.GL;
+    const float k2 = a.w2 * 2.0f / (a.mask ? (float)__ldcg(a.count2) : (float)(total_poses * B * 2));
+    const float k3 = a.w3 * 2.0f / (float)a.count3;
+    const M3 camR = m3_from(a.cam.R);
+    const float camf = a.cam.f;
+    float s2 = 0.f, s3 = 0.f;
+
+    auto frames_of = [&](long g) { return (int)min((long)a.GL, total_poses - g * a.GL); };
+    auto in_bulk = [&](long g) {
+        const long m0 = g * a.GL;
+        const int nf = frames_of(g);
+        return bulk_ok(a.d6, m0 * B6, nf * B6) && bulk_ok(a.gt3, m0 * B3, nf * B3) && bulk_ok(a.gt2, m0 * Bc, nf * Bc);
+    };
+    auto issue_load = [&](long g, int st) {  // one thread
+        const long m0 = g * a.GL;
+        const int nf = frames_of(g);
+        mbar_expect_tx(bars + st, (uint32_t)(nf * (B6 + B3 + Bc)) * 4u);
+        float* in = smem + st * sm.stage;
+        bulk_g2s(in, a.d6 + m0 * B6, (uint32_t)(nf * B6) * 4u, bars + st);
+        bulk_g2s(in + sm.in_g3, a.gt3 + m0 * B3, (uint32_t)(nf * B3) * 4u, bars + st);
+        bulk_g2s(in + sm.in_g2, a.gt2 + m0 * Bc, (uint32_t)(nf * Bc) * 4u, bars + st);
+    };
+    auto store_out = [&](float* g, const float* s, long off, int n) {  // all threads call; after a barrier
+        if (g == nullptr) return;
+        if (bulk_ok(g, off, n)) {
+            if (tid == 0) bulk_s2g(g + off, s, (uint32_t)n * 4u);
+        } else {
+            block_copy_out<NT>(g + off, s, n, tid);
+        }
+    };
+
+    unsigned uses0 = 0, uses1 = 0;  // completed TMA fills per stage (mbarrier phase parity)
+    int it = 0;
+    if ((long)blockIdx.x < groups && in_bulk(blockIdx.x) && tid == 0) issue_load(blockIdx.x, 0);
+
+    for (long grp = blockIdx.x; grp < groups; grp += gridDim.x, ++it) {
+        const int st = it & 1;
+        const long m0 = grp * a.GL;
+        const int nf = frames_of(grp);
+        float* d6s = smem + st * sm.stage;
+        float* g3s = d6s + sm.in_g3;
+        float* g2s = d6s + sm.in_g2;
+        {   // prefetch the next group of this CTA into the other stage (its last readers passed the closing barrier)
+            const long nxt = grp + gridDim.x;
+            if (nxt < groups && in_bulk(nxt) && tid == 0) issue_load(nxt, st ^ 1);
+        }
+        if (in_bulk(grp)) {
+            const unsigned u = st ? uses1 : uses0;
+            while (!mbar_try_wait(bars + st, u & 1u)) {}
+            if (st) ++uses1; else ++uses0;
+        } else {  // unaligned group (odd clip length / odd pose offset): synchronous cooperative fill
+            for (int i = tid; i < nf * B6; i += NT) d6s[i] = __ldg(a.d6 + m0 * B6 + i);
+            for (int i = tid; i < nf * B3; i += NT) g3s[i] = __ldg(a.gt3 + m0 * B3 + i);
+            for (int i = tid; i < nf * Bc; i += NT) g2s[i] = __ldg(a.gt2 + m0 * Bc + i);
+            __syncthreads();
+        }
+        V3 lref{0.f, 0.f, 0.f};
+        if (a.scan) {  // one skeleton per clip: its bone offsets stay in registers for the whole group
+            const long row = a.ref_index ? (long)__ldg(a.ref_index + grp) : grp;
+            const float* rl = a.ref_loc + (row * B + lb) * 3;
+            lref = V3{__ldg(rl), __ldg(rl + 1), __ldg(rl + 2)};
+        }
+
+        // ---- phase A: 6-D -> C[t] (rotation_6d_to_matrix)
+        for (int f = wib; f < nf; f += WARPS) {
+            const float2* dp = reinterpret_cast<const float2*>(d6s + f * B6 + lb * 6);
+            const float2 u0 = dp[0], u1 = dp[1], u2 = dp[2];
+            const float d[6] = {u0.x, u0.y, u1.x, u1.y, u2.x, u2.y};
+            const GS r = gram_schmidt(d);
+            if (act) {
+                float* o = Rs + f * slot + lane * 9;
+                o[0] = r.b1.x; o[1] = r.b1.y; o[2] = r.b1.z;
+                o[3] = r.b2.x; o[4] = r.b2.y; o[5] = r.b2.z;
+                o[6] = r.b3.x; o[7] = r.b3.y; o[8] = r.b3.z;
+            }
+        }
+        fence_async_smem();   // relative_rot mode: these records are what the TMA store below reads
+        __syncthreads();
+        // ---- phase B: R[t] = C[t] . R[t-1] per bone
+        if (a.scan) {
+            if (tid < B) {
+                const long row = a.ref_index ? (long)__ldg(a.ref_index + grp) : grp;
+                M3 prev;
+                const float* rr = a.ref_rot + (row * B + tid) * 9;
+#pragma unroll
+                for (int i = 0; i < 9; ++i) prev.m[i] = __ldg(rr + i);
+                float* o = Rs + tid * 9;
+                M3 cur = m3_from(o);
+                for (int f = 0; f < nf; ++f) {
+                    M3 nxt;
+                    if (f + 1 < nf) nxt = m3_from(o + slot);
+                    prev = m3_mul(cur, prev);
+                    m3_to(o, prev);
+                    cur = nxt;
+                    o += slot;
+                }
+                fence_async_smem();
+            }
+            __syncthreads();
+        }
+        store_out(a.rel_rot, Rs, m0 * slot, nf * slot);
+        if (tid == 0) bulk_commit();
+
+        // ---- phase C: per frame FK + projection + loss + torque backward
+        for (int f = wib; f < nf; f += WARPS) {
+            const long m = m0 + f;
+            const float* q3 = g3s + f * B3 + lb * 3;
+            const V3 g3{q3[0], q3[1], q3[2]};
+            const float* q2 = g2s + (f * B + lb) * a.gt_c;
+            const float g2x = q2[0], g2y = q2[1];
+            V3 t = lref;
+            if (!a.scan) {
+                const long clip = m / a.L;
+                const long row = a.ref_index ? (long)__ldg(a.ref_index + clip) : clip;
+                const float* rl = a.ref_loc + (row * B + lb) * 3;
+                t = V3{__ldg(rl), __ldg(rl + 1), __ldg(rl + 2)};
+            }
+            if (!act) t = V3{0.f, 0.f, 0.f};
+            M3 A = m3_from(act ? Rs + f * slot + lane * 9 : ident);
+            for (int k = 0; k < a.nrounds; ++k) {
+                const int src = (ancp >> (5 * k)) & 31;
+                const M3 Am = m3_shfl(A, src);
+                const V3 tm = v3_shfl(t, src);
+                const V3 q = v3_mul_m(t, Am);
+                t = V3{q.x + tm.x, q.y + tm.y, q.z + tm.z};
+                A = m3_mul(A, Am);
+            }
+            V3 c;
+            {
+                V3 wp{t.y, -t.x, t.z};
+                if (a.world_rot) wp = v3_mul_m(wp, m3_from(a.world_rot + m * 9));
+                if (a.world_loc) { wp.x += __ldg(a.world_loc + m * 3); wp.y += __ldg(a.world_loc + m * 3 + 1); wp.z += __ldg(a.world_loc + m * 3 + 2); }
+                c = v3_mul_m(wp, camR);
+                c.x += a.cam.T[0]; c.y += a.cam.T[1]; c.z += a.cam.T[2];
+            }
+            const float iz = __fdividef(1.0f, c.z);
+            const V3 p{fmaf(-camf * c.x, iz, a.cam.px), fmaf(-camf * c.y, iz, a.cam.py), iz};
+            if (act) {
+                m3_to(As + f * slot + lane * 9, A);
+                float* o = Ts + f * B3 + lane * 3;
+                o[0] = t.x; o[1] = t.y; o[2] = t.z;
+                o = Ps + f * B3 + lane * 3;
+                o[0] = p.x; o[1] = p.y; o[2] = p.z;
+            }
+            float x = p.x, y = p.y;
+            bool lx = true, ly = true;
+            float inv = 1.f, dx = 0.f, dy = 0.f;
+            bool okn = true;
+            if (a.normalize) {
+                const float sx = __shfl_sync(FULL_MASK, p.x, a.hips), sy = __shfl_sync(FULL_MASK, p.y, a.hips);
+                dx = __shfl_sync(FULL_MASK, p.x, a.neck) - sx;
+                dy = __shfl_sync(FULL_MASK, p.y, a.neck) - sy;
+                const float scale = sqrtf(fmaf(dx, dx, dy * dy));
+                okn = scale > 0.f && scale <= 3.402823466e38f;
+                inv = __fdividef(1.0f, scale);
+                const float rx = (p.x - sx) * inv, ry = (p.y - sy) * inv;
+                lx = fabsf(rx) <= 3.402823466e38f;
+                ly = fabsf(ry) <= 3.402823466e38f;
+                x = lx ? rx : 0.f;
+                y = ly ? ry : 0.f;
+                const float q = nan_to_zero(p.z);
+                if (!(q >= 1e-5f)) { x = 0.f; y = 0.f; lx = ly = false; }
+                if (a.proj_norm && act) {
+                    float* o = Ns + f * B3 + lane * 3;
+                    o[0] = x; o[1] = y; o[2] = q;
+                }
+            }
+            const bool kept = act && (!a.mask || lane == a.hips || (g2x != 0.f && g2y != 0.f));
+            float gx = 0.f, gy = 0.f;
+            if (kept) {
+                const float ex = x - g2x, ey = y - g2y;
+                s2 = fmaf(ex, ex, fmaf(ey, ey, s2));
+                gx = lx ? k2 * ex : 0.f;
+                gy = ly ? k2 * ey : 0.f;
+            }
+            if (a.normalize) {
+                if (!okn) { gx = 0.f; gy = 0.f; inv = 0.f; }
+                const float sgx = warp_sum(gx), sgy = warp_sum(gy), sgn = warp_sum(fmaf(gx, x, gy * y));
+                gx *= inv;
+                gy *= inv;
+                const float gs = -sgn * inv * inv;
+                const float kx = gs * dx, ky = gs * dy;
+                if (lane == a.neck) { gx += kx; gy += ky; }
+                if (lane == a.hips) { gx -= fmaf(sgx, inv, kx); gy -= fmaf(sgy, inv, ky); }
+            }
+            V3 g;
+            {
+                const V3 e{t.x - g3.x, t.y - g3.y, t.z - g3.z};
+                if (act) s3 = fmaf(e.x, e.x, fmaf(e.y, e.y, fmaf(e.z, e.z, s3)));
+                const float fgx = camf * gx * iz, fgy = camf * gy * iz;
+                const V3 gc{-fgx, -fgy, fmaf(fgx, c.x, fgy * c.y) * iz};
+                V3 gw = v3_mul_mt(gc, camR);
+                if (a.world_rot) gw = v3_mul_mt(gw, m3_from(a.world_rot + m * 9));
+                g = V3{fmaf(k3, e.x, -gw.y), fmaf(k3, e.y, gw.x), fmaf(k3, e.z, gw.z)};
+                if (!act) g = V3{0.f, 0.f, 0.f};
+            }
+            float w[6] = {g.y * t.z - g.z * t.y, g.z * t.x - g.x * t.z, g.x * t.y - g.y * t.x, g.x, g.y, g.z};
+            float ex_[6];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) ex_[i] = w[i];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+#pragma unroll
+                for (int i = 0; i < 6; ++i) {
+                    const float v = __shfl_up_sync(FULL_MASK, w[i], o);
+                    if (lane >= o) w[i] += v;
+                }
+            }
+            float s[6];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) s[i] = __shfl_sync(FULL_MASK, w[i], sub_end) - (w[i] - ex_[i]);
+            const V3 mv{s[0] - (s[4] * t.z - s[5] * t.y), s[1] - (s[5] * t.x - s[3] * t.z), s[2] - (s[3] * t.y - s[4] * t.x)};
+            const M3 Ap = m3_shfl(A, psrc);
+            const V3 yv = v3_mul_mt(mv, Ap);
+            if (act) {
+                float* o = Ys + f * B3 + lane * 3;
+                o[0] = yv.x; o[1] = yv.y; o[2] = yv.z;
+            }
+        }
+        fence_async_smem();
+        if (tid == 0) bulk_wait_read_all();   // the previous group's grad store has finished reading Gd
+        __syncthreads();
+        store_out(a.abs_rot, As, m0 * slot, nf * slot);
+        store_out(a.abs_loc, Ts, m0 * B3, nf * B3);
+        store_out(a.proj, Ps, m0 * B3, nf * B3);
+        store_out(a.proj_norm, Ns, m0 * B3, nf * B3);
+        if (tid == 0) bulk_commit();
+        // ---- phase D: z[t] = sum_{s >= t} y[s]
+        if (a.scan) {
+            for (int col = tid; col < B3; col += NT) {
+                float acc = 0.f;
+                for (int f = nf - 1; f >= 0; --f) {
+                    acc += Ys[f * B3 + col];
+                    Ys[f * B3 + col] = acc;
+                }
+            }
+            __syncthreads();
+        }
+        // ---- phase E: omega[t] = R[t] z[t]; tangent-form Gram-Schmidt backward -> grad wrt the 6-D input
+        for (int f = wib; f < nf; f += WARPS) {
+            const float2* dp = reinterpret_cast<const float2*>(d6s + f * B6 + lb * 6);
+            const float2 u0 = dp[0], u1 = dp[1], u2 = dp[2];
+            const float d[6] = {u0.x, u0.y, u1.x, u1.y, u2.x, u2.y};
+            float o6[6];
+            const float* zp = Ys + f * B3 + lb * 3;
+            const V3 z{zp[0], zp[1], zp[2]};
+            const V3 om = v3_mul_mt(z, m3_from(Rs + f * slot + lb * 9));
+            gram_schmidt_bwd_tangent(gram_schmidt(d), om, o6);
+            if (act) {
+                float2* o = reinterpret_cast<float2*>(Gd + f * B6 + lane * 6);
+                o[0] = make_float2(o6[0], o6[1]);
+                o[1] = make_float2(o6[2], o6[3]);
+                o[2] = make_float2(o6[4], o6[5]);
+            }
+        }
+        fence_async_smem();
+        if (tid == 0) bulk_wait_read_all();   // rel_rot / abs_* / projection stores have finished reading their regions
+        __syncthreads();
+        store_out(a.g_d6, Gd, m0 * B6, nf * B6);
+        if (tid == 0) bulk_commit();
+    }
+    if (tid == 0) bulk_wait_all();
+
+    // ---- loss sums: fixed-order reduction, the last CTA to finish folds the per-CTA partials
+    s2 = warp_sum(s2);
+    s3 = warp_sum(s3);
+    if (lane == 0) { red[wib * 2] = s2; red[wib * 2 + 1] = s3; }
+    __syncthreads();
+    __shared__ bool last;
+    if (tid == 0) {
+        float x = 0.f, y = 0.f;
+        for (int w = 0; w < WARPS; ++w) { x += red[w * 2]; y += red[w * 2 + 1]; }
+        a.partials[blockIdx.x * 2] = x;
+        a.partials[blockIdx.x * 2 + 1] = y;
+        __threadfence();
+        last = (atomicAdd(a.ticket, 1u) == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (last && wib == 0) {
+        __threadfence();
+        double d2 = 0.0, d3 = 0.0;
+        for (int i = lane; i < (int)gridDim.x; i += 32) {
+            d2 += (double)__ldcg(a.partials + i * 2);
+            d3 += (double)__ldcg(a.partials + i * 2 + 1);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            d2 += __shfl_xor_sync(FULL_MASK, d2, o);
+            d3 += __shfl_xor_sync(FULL_MASK, d3, o);
+        }
+        if (lane == 0) {
+            const double c2 = a.mask ? (double)*a.count2 : (double)total_poses * B * 2;
+            const float l2 = (float)(d2 / c2), l3 = (float)(d3 / a.count3);
+            a.losses[0] = l2; a.losses[1] = l3; a.losses[2] = a.w2 * l2 + a.w3 * l3;
+            a.losses[3] = (float)d2; a.losses[4] = (float)c2; a.losses[5] = (float)d3; a.losses[6] = (float)a.count3;
+            a.losses[7] = 0.f;
+            *a.ticket = 0u;
+            *a.count2 = 0;
+        }
+    }
+}
+
 struct Plan {
-    int ok, warps, grid, gl;
+    int ok, warps, grid, gl, staged;
     size_t smem;
 };
 
@@ -509,14 +912,21 @@ Plan make_plan(const p2c_fused_step_t* p) {
     const int B = p->tree.n_bones;
     const long total = (long)p->n_clips * p->clip_len;
     pl.gl = p->mode == P2C_MODE_POSE_CHANGES ? p->clip_len : (int)(total < 16 ? total : 16);
-    const size_t cap = 227 * 1024, s8 = smem_bytes(pl.gl, B, 8, p->proj_norm != nullptr),
-                 s16 = smem_bytes(pl.gl, B, 16, p->proj_norm != nullptr);
-    if (2 * (s8 + 1024) <= cap || pl.gl <= 8) {
-        pl.warps = 8;
-        pl.smem = s8;
+    const size_t cap = 227 * 1024;
+    const int want_norm = p->proj_norm != nullptr;
+    const size_t t8 = (size_t)staged_plan(pl.gl, B, p->gt_2d_channels, 8, want_norm).total * sizeof(float);
+    const size_t t16 = (size_t)staged_plan(pl.gl, B, p->gt_2d_channels, 16, want_norm).total * sizeof(float);
+    const size_t s8 = smem_bytes(pl.gl, B, 8, want_norm), s16 = smem_bytes(pl.gl, B, 16, want_norm);
+    const char* no_tma = getenv("P2C_DISABLE_TMA");  // test hook: the register-staged variant
+    const bool allow_staged = !(no_tma && no_tma[0] == '1');
+    if (allow_staged && (2 * (t8 + 1024) <= cap || pl.gl <= 8) && t8 + 1024 <= cap) {
+        pl.warps = 8; pl.smem = t8; pl.staged = 1;       // TMA-staged, two CTAs per SM
+    } else if (allow_staged && t16 + 1024 <= cap) {
+        pl.warps = 16; pl.smem = t16; pl.staged = 1;     // TMA-staged, one 16-warp CTA per SM
+    } else if (2 * (s8 + 1024) <= cap || pl.gl <= 8) {
+        pl.warps = 8; pl.smem = s8;
     } else {
-        pl.warps = 16;
-        pl.smem = s16;
+        pl.warps = 16; pl.smem = s16;
     }
     if (pl.smem + 1024 > cap) return pl;
     const long groups = p->mode == P2C_MODE_POSE_CHANGES ? p->n_clips : (total + pl.gl - 1) / pl.gl;
@@ -576,10 +986,15 @@ extern "C" int p2c_fused_fast(const p2c_fused_step_t* p, void* stream) {
     }
     typedef void (*kern_t)(const FastArgs);
     const bool carla = (B == 26);   // CARLA_SKELETON: bone count known at compile time (unrolled copies, immediates)
-    kern_t k = pl.warps == 8 ? (carla ? fast_kernel<8, 26> : fast_kernel<8, 0>)
-                             : (carla ? fast_kernel<16, 26> : fast_kernel<16, 0>);
-    static kern_t configured[4] = {nullptr, nullptr, nullptr, nullptr};
-    const int ki = (pl.warps == 8 ? 0 : 2) + (carla ? 0 : 1);
+    kern_t k;
+    if (pl.staged)
+        k = pl.warps == 8 ? (carla ? staged_kernel<8, 26> : staged_kernel<8, 0>)
+                          : (carla ? staged_kernel<16, 26> : staged_kernel<16, 0>);
+    else
+        k = pl.warps == 8 ? (carla ? fast_kernel<8, 26> : fast_kernel<8, 0>)
+                          : (carla ? fast_kernel<16, 26> : fast_kernel<16, 0>);
+    static kern_t configured[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    const int ki = (pl.staged ? 4 : 0) + (pl.warps == 8 ? 0 : 2) + (carla ? 0 : 1);
     if (configured[ki] != k) {
         cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
         if (e != cudaSuccess) return (int)e;
