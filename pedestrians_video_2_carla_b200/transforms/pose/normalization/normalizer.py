@@ -1,0 +1,18 @@
+"""Normalizer (reference transforms/pose/normalization/normalizer.py:20-41): hips -> (0,0), |neck - hips| -> 1,
+NaN/inf -> 0, xy zeroed where channel 2 < near_zero.  Forward and backward are one kernel each."""
+from .... import ops
+from .hips_neck_extractor import HipsNeckExtractor
+
+
+class Normalizer(object):
+    def __init__(self, extractor=None, near_zero=1e-5):
+        self.extractor = extractor if extractor is not None else HipsNeckExtractor()
+        self._near_zero = near_zero
+
+    def __repr__(self):
+        return '%s(extractor=%s)' % (self.__class__.__name__, self.extractor.__class__.__name__)
+
+    def __call__(self, sample, dim=2, *args, **kwargs):
+        if dim != 2:
+            raise NotImplementedError('only the 2-D normalisation of the projection is on the accelerated path')
+        return ops.hips_neck_normalize(sample, self.extractor.hips, self.extractor.neck, self._near_zero)
