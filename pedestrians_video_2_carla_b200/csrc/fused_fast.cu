@@ -487,19 +487,31 @@ struct SmemStaged {
     int in_g3, in_g2, stage;  // input stage k starts at k * stage: 6-D records at +0, 3-D targets, 2-D targets
     int rs, as, ts, ps, ns, gd, ys, ident, red, bars, total;
 };
-__device__ __host__ __forceinline__ SmemStaged staged_plan(int gl, int B, int gt_c, int warps, int want_norm) {
+// slim = 1: one input stage, abs_loc / projection records written over the target records they were computed from,
+// gradient records over the abs_rot records: 55 KB per 16-frame CARLA clip, four CTAs per SM
+__device__ __host__ __forceinline__ SmemStaged staged_plan(int gl, int B, int gt_c, int warps, int want_norm,
+                                                           int slim = 0) {
     SmemStaged s;
     int o = 0;
     s.in_g3 = round4(gl * B * 6);
     s.in_g2 = s.in_g3 + round4(gl * B * 3);
-    s.stage = s.in_g2 + round4(gl * B * gt_c);
-    o = 2 * s.stage;
+    s.stage = s.in_g2 + round4(gl * B * (gt_c > 3 ? gt_c : 3));
+    o = (slim ? 1 : 2) * s.stage;
     s.rs = o; o += round4(gl * B * 9);
     s.as = o; o += round4(gl * B * 9);
-    s.ts = o; o += round4(gl * B * 3);
-    s.ps = o; o += round4(gl * B * 3);
+    if (slim) {
+        s.ts = s.in_g3;
+        s.ps = s.in_g2;
+    } else {
+        s.ts = o; o += round4(gl * B * 3);
+        s.ps = o; o += round4(gl * B * 3);
+    }
     s.ns = o; o += want_norm ? round4(gl * B * 3) : 0;
-    s.gd = o; o += round4(gl * B * 6);
+    if (slim) {
+        s.gd = s.as;
+    } else {
+        s.gd = o; o += round4(gl * B * 6);
+    }
     s.ys = o; o += round4(gl * B * 3);
     s.ident = o; o += 12;
     s.red = o; o += round4(warps * 2);
@@ -513,8 +525,8 @@ __device__ __forceinline__ bool bulk_ok(const void* g, long off_floats, int n_fl
     return (((reinterpret_cast<uintptr_t>(g) + (uintptr_t)off_floats * 4) & 15) == 0) && ((n_floats & 3) == 0);
 }
 
-template <int WARPS, int BT>
-__global__ void __launch_bounds__(WARPS * 32, (WARPS == 8 ? 2 : 1)) staged_kernel(const FastArgs a) {
+template <int WARPS, int BT, bool SLIM>
+__global__ void __launch_bounds__(WARPS * 32, (SLIM ? 4 : (WARPS == 8 ? 2 : 1))) staged_kernel(const FastArgs a) {
     extern __shared__ __align__(16) float smem[];
     constexpr int NT = WARPS * 32;
     const int tid = threadIdx.x, lane = tid & 31, wib = tid >> 5;
@@ -522,7 +534,7 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 8 ? 2 : 1)) staged_kerne
     const int B3 = B * 3, B6 = B * 6, slot = B * 9, Bc = B * a.gt_c;
     const bool act = lane < B;
     const int lb = act ? lane : B - 1;
-    const SmemStaged sm = staged_plan(a.GL, B, a.gt_c, WARPS, a.proj_norm != nullptr);
+    const SmemStaged sm = staged_plan(a.GL, B, a.gt_c, WARPS, a.proj_norm != nullptr, SLIM ? 1 : 0);
     float* Rs = smem + sm.rs;
     float* As = smem + sm.as;
     float* Ts = smem + sm.ts;
@@ -579,16 +591,18 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 8 ? 2 : 1)) staged_kerne
 
     unsigned uses0 = 0, uses1 = 0;  // completed TMA fills per stage (mbarrier phase parity)
     int it = 0;
-    if ((long)blockIdx.x < groups && in_bulk(blockIdx.x) && tid == 0) issue_load(blockIdx.x, 0);
+    if (!SLIM && (long)blockIdx.x < groups && in_bulk(blockIdx.x) && tid == 0) issue_load(blockIdx.x, 0);
 
     for (long grp = blockIdx.x; grp < groups; grp += gridDim.x, ++it) {
-        const int st = it & 1;
+        const int st = SLIM ? 0 : (it & 1);
         const long m0 = grp * a.GL;
         const int nf = frames_of(grp);
         float* d6s = smem + st * sm.stage;
         float* g3s = d6s + sm.in_g3;
         float* g2s = d6s + sm.in_g2;
-        {   // prefetch the next group of this CTA into the other stage (its last readers passed the closing barrier)
+        if (SLIM) {  // single stage: its readers passed the closing barrier, the stores out of it were waited for
+            if (in_bulk(grp) && tid == 0) issue_load(grp, 0);
+        } else {     // prefetch the next group of this CTA into the other stage
             const long nxt = grp + gridDim.x;
             if (nxt < groups && in_bulk(nxt) && tid == 0) issue_load(nxt, st ^ 1);
         }
@@ -773,6 +787,7 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 8 ? 2 : 1)) staged_kerne
         store_out(a.proj, Ps, m0 * B3, nf * B3);
         store_out(a.proj_norm, Ns, m0 * B3, nf * B3);
         if (tid == 0) bulk_commit();
+        if (SLIM && tid == 0) bulk_wait_read_all();   // abs_rot records are about to be overwritten by the gradient
         // ---- phase D: z[t] = sum_{s >= t} y[s]
         if (a.scan) {
             for (int col = tid; col < B3; col += NT) {
@@ -782,6 +797,8 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 8 ? 2 : 1)) staged_kerne
                     Ys[f * B3 + col] = acc;
                 }
             }
+            __syncthreads();
+        } else if (SLIM) {
             __syncthreads();
         }
         // ---- phase E: omega[t] = R[t] z[t]; tangent-form Gram-Schmidt backward -> grad wrt the 6-D input
@@ -849,7 +866,7 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 8 ? 2 : 1)) staged_kerne
 }
 
 struct Plan {
-    int ok, warps, grid, gl, staged;
+    int ok, warps, grid, gl, staged, slim;
     size_t smem;
 };
 
@@ -919,7 +936,13 @@ Plan make_plan(const p2c_fused_step_t* p) {
     const size_t s8 = smem_bytes(pl.gl, B, 8, want_norm), s16 = smem_bytes(pl.gl, B, 16, want_norm);
     const char* no_tma = getenv("P2C_DISABLE_TMA");  // test hook: the register-staged variant
     const bool allow_staged = !(no_tma && no_tma[0] == '1');
-    if (allow_staged && (2 * (t8 + 1024) <= cap || pl.gl <= 8) && t8 + 1024 <= cap) {
+    const long groups_ = p->mode == P2C_MODE_POSE_CHANGES ? p->n_clips : (total + pl.gl - 1) / pl.gl;
+    const size_t tslim = (size_t)staged_plan(pl.gl, B, p->gt_2d_channels, 8, want_norm, 1).total * sizeof(float);
+    const char* no_slim = getenv("P2C_DISABLE_SLIM");
+    if (allow_staged && !(no_slim && no_slim[0] == '1') && p->gt_2d_channels == 3 && 4 * (tslim + 1024) <= 228 * 1024 &&
+        (groups_ >= 3L * sm_count() || (getenv("P2C_FORCE_SLIM") && getenv("P2C_FORCE_SLIM")[0] == '1'))) {
+        pl.warps = 8; pl.smem = tslim; pl.staged = 1; pl.slim = 1;   // many clips: 4 CTAs (32 warps) per SM
+    } else if (allow_staged && (2 * (t8 + 1024) <= cap || pl.gl <= 8) && t8 + 1024 <= cap) {
         pl.warps = 8; pl.smem = t8; pl.staged = 1;       // TMA-staged, two CTAs per SM
     } else if (allow_staged && t16 + 1024 <= cap) {
         pl.warps = 16; pl.smem = t16; pl.staged = 1;     // TMA-staged, one 16-warp CTA per SM
@@ -931,7 +954,8 @@ Plan make_plan(const p2c_fused_step_t* p) {
     if (pl.smem + 1024 > cap) return pl;
     const long groups = p->mode == P2C_MODE_POSE_CHANGES ? p->n_clips : (total + pl.gl - 1) / pl.gl;
     int per_sm = pl.warps == 8 ? (int)(cap / (pl.smem + 1024)) : 1;
-    if (per_sm > 2) per_sm = 2;   // __launch_bounds__(256, 2): 128 registers per thread
+    if (pl.slim) per_sm = 4;      // __launch_bounds__(256, 4): 64 registers per thread
+    else if (per_sm > 2) per_sm = 2;   // __launch_bounds__(256, 2): 128 registers per thread
     if (per_sm < 1) per_sm = 1;
     const long slots = (long)sm_count() * per_sm;
     pl.grid = (int)(groups < slots ? groups : slots);
@@ -988,13 +1012,14 @@ extern "C" int p2c_fused_fast(const p2c_fused_step_t* p, void* stream) {
     const bool carla = (B == 26);   // CARLA_SKELETON: bone count known at compile time (unrolled copies, immediates)
     kern_t k;
     if (pl.staged)
-        k = pl.warps == 8 ? (carla ? staged_kernel<8, 26> : staged_kernel<8, 0>)
-                          : (carla ? staged_kernel<16, 26> : staged_kernel<16, 0>);
+        k = pl.slim ? (carla ? staged_kernel<8, 26, true> : staged_kernel<8, 0, true>)
+            : pl.warps == 8 ? (carla ? staged_kernel<8, 26, false> : staged_kernel<8, 0, false>)
+                            : (carla ? staged_kernel<16, 26, false> : staged_kernel<16, 0, false>);
     else
         k = pl.warps == 8 ? (carla ? fast_kernel<8, 26> : fast_kernel<8, 0>)
                           : (carla ? fast_kernel<16, 26> : fast_kernel<16, 0>);
-    static kern_t configured[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    const int ki = (pl.staged ? 4 : 0) + (pl.warps == 8 ? 0 : 2) + (carla ? 0 : 1);
+    static kern_t configured[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    const int ki = pl.slim ? 8 + (carla ? 0 : 1) : (pl.staged ? 4 : 0) + (pl.warps == 8 ? 0 : 2) + (carla ? 0 : 1);
     if (configured[ki] != k) {
         cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
         if (e != cudaSuccess) return (int)e;

@@ -105,6 +105,21 @@ def test_fused_step_shapes(ops, lib, n, l):
     compare(res, grad, want, d6.grad, ref_grad32=oracle_grad32(c, gt2, gt3))
 
 
+@pytest.mark.parametrize('variant', ['P2C_FORCE_SLIM', 'P2C_DISABLE_TMA', 'P2C_DISABLE_FAST'])
+@pytest.mark.parametrize('mode', ['pose_changes', 'relative_rot'])
+def test_fused_step_kernel_variants(ops, lib, monkeypatch, variant, mode):
+    """Every kernel variant behind p2c_fused_step (4-CTA/SM slim TMA kernel, register-staged kernel, exact generic
+    composite) against the oracle on the same case; the default (double-buffered TMA) variant is covered above."""
+    monkeypatch.setenv(variant, '1')
+    c = make_case(20, 16, 4242)
+    gt2, gt3 = make_targets(c, mode)
+    d6 = c['d6'].clone().requires_grad_(True)
+    want = oracle_step(c, O.rotation_6d_to_matrix(d6), mode, gt=(gt2, gt3))
+    want['loc_2d_3d'].backward()
+    res, grad = run_cuda(ops, lib, c, c['d6'], gt2, gt3, mode, True, True)
+    compare(res, grad, want, d6.grad, ref_grad32=oracle_grad32(c, gt2, gt3, mode))
+
+
 def test_fused_step_weights(ops, lib):
     c = make_case(6, 4, 5)
     gt2, gt3 = make_targets(c)
