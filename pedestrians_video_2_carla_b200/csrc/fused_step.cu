@@ -10,6 +10,10 @@
 extern "C" int p2c_fused_fast_supported(const p2c_fused_step_t* p);
 extern "C" long p2c_fused_fast_workspace_floats(void);
 extern "C" int p2c_fused_fast(const p2c_fused_step_t* p, void* stream);
+// the pose-per-lane tile kernel (fused_tile.cu): preferred whenever it supports the call
+extern "C" int p2c_fused_tile_supported(const p2c_fused_step_t* p);
+extern "C" int p2c_fused_tile_launches(const p2c_fused_step_t* p);
+extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream);
 
 namespace {
 
@@ -201,6 +205,7 @@ extern "C" int p2c_fused_fast_launches(const p2c_fused_step_t* p);
 extern "C" int p2c_fused_step_launches(const p2c_fused_step_t* p) {
     if (!p) return P2C_E_NULL;
     if (p->n_clips == 0) return 0;
+    if (p2c_fused_tile_supported(p)) return p2c_fused_tile_launches(p);
     if (p2c_fused_fast_supported(p)) return p2c_fused_fast_launches(p);
     return 5 + (p->input_6d ? 2 : 0);  // fk_fwd, loss_fwd, finalize, loss_bwd, fk_bwd (+ rot6d fwd/bwd)
 }
@@ -214,6 +219,7 @@ extern "C" int p2c_fused_step(const p2c_fused_step_t* p, void* stream) {
     if (p->n_clips == 0) return 0;
     if (!p->pose_in || !p->ref_loc || !p->gt_2d || !p->gt_3d || !p->g_pose_in || !p->workspace || !p->losses)
         return P2C_E_NULL;
+    if (p2c_fused_tile_supported(p)) return p2c_fused_tile(p, stream);
     if (p2c_fused_fast_supported(p)) return p2c_fused_fast(p, stream);
 
     if (!p->rel_rot && p->mode == P2C_MODE_POSE_CHANGES) return P2C_E_NULL;

@@ -105,11 +105,12 @@ def test_fused_step_shapes(ops, lib, n, l):
     compare(res, grad, want, d6.grad, ref_grad32=oracle_grad32(c, gt2, gt3))
 
 
-@pytest.mark.parametrize('variant', ['P2C_FORCE_SLIM', 'P2C_DISABLE_TMA', 'P2C_DISABLE_FAST'])
+@pytest.mark.parametrize('variant', ['P2C_DISABLE_TILE', 'P2C_FORCE_SLIM', 'P2C_DISABLE_TMA', 'P2C_DISABLE_FAST'])
 @pytest.mark.parametrize('mode', ['pose_changes', 'relative_rot'])
 def test_fused_step_kernel_variants(ops, lib, monkeypatch, variant, mode):
-    """Every kernel variant behind p2c_fused_step (4-CTA/SM slim TMA kernel, register-staged kernel, exact generic
-    composite) against the oracle on the same case; the default (double-buffered TMA) variant is covered above."""
+    """Every older kernel variant behind p2c_fused_step (bone-per-lane double-buffered TMA kernel, its 4-CTA/SM slim
+    form, the register-staged kernel, the exact generic composite) against the oracle on the same case; the default
+    (pose-per-lane tile kernel, fused_tile.cu) is what every other test in this file runs."""
     monkeypatch.setenv(variant, '1')
     c = make_case(20, 16, 4242)
     gt2, gt3 = make_targets(c, mode)
