@@ -43,7 +43,7 @@ constexpr int MAX_THREADS = 832;
 struct TileArgs {
     int N, L, B, P, PS, slices, scan;   // clips, frames per clip, bones, poses per tile, P rounded up to 32, PS/32
     int hips, neck, normalize, mask, nlevels, npairs;
-    int stop;   // debug: leave the tile after phase `stop` (P2C_TILE_STOP; default: never)
+    int tree_warps;   // warps that take part in the level-synchronous tree phases
     int8_t parent[P2C_MAX_BONES];
     int8_t order[P2C_MAX_BONES];          // bones sorted by tree level
     int8_t lvl_start[MAX_LEVELS + 1];     // order[lvl_start[l] .. lvl_start[l+1]) = bones of level l
@@ -204,10 +204,6 @@ __device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bu
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-__device__ __host__ __forceinline__ bool aligned16(const void* g, long off_floats) {
-    return ((reinterpret_cast<uintptr_t>(g) + (uintptr_t)off_floats * 4) & 15) == 0;
-}
-
 // shared-memory plan (floats); every region starts 16-byte aligned (PS is a multiple of 32)
 struct TilePlan {
     int d, g3, g2, r, a, nrm, part, row, red, bars, total;
@@ -222,9 +218,9 @@ __device__ __host__ __forceinline__ TilePlan tile_plan(int PS, int B, int npairs
     s.a = o; o += PS * B * 9;
     s.nrm = o; o += 8 * PS;            // sx, sy, dx, dy, inv, ok per pose
     s.part = o; o += npairs * 3 * PS;  // per bone pair: sum gx, sum gy, sum (gx x + gy y) per pose
-    s.row = o; o += PS;                // skeleton-table row per pose
+    s.row = o; o += 2 * PS;            // skeleton-table row per pose, double buffered (next tile's rows prefetched)
     s.red = o; o += 2 * 32;            // loss partials per warp
-    s.bars = o; o += 4;                // two 8-byte mbarriers
+    s.bars = o; o += 8;                // three 8-byte mbarriers
     s.total = o;
     return s;
 }
@@ -315,90 +311,88 @@ __device__ __forceinline__ V3 bone_loss(const TileArgs& a, int b, const V3& t, f
     return V3{fmaf(cx.k3, e.x, gp.x), fmaf(cx.k3, e.y, gp.y), fmaf(cx.k3, e.z, gp.z)};
 }
 
-#define TILE_STOP(k)                                  \
-    if (a.stop <= (k)) {                              \
-        if (tid == 0) { bulk_commit(); bulk_wait_read_all(); } \
-        __syncthreads();                              \
-        continue;                                     \
-    }
+__device__ __forceinline__ void named_barrier(int id, int threads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
 
+// BT / SL: bones and 32-pose slices per tile at compile time (0 = read from the arguments)
+template <int BT, int SL>
 __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) {
     extern __shared__ __align__(16) float smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NT = blockDim.x, W = NT >> 5;
-    const int B = a.B, B3 = B * 3, B6 = B * 6, B9 = B * 9, PS = a.PS, L = a.L;
-    const TilePlan sm = tile_plan(PS, B, a.npairs);
+    const int B = BT ? BT : a.B, slices = SL ? SL : a.slices, npairs = B / 2;
+    const int B3 = B * 3, B6 = B * 6, B9 = B * 9, PS = 32 * slices, L = a.L;
+    const TilePlan sm = tile_plan(PS, B, npairs);
     float* D = smem + sm.d;
-    float* G3 = smem + sm.g3;
+    float* G3 = smem + sm.g3;     // G3 and G2 are adjacent: together they hold the re-fetched 6-D records
     float* G2 = smem + sm.g2;
     float* R = smem + sm.r;
     float* A = smem + sm.a;
     float* NRM = smem + sm.nrm;
     float* PART = smem + sm.part;
-    int* ROW = reinterpret_cast<int*>(smem + sm.row);
+    int* ROW = reinterpret_cast<int*>(smem + sm.row);   // two buffers of PS
     float* red = smem + sm.red;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + sm.bars);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + sm.bars);   // [0] 6-D in, [1] targets in, [2] 6-D again
     float* TS = D;               // SoA scratch rows [0, 3B): t_b, later subtree sums of g x t
     float* GV = D + B3 * PS;     // SoA scratch rows [3B, 6B): g_b, later subtree sums of g
-    if (tid == 0) {
-        mbar_init(bars, 1);
-        mbar_init(bars + 1, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncthreads();
-
+    const bool tma = tid == (W - 1) * 32;   // the thread that issues every bulk copy (a warp without tree work)
+    const int TW = a.tree_warps;            // warps that walk the tree; the others skip to the next CTA barrier
     const long total = (long)a.N * L;
     const long ntiles = (total + a.P - 1) / a.P;
+
+    auto load_d6 = [&](long tile) {
+        const long m0 = tile * a.P;
+        const uint32_t bytes = (uint32_t)((int)min((long)a.P, total - m0) * B6) * 4u;
+        mbar_expect_tx(bars, bytes);
+        bulk_g2s(D, a.d6 + m0 * B6, bytes, bars);
+    };
+    auto load_targets = [&](long tile) {
+        const long m0 = tile * a.P;
+        const uint32_t bytes = (uint32_t)((int)min((long)a.P, total - m0) * B3) * 4u;
+        mbar_expect_tx(bars + 1, 2u * bytes);
+        bulk_g2s(G3, a.gt3 + m0 * B3, bytes, bars + 1);
+        bulk_g2s(G2, a.gt2 + m0 * B3, bytes, bars + 1);
+    };
+    auto fill_rows = [&](long tile, int buf) {   // skeleton-table row of every pose (lanes past the tile repeat its last)
+        const long m0 = tile * a.P;
+        const int np = (int)min((long)a.P, total - m0);
+        for (int i = lane; i < PS; i += 32) {
+            const long clip = (m0 + min(i, np - 1)) / L;
+            ROW[buf * PS + i] = a.ref_index ? __ldg(a.ref_index + clip) : (int)clip;
+        }
+    };
+
+    if (tma) {
+        mbar_init(bars, 1);
+        mbar_init(bars + 1, 1);
+        mbar_init(bars + 2, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        if ((long)blockIdx.x < ntiles) {
+            load_d6(blockIdx.x);
+            load_targets(blockIdx.x);
+        }
+    }
+    if (warp == 0 && (long)blockIdx.x < ntiles) fill_rows(blockIdx.x, 0);
+    __syncthreads();
+
     const float k2 = a.w2 * 2.0f / (a.mask ? (float)__ldcg(a.count2) : (float)(total * B * 2));
     const float k3 = a.w3 * 2.0f / (float)a.count3;
     float s2 = 0.f, s3 = 0.f;
-    unsigned use0 = 0, use1 = 0;   // completed fills per mbarrier (phase parity)
+    unsigned it = 0;
 
-    for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
-        const long m0 = tile * a.P;
+    for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        const long m0 = tile * a.P, nxt = tile + gridDim.x;
         const int np = (int)min((long)a.P, total - m0);
-        // TMA needs 16-byte aligned addresses and sizes on both sides; otherwise cooperative copies (odd tiles)
-        const bool bulk = ((np * B3) & 3) == 0 && aligned16(a.d6, m0 * B6) && aligned16(a.gt3, m0 * B3) &&
-                          aligned16(a.gt2, m0 * B3) && aligned16(a.g_d6, m0 * B6) &&
-                          (!a.rel_rot || aligned16(a.rel_rot, m0 * B9)) && (!a.abs_rot || aligned16(a.abs_rot, m0 * B9)) &&
-                          (!a.abs_loc || aligned16(a.abs_loc, m0 * B3)) && (!a.proj || aligned16(a.proj, m0 * B3));
-        auto store_out = [&](float* g, const float* s, long off, int n) {   // all threads call; after a barrier
-            if (g == nullptr) return;
-            if (bulk) {
-                if (tid == 0) bulk_s2g(g + off, s, (uint32_t)n * 4u);
-            } else {
-                for (int i = tid; i < n; i += NT) g[off + i] = s[i];
-            }
-        };
-        // ---- inputs
-        if (bulk) {
-            if (tid == 0) {
-                mbar_expect_tx(bars, (uint32_t)(np * (B6 + B3 + B3)) * 4u);
-                bulk_g2s(D, a.d6 + m0 * B6, (uint32_t)(np * B6) * 4u, bars);
-                bulk_g2s(G3, a.gt3 + m0 * B3, (uint32_t)(np * B3) * 4u, bars);
-                bulk_g2s(G2, a.gt2 + m0 * B3, (uint32_t)(np * B3) * 4u, bars);
-            }
-        } else {
-            for (int i = tid; i < np * B6; i += NT) D[i] = __ldg(a.d6 + m0 * B6 + i);
-            for (int i = tid; i < np * B3; i += NT) G3[i] = __ldg(a.gt3 + m0 * B3 + i);
-            for (int i = tid; i < np * B3; i += NT) G2[i] = __ldg(a.gt2 + m0 * B3 + i);
-        }
-        if (tid < PS) {   // skeleton-table row of every pose of the tile (lanes past the tile repeat its last pose)
-            const long clip = (m0 + min(tid, np - 1)) / L;
-            ROW[tid] = a.ref_index ? __ldg(a.ref_index + clip) : (int)clip;
-        }
-        if (bulk) {
-            while (!mbar_try_wait(bars, use0 & 1u)) {}
-            ++use0;
-        }
-        __syncthreads();
+        const int* row = ROW + (it & 1) * PS;
+        while (!mbar_try_wait(bars, it & 1u)) {}
+        __syncthreads();   // #1 (first tile: the row table; later tiles: ordered by the barriers of the previous tile)
 
-        TILE_STOP(0)
         // ---- phase A: 6-D -> C[t] (rotation_6d_to_matrix), two bones per task
         {
             float* dst = a.scan ? A : R;
-            const int nt = a.slices * a.npairs;
+            const int nt = slices * npairs;
             for (int task = warp; task < nt; task += W) {
-                const int slice = task / a.npairs, q = task - slice * a.npairs;
+                const int slice = task >= npairs ? 1 : 0, q = task - slice * npairs;
                 const int col = slice * 32 + lane, pl = min(col, np - 1);
                 const float4* dp = reinterpret_cast<const float4*>(D + pl * B6 + q * 12);
                 const float4 u0 = dp[0], u1 = dp[1], u2 = dp[2];
@@ -414,15 +408,15 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 }
             }
         }
-        __syncthreads();
-        TILE_STOP(1)
+        if (!a.scan) fence_async_smem();
+        __syncthreads();   // #2
         // ---- phase B: R[t] = C[t] . R[t-1] (p3d_pose.py:98-114 looped by layers/projection.py:190-193); one thread
         //      per (clip, bone, column of R), serial over the frames of the clip
         if (a.scan) {
             const int items = (np / L) * B3;
             for (int idx = tid; idx < items; idx += NT) {
                 const int c = idx / B3, rem = idx - c * B3, b = rem / 3, j = rem - b * 3;
-                const float* rr = a.ref_rot + ((long)ROW[c * L] * B + b) * 9 + j;
+                const float* rr = a.ref_rot + ((long)row[c * L] * B + b) * 9 + j;
                 float p0 = __ldg(rr), p1 = __ldg(rr + 3), p2 = __ldg(rr + 6);
                 const float* src = A + (c * L) * B9 + b * 9;
                 float* dst = R + (c * L) * B9 + b * 9 + j;
@@ -437,48 +431,45 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                     dst += B9;
                 }
             }
+            fence_async_smem();
+            __syncthreads();   // #3
         }
-        fence_async_smem();
-        __syncthreads();
-        store_out(a.rel_rot, R, m0 * B9, np * B9);
-        if (tid == 0) bulk_commit();
+        if (tma && a.rel_rot) {
+            bulk_s2g(a.rel_rot + m0 * B9, R, (uint32_t)(np * B9) * 4u);
+            bulk_commit();
+        }
 
-        TILE_STOP(2)
-        // ---- phase C: FK, level by level (p3d_pose.py:116-184): A_b = R_b . A_parent, t_b = loc_b . A_parent + t_parent
-        for (int lv = 0; lv < a.nlevels; ++lv) {
-            const int s0 = a.lvl_start[lv], cnt = a.lvl_start[lv + 1] - s0;
-            const int nt = a.slices * cnt;
-            for (int task = warp; task < nt; task += W) {
-                const int slice = task / cnt, b = a.order[s0 + task - slice * cnt], par = a.parent[b];
-                const int col = slice * 32 + lane, pl = min(col, np - 1);
-                const M3 Rb = lds9(R + pl * B9, b);
-                const float* rl = a.ref_loc + ((long)ROW[col] * B + b) * 3;
-                const V3 loc{__ldg(rl), __ldg(rl + 1), __ldg(rl + 2)};
-                M3 Ab = Rb;
-                V3 tb = loc;
-                if (par >= 0) {
-                    const M3 Ap = lds9(A + pl * B9, par);
-                    const V3 q = v3_mul_m(loc, Ap);
-                    tb = V3{q.x + TS[(par * 3) * PS + col], q.y + TS[(par * 3 + 1) * PS + col],
-                            q.z + TS[(par * 3 + 2) * PS + col]};
-                    Ab = m3_mul(Rb, Ap);
+        // ---- phase C: FK, level by level (p3d_pose.py:116-184): A_b = R_b . A_parent, t_b = loc_b . A_parent + t_parent;
+        //      only the first TW warps take part (named barrier 1 between levels)
+        if (warp < TW) {
+            for (int lv = 0; lv < a.nlevels; ++lv) {
+                const int s0 = a.lvl_start[lv], cnt = a.lvl_start[lv + 1] - s0;
+                const int nt = slices * cnt;
+                for (int task = warp; task < nt; task += TW) {
+                    const int slice = task >= cnt ? 1 : 0, b = a.order[s0 + task - slice * cnt], par = a.parent[b];
+                    const int col = slice * 32 + lane, pl = min(col, np - 1);
+                    const M3 Rb = lds9(R + pl * B9, b);
+                    const float* rl = a.ref_loc + ((long)row[col] * B + b) * 3;
+                    const V3 loc{__ldg(rl), __ldg(rl + 1), __ldg(rl + 2)};
+                    M3 Ab = Rb;
+                    V3 tb = loc;
+                    if (par >= 0) {
+                        const M3 Ap = lds9(A + pl * B9, par);
+                        const V3 q = v3_mul_m(loc, Ap);
+                        tb = V3{q.x + TS[(par * 3) * PS + col], q.y + TS[(par * 3 + 1) * PS + col],
+                                q.z + TS[(par * 3 + 2) * PS + col]};
+                        Ab = m3_mul(Rb, Ap);
+                    }
+                    if (col < np) sts9(A + pl * B9, b, Ab);
+                    TS[(b * 3) * PS + col] = tb.x;
+                    TS[(b * 3 + 1) * PS + col] = tb.y;
+                    TS[(b * 3 + 2) * PS + col] = tb.z;
                 }
-                if (col < np) sts9(A + pl * B9, b, Ab);
-                TS[(b * 3) * PS + col] = tb.x;
-                TS[(b * 3 + 1) * PS + col] = tb.y;
-                TS[(b * 3 + 2) * PS + col] = tb.z;
+                named_barrier(1, TW * 32);
             }
-            if (lv == a.nlevels - 1) fence_async_smem();
-            __syncthreads();
-        }
-        store_out(a.abs_rot, A, m0 * B9, np * B9);
-        if (tid == 0) bulk_commit();
-
-        TILE_STOP(3)
-        // ---- hips/neck shift and scale of every pose (extractor.py:23-36, hips_neck_extractor.py:6-13)
-        if (a.normalize) {
-            for (int slice = warp; slice < a.slices; slice += W) {
-                const int col = slice * 32 + lane;
+            // hips/neck shift and scale of every pose (extractor.py:23-36, hips_neck_extractor.py:6-13)
+            if (a.normalize && warp < slices) {
+                const int col = warp * 32 + lane;
                 const long m = m0 + min(col, np - 1);
                 const V3 th{TS[(a.hips * 3) * PS + col], TS[(a.hips * 3 + 1) * PS + col], TS[(a.hips * 3 + 2) * PS + col]};
                 const V3 tn{TS[(a.neck * 3) * PS + col], TS[(a.neck * 3 + 1) * PS + col], TS[(a.neck * 3 + 2) * PS + col]};
@@ -492,15 +483,21 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 NRM[4 * PS + col] = __fdividef(1.0f, scale);
                 NRM[5 * PS + col] = (scale > 0.f && scale <= 3.402823466e38f) ? 1.f : 0.f;
             }
-            __syncthreads();
+            fence_async_smem();
+        }
+        __syncthreads();   // #4
+        if (tma && a.abs_rot) {
+            bulk_s2g(a.abs_rot + m0 * B9, A, (uint32_t)(np * B9) * 4u);
+            bulk_commit();
         }
 
         // ---- projection, normaliser, loss terms, dL/d abs_loc; two bones per task; abs_loc and projection records are
         //      written over the target records they were compared with
+        while (!mbar_try_wait(bars + 1, it & 1u)) {}
         {
-            const int nt = a.slices * a.npairs;
+            const int nt = slices * npairs;
             for (int task = warp; task < nt; task += W) {
-                const int slice = task / a.npairs, q = task - slice * a.npairs;
+                const int slice = task >= npairs ? 1 : 0, q = task - slice * npairs;
                 const int col = slice * 32 + lane, pl = min(col, np - 1);
                 const bool valid = col < np;
                 const long m = m0 + pl;
@@ -540,70 +537,74 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             }
         }
         fence_async_smem();
-        if (tid == 0) bulk_wait_read_all();   // rel_rot / abs_rot stores have read R and A: A is about to take y_b
-        __syncthreads();
-        store_out(a.abs_loc, G3, m0 * B3, np * B3);
-        store_out(a.proj, G2, m0 * B3, np * B3);
-        if (tid == 0) bulk_commit();
+        if (tma) bulk_wait_read_all();   // rel_rot / abs_rot stores have read R and A: A is about to take y_b
+        __syncthreads();   // #5
+        if (tma) {
+            if (a.abs_loc) bulk_s2g(a.abs_loc + m0 * B3, G3, (uint32_t)(np * B3) * 4u);
+            if (a.proj) bulk_s2g(a.proj + m0 * B3, G2, (uint32_t)(np * B3) * 4u);
+            bulk_commit();
+            bulk_wait_read_all();
+            // the 6-D records come back (L2 hot) over the two target regions; phase E waits for them
+            mbar_expect_tx(bars + 2, (uint32_t)(np * B6) * 4u);
+            bulk_g2s(G3, a.d6 + m0 * B6, (uint32_t)(np * B6) * 4u, bars + 2);
+        }
 
-        TILE_STOP(4)
         // ---- torque backward, leaves first:  S_b = (g_b x t_b, g_b) + sum over children S_c  (in place over t_b, g_b),
         //      m_b = S_b[0:3] - S_b[3:6] x t_b,  y_b = A_parent m_b  -> words 0..2 of slot b of the A records
-        for (int lv = a.nlevels - 1; lv >= 0; --lv) {
-            const int s0 = a.lvl_start[lv], cnt = a.lvl_start[lv + 1] - s0;
-            const int nt = a.slices * cnt;
-            for (int task = warp; task < nt; task += W) {
-                const int slice = task / cnt, b = a.order[s0 + task - slice * cnt], par = a.parent[b];
-                const int col = slice * 32 + lane, pl = min(col, np - 1);
-                const V3 t{TS[(b * 3) * PS + col], TS[(b * 3 + 1) * PS + col], TS[(b * 3 + 2) * PS + col]};
-                V3 g{GV[(b * 3) * PS + col], GV[(b * 3 + 1) * PS + col], GV[(b * 3 + 2) * PS + col]};
-                if (a.normalize && (b == a.hips || b == a.neck)) {
-                    // normaliser backward through shift (hips) and scale (|neck - hips|): needs the sums over all bones
-                    float sgx = 0.f, sgy = 0.f, sgn = 0.f;
-                    for (int q = 0; q < a.npairs; ++q) {
-                        sgx += PART[(q * 3) * PS + col];
-                        sgy += PART[(q * 3 + 1) * PS + col];
-                        sgn += PART[(q * 3 + 2) * PS + col];
+        if (warp < TW) {
+            for (int lv = a.nlevels - 1; lv >= 0; --lv) {
+                const int s0 = a.lvl_start[lv], cnt = a.lvl_start[lv + 1] - s0;
+                const int nt = slices * cnt;
+                for (int task = warp; task < nt; task += TW) {
+                    const int slice = task >= cnt ? 1 : 0, b = a.order[s0 + task - slice * cnt], par = a.parent[b];
+                    const int col = slice * 32 + lane, pl = min(col, np - 1);
+                    const V3 t{TS[(b * 3) * PS + col], TS[(b * 3 + 1) * PS + col], TS[(b * 3 + 2) * PS + col]};
+                    V3 g{GV[(b * 3) * PS + col], GV[(b * 3 + 1) * PS + col], GV[(b * 3 + 2) * PS + col]};
+                    if (a.normalize && (b == a.hips || b == a.neck)) {
+                        // normaliser backward through shift (hips) and scale (|neck - hips|): sums over all bones
+                        float sgx = 0.f, sgy = 0.f, sgn = 0.f;
+                        for (int q = 0; q < npairs; ++q) {
+                            sgx += PART[(q * 3) * PS + col];
+                            sgy += PART[(q * 3 + 1) * PS + col];
+                            sgn += PART[(q * 3 + 2) * PS + col];
+                        }
+                        const float inv = NRM[5 * PS + col] != 0.f ? NRM[4 * PS + col] : 0.f;
+                        const float gs = -sgn * inv * inv;   // dL/dscale . (1/scale)
+                        const float kx = gs * NRM[2 * PS + col], ky = gs * NRM[3 * PS + col];
+                        float cx = 0.f, cy = 0.f;
+                        if (b == a.neck) { cx += kx; cy += ky; }
+                        if (b == a.hips) { cx -= fmaf(sgx, inv, kx); cy -= fmaf(sgy, inv, ky); }
+                        const long m = m0 + pl;
+                        const V3 gp = project_bwd(a, project(a, t, m), cx, cy, m);
+                        g.x += gp.x; g.y += gp.y; g.z += gp.z;
                     }
-                    const float inv = NRM[5 * PS + col] != 0.f ? NRM[4 * PS + col] : 0.f;
-                    const float gs = -sgn * inv * inv;   // dL/dscale . (1/scale)
-                    const float kx = gs * NRM[2 * PS + col], ky = gs * NRM[3 * PS + col];
-                    float cx = 0.f, cy = 0.f;
-                    if (b == a.neck) { cx += kx; cy += ky; }
-                    if (b == a.hips) { cx -= fmaf(sgx, inv, kx); cy -= fmaf(sgy, inv, ky); }
-                    const long m = m0 + pl;
-                    const V3 gp = project_bwd(a, project(a, t, m), cx, cy, m);
-                    g.x += gp.x; g.y += gp.y; g.z += gp.z;
+                    float S[6] = {g.y * t.z - g.z * t.y, g.z * t.x - g.x * t.z, g.x * t.y - g.y * t.x, g.x, g.y, g.z};
+                    for (int ci = a.child_start[b]; ci < a.child_start[b + 1]; ++ci) {
+                        const int c = a.child_list[ci];
+                        S[0] += TS[(c * 3) * PS + col]; S[1] += TS[(c * 3 + 1) * PS + col]; S[2] += TS[(c * 3 + 2) * PS + col];
+                        S[3] += GV[(c * 3) * PS + col]; S[4] += GV[(c * 3 + 1) * PS + col]; S[5] += GV[(c * 3 + 2) * PS + col];
+                    }
+                    if (par >= 0) {   // the root's sums are not read by anyone
+                        TS[(b * 3) * PS + col] = S[0]; TS[(b * 3 + 1) * PS + col] = S[1]; TS[(b * 3 + 2) * PS + col] = S[2];
+                        GV[(b * 3) * PS + col] = S[3]; GV[(b * 3 + 1) * PS + col] = S[4]; GV[(b * 3 + 2) * PS + col] = S[5];
+                    }
+                    const V3 mv{S[0] - (S[4] * t.z - S[5] * t.y), S[1] - (S[5] * t.x - S[3] * t.z),
+                                S[2] - (S[3] * t.y - S[4] * t.x)};
+                    V3 yv = mv;
+                    if (par >= 0) yv = v3_mul_mt(mv, lds9(A + pl * B9, par));
+                    if (col < np) {
+                        float* o = A + pl * B9 + b * 9;
+                        o[0] = yv.x; o[1] = yv.y; o[2] = yv.z;
+                    }
                 }
-                float S[6] = {g.y * t.z - g.z * t.y, g.z * t.x - g.x * t.z, g.x * t.y - g.y * t.x, g.x, g.y, g.z};
-                for (int ci = a.child_start[b]; ci < a.child_start[b + 1]; ++ci) {
-                    const int c = a.child_list[ci];
-                    S[0] += TS[(c * 3) * PS + col]; S[1] += TS[(c * 3 + 1) * PS + col]; S[2] += TS[(c * 3 + 2) * PS + col];
-                    S[3] += GV[(c * 3) * PS + col]; S[4] += GV[(c * 3 + 1) * PS + col]; S[5] += GV[(c * 3 + 2) * PS + col];
-                }
-                TS[(b * 3) * PS + col] = S[0]; TS[(b * 3 + 1) * PS + col] = S[1]; TS[(b * 3 + 2) * PS + col] = S[2];
-                GV[(b * 3) * PS + col] = S[3]; GV[(b * 3 + 1) * PS + col] = S[4]; GV[(b * 3 + 2) * PS + col] = S[5];
-                const V3 mv{S[0] - (S[4] * t.z - S[5] * t.y), S[1] - (S[5] * t.x - S[3] * t.z),
-                            S[2] - (S[3] * t.y - S[4] * t.x)};
-                V3 yv = mv;
-                if (par >= 0) yv = v3_mul_mt(mv, lds9(A + pl * B9, par));
-                if (col < np) {
-                    float* o = A + pl * B9 + b * 9;
-                    o[0] = yv.x; o[1] = yv.y; o[2] = yv.z;
-                }
+                if (lv > 0) named_barrier(1, TW * 32);
             }
-            if (lv == 0) fence_async_smem();
-            __syncthreads();
+            fence_async_smem();   // the scratch rows are about to be overwritten by the next tile's 6-D records (TMA)
         }
-        TILE_STOP(5)
-        // the 6-D records come back (L2 hot) into the region that served as scratch; phase E waits for them
-        if (bulk) {
-            if (tid == 0) {
-                mbar_expect_tx(bars + 1, (uint32_t)(np * B6) * 4u);
-                bulk_g2s(D, a.d6 + m0 * B6, (uint32_t)(np * B6) * 4u, bars + 1);
-            }
-        } else {
-            for (int i = tid; i < np * B6; i += NT) D[i] = __ldg(a.d6 + m0 * B6 + i);
+        __syncthreads();   // #6
+        if (nxt < ntiles) {   // the D region and the other row buffer are free: prefetch for the next tile
+            if (tma) load_d6(nxt);
+            if (warp == W - 1) fill_rows(nxt, (it + 1) & 1);
         }
         // ---- phase D: z[t] = sum_{s >= t} y[s] per clip (the reverse-time scan in tangent form is a suffix sum)
         if (a.scan) {
@@ -620,19 +621,15 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 }
             }
         }
-        if (bulk) {
-            while (!mbar_try_wait(bars + 1, use1 & 1u)) {}
-            ++use1;
-        }
-        __syncthreads();
-        TILE_STOP(6)
+        while (!mbar_try_wait(bars + 2, it & 1u)) {}
+        __syncthreads();   // #7
         // ---- phase E: omega[t] = R[t] z[t]; tangent-form Gram-Schmidt backward -> gradient records over the 6-D records
         {
-            const int nt = a.slices * a.npairs;
+            const int nt = slices * npairs;
             for (int task = warp; task < nt; task += W) {
-                const int slice = task / a.npairs, q = task - slice * a.npairs;
+                const int slice = task >= npairs ? 1 : 0, q = task - slice * npairs;
                 const int col = slice * 32 + lane, pl = min(col, np - 1);
-                float4* dp = reinterpret_cast<float4*>(D + pl * B6 + q * 12);
+                float4* dp = reinterpret_cast<float4*>(G3 + pl * B6 + q * 12);
                 const float4 u0 = dp[0], u1 = dp[1], u2 = dp[2];
                 const float d[12] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w, u2.x, u2.y, u2.z, u2.w};
                 const float2* rp = reinterpret_cast<const float2*>(R + pl * B9 + q * 18);
@@ -659,15 +656,15 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             }
         }
         fence_async_smem();
-        __syncthreads();
-        store_out(a.g_d6, D, m0 * B6, np * B6);
-        if (tid == 0) {
+        __syncthreads();   // #8
+        if (tma) {
+            bulk_s2g(a.g_d6 + m0 * B6, G3, (uint32_t)(np * B6) * 4u);
             bulk_commit();
-            bulk_wait_read_all();   // every store of this tile has read its region: the next tile may overwrite them
+            bulk_wait_read_all();   // the gradient has left the target regions: the next tile's targets may land
+            if (nxt < ntiles) load_targets(nxt);
         }
-        __syncthreads();
     }
-    if (tid == 0) bulk_wait_all();
+    if (tma) bulk_wait_all();
 
     // ---- loss sums: fixed-order reduction, the last CTA to finish folds the per-CTA partials
     s2 = warp_sum(s2);
@@ -743,6 +740,9 @@ bool tree_tables(const p2c_tree_t& t, TileArgs& a) {
             if (level[b] == l) a.order[n++] = (int8_t)b;
     }
     a.lvl_start[maxl + 1] = (int8_t)n;
+    a.tree_warps = 1;   // widest level (x slices, set by the launcher)
+    for (int l = 0; l <= maxl; ++l)
+        if (a.lvl_start[l + 1] - a.lvl_start[l] > a.tree_warps) a.tree_warps = a.lvl_start[l + 1] - a.lvl_start[l];
     n = 0;
     for (int b = 0; b < B; ++b) {
         a.parent[b] = (int8_t)t.parent[b];
@@ -772,6 +772,13 @@ TileLaunch make_launch(const p2c_fused_step_t* p) {
         t.P = 32;
     }
     if ((long)t.P > total) t.P = (int)total;
+    // every tile moves by TMA: 16-byte aligned records on both sides => even pose counts per tile (B*3 floats per
+    // pose record is an even, not a multiple-of-four, count) and 16-byte aligned tensors; anything else takes the
+    // bone-per-lane kernels of fused_fast.cu, which also copy cooperatively
+    if ((t.P & 1) || (total & 1)) return t;
+    const void* ptrs[] = {p->pose_in, p->gt_2d, p->gt_3d, p->g_pose_in, p->rel_rot, p->abs_rot, p->abs_loc, p->proj};
+    for (const void* q : ptrs)
+        if (reinterpret_cast<uintptr_t>(q) & 15) return t;
     t.PS = (t.P + 31) & ~31;
     t.slices = t.PS / 32;
     t.smem = (size_t)tile_plan(t.PS, B, B / 2).total * sizeof(float);
@@ -821,8 +828,9 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     if (!t.ok) return P2C_E_UNSUPPORTED;
     const int B = p->tree.n_bones;
     a.N = p->n_clips; a.L = p->clip_len; a.P = t.P; a.PS = t.PS; a.slices = t.slices;
+    a.tree_warps *= t.slices;
+    if (a.tree_warps > t.threads / 32) a.tree_warps = t.threads / 32;
     a.scan = p->mode == P2C_MODE_POSE_CHANGES;
-    a.stop = getenv("P2C_TILE_STOP") ? atoi(getenv("P2C_TILE_STOP")) : 99;
     a.hips = p->hips; a.neck = p->neck; a.normalize = p->normalize; a.mask = p->mask_missing_joints;
     a.d6 = p->pose_in; a.ref_loc = p->ref_loc; a.ref_rot = p->ref_rot; a.ref_index = p->ref_index;
     a.world_loc = p->world_loc; a.world_rot = p->world_rot; a.cam = p->camera;
@@ -842,13 +850,16 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
         tile_count_kernel<<<(int)blocks, 256, 0, st>>>(p->gt_2d, total, B, p->gt_2d_channels, p->hips, a.count2);
         P2C_LAUNCH_CHECK();
     }
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
+    typedef void (*kern_t)(const TileArgs);
+    const int ki = B == 26 ? (t.slices == 1 ? 0 : 1) : 2;   // CARLA_SKELETON gets compile-time bone and slice counts
+    const kern_t k = ki == 0 ? tile_kernel<26, 1> : ki == 1 ? tile_kernel<26, 2> : tile_kernel<0, 0>;
+    static bool configured[3] = {false, false, false};
+    if (!configured[ki]) {
+        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
         if (e != cudaSuccess) return (int)e;
-        configured = true;
+        configured[ki] = true;
     }
-    tile_kernel<<<t.grid, t.threads, t.smem, st>>>(a);
+    k<<<t.grid, t.threads, t.smem, st>>>(a);
     P2C_LAUNCH_CHECK();
     return 0;
 }
