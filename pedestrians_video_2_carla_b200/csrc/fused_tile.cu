@@ -44,6 +44,8 @@ struct TileArgs {
     int N, L, B, P, PS, slices, scan;   // clips, frames per clip, bones, poses per tile, P rounded up to 32, PS/32
     int hips, neck, normalize, mask, nlevels, npairs;
     int tree_warps;   // warps that take part in the level-synchronous tree phases
+    int count_inline; // every CTA owns exactly one tile: the mask count happens inside the kernel (no pre-pass)
+    int clocks;       // debug (P2C_TILE_CLOCKS=1): CTA 0 records clock64() at every phase boundary of its second tile
     int8_t parent[P2C_MAX_BONES];
     int8_t order[P2C_MAX_BONES];          // bones sorted by tree level
     int8_t lvl_start[MAX_LEVELS + 1];     // order[lvl_start[l] .. lvl_start[l+1]) = bones of level l
@@ -68,9 +70,28 @@ struct TileArgs {
     float* partials;       // gridDim.x x 2
     unsigned int* ticket;  // self-resetting
     int* count2;           // self-resetting, filled by count_kernel when mask is on
+    unsigned int* arrive;  // self-resetting: CTAs that have added their part of count2 (count_inline)
     float* losses;
     double count3;
 };
+
+// MUFU approximations (rel. error ~2^-22, well inside the 1e-4 parity bar); ftz only touches denormals, which the
+// clamps below keep out of rsqrt and which make no difference to 1/z or the hips-neck scale
+__device__ __forceinline__ float frcp(float x) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float frsqrt(float x) {
+    float r;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+__device__ __forceinline__ float fsqrt(float x) {
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
 
 struct GS {
     V3 b1, b2, b3;
@@ -87,11 +108,11 @@ __device__ __forceinline__ GS gram_schmidt(const float* a) {
     GS r;
     const V3 a1{a[0], a[1], a[2]};
     const V3 a2{a[3], a[4], a[5]};
-    r.inv1 = rsqrtf(fmaxf(dot3(a1, a1), 1e-24f));
+    r.inv1 = frsqrt(fmaxf(dot3(a1, a1), 1e-24f));
     r.b1 = V3{a1.x * r.inv1, a1.y * r.inv1, a1.z * r.inv1};
     r.s = dot3(r.b1, a2);
     const V3 u{fmaf(-r.s, r.b1.x, a2.x), fmaf(-r.s, r.b1.y, a2.y), fmaf(-r.s, r.b1.z, a2.z)};
-    r.inv2 = rsqrtf(fmaxf(dot3(u, u), 1e-24f));
+    r.inv2 = frsqrt(fmaxf(dot3(u, u), 1e-24f));
     r.b2 = V3{u.x * r.inv2, u.y * r.inv2, u.z * r.inv2};
     r.b3 = cross3(r.b1, r.b2);
     return r;
@@ -206,9 +227,9 @@ __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.a
 
 // shared-memory plan (floats); every region starts 16-byte aligned (PS is a multiple of 32)
 struct TilePlan {
-    int d, g3, g2, r, a, nrm, part, row, red, bars, total;
+    int d, g3, g2, r, a, nrm, part, row, red, bars, desc, child, total;
 };
-__device__ __host__ __forceinline__ TilePlan tile_plan(int PS, int B, int npairs) {
+__device__ __host__ __forceinline__ TilePlan tile_plan(int PS, int B, int ndesc) {
     TilePlan s;
     int o = 0;
     s.d = o; o += PS * B * 6;
@@ -217,10 +238,12 @@ __device__ __host__ __forceinline__ TilePlan tile_plan(int PS, int B, int npairs
     s.r = o; o += PS * B * 9;
     s.a = o; o += PS * B * 9;
     s.nrm = o; o += 8 * PS;            // sx, sy, dx, dy, inv, ok per pose
-    s.part = o; o += npairs * 3 * PS;  // per bone pair: sum gx, sum gy, sum (gx x + gy y) per pose
+    s.part = o; o += B * 3 * PS;       // per bone: gx, gy, gx x + gy y per pose (normaliser backward)
     s.row = o; o += 2 * PS;            // skeleton-table row per pose, double buffered (next tile's rows prefetched)
     s.red = o; o += 2 * 32;            // loss partials per warp
     s.bars = o; o += 8;                // three 8-byte mbarriers
+    s.desc = o; o += 4 * ndesc;        // int4 task descriptor per (tree level, tree warp)
+    s.child = o; o += P2C_MAX_BONES;   // child lists
     s.total = o;
     return s;
 }
@@ -237,29 +260,31 @@ __device__ __forceinline__ M3 ldg9(const float* g) {
     return r;
 }
 // p3d_pose_projection.py:137-152
+template <bool WORLD>
 __device__ __forceinline__ Proj project(const TileArgs& a, const V3& t, long m) {
     Proj r;
     V3 wp{t.y, -t.x, t.z};
-    if (a.world_rot) wp = v3_mul_m(wp, ldg9(a.world_rot + m * 9));
-    if (a.world_loc) {
+    if (WORLD && a.world_rot) wp = v3_mul_m(wp, ldg9(a.world_rot + m * 9));
+    if (WORLD && a.world_loc) {
         wp.x += __ldg(a.world_loc + m * 3); wp.y += __ldg(a.world_loc + m * 3 + 1); wp.z += __ldg(a.world_loc + m * 3 + 2);
     }
     const float* cr = a.cam.R;
     r.c.x = fmaf(wp.z, cr[6], fmaf(wp.y, cr[3], wp.x * cr[0])) + a.cam.T[0];
     r.c.y = fmaf(wp.z, cr[7], fmaf(wp.y, cr[4], wp.x * cr[1])) + a.cam.T[1];
     r.c.z = fmaf(wp.z, cr[8], fmaf(wp.y, cr[5], wp.x * cr[2])) + a.cam.T[2];
-    r.iz = __fdividef(1.0f, r.c.z);
+    r.iz = frcp(r.c.z);
     r.p = V3{fmaf(-a.cam.f * r.c.x, r.iz, a.cam.px), fmaf(-a.cam.f * r.c.y, r.iz, a.cam.py), r.iz};
     return r;
 }
 // pixel-space gradient (gx, gy) -> gradient wrt the p3d-space point
+template <bool WORLD>
 __device__ __forceinline__ V3 project_bwd(const TileArgs& a, const Proj& r, float gx, float gy, long m) {
     const float fgx = a.cam.f * gx * r.iz, fgy = a.cam.f * gy * r.iz;
     const V3 gc{-fgx, -fgy, fmaf(fgx, r.c.x, fgy * r.c.y) * r.iz};
     const float* cr = a.cam.R;
     V3 gw{fmaf(gc.z, cr[2], fmaf(gc.y, cr[1], gc.x * cr[0])), fmaf(gc.z, cr[5], fmaf(gc.y, cr[4], gc.x * cr[3])),
           fmaf(gc.z, cr[8], fmaf(gc.y, cr[7], gc.x * cr[6]))};
-    if (a.world_rot) gw = v3_mul_mt(gw, ldg9(a.world_rot + m * 9));
+    if (WORLD && a.world_rot) gw = v3_mul_mt(gw, ldg9(a.world_rot + m * 9));
     return V3{-gw.y, gw.x, gw.z};
 }
 
@@ -272,9 +297,10 @@ struct LossCtx {   // per-lane state of one element-wise task
 
 // one bone of one pose: projection, normaliser, loc_2d / loc_3d terms, dL/d abs_loc (without the hips/neck terms of
 // the normaliser backward, which the torque pass adds).  Returns the projection record through `pout`.
+template <bool WORLD>
 __device__ __forceinline__ V3 bone_loss(const TileArgs& a, int b, const V3& t, float g2x, float g2y, const V3& g3, long m,
                                         bool valid, LossCtx& cx, V3& pout, V3& nout) {
-    const Proj pr = project(a, t, m);
+    const Proj pr = project<WORLD>(a, t, m);
     pout = pr.p;
     float x = pr.p.x, y = pr.p.y;
     bool lx = true, ly = true;
@@ -307,22 +333,82 @@ __device__ __forceinline__ V3 bone_loss(const TileArgs& a, int b, const V3& t, f
     }
     const V3 e{t.x - g3.x, t.y - g3.y, t.z - g3.z};
     if (valid) cx.s3 = fmaf(e.x, e.x, fmaf(e.y, e.y, fmaf(e.z, e.z, cx.s3)));
-    const V3 gp = project_bwd(a, pr, gx, gy, m);
+    const V3 gp = project_bwd<WORLD>(a, pr, gx, gy, m);
     return V3{fmaf(cx.k3, e.x, gp.x), fmaf(cx.k3, e.y, gp.y), fmaf(cx.k3, e.z, gp.z)};
 }
+
+__device__ long long g_tile_clocks[64];
+#define TILE_CLOCK(k)                                                              \
+    if (a.clocks && blockIdx.x == 0 && it == 1 && tid == 0) g_tile_clocks[k] = clock64();
 
 __device__ __forceinline__ void named_barrier(int id, int threads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
+__device__ __forceinline__ float4 lds128(const float* p) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "r"(smem_u32(p))
+                 : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts128(float* p, float x, float y, float z, float w) {
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(p)), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
+}
+// 6-word bone record b of a 16-byte aligned AoS pose record (6-D / gradient records): 128 + 64 bits, order by parity
+__device__ __forceinline__ void lds6(const float* pose, int b, float* d) {
+    const float* p = pose + 6 * b;
+    if (b & 1) {
+        const float2 u = lds64(p);
+        const float4 v = lds128(p + 2);
+        d[0] = u.x; d[1] = u.y; d[2] = v.x; d[3] = v.y; d[4] = v.z; d[5] = v.w;
+    } else {
+        const float4 v = lds128(p);
+        const float2 u = lds64(p + 4);
+        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w; d[4] = u.x; d[5] = u.y;
+    }
+}
+__device__ __forceinline__ void sts6(float* pose, int b, const float* d) {
+    float* p = pose + 6 * b;
+    if (b & 1) {
+        sts64(p, d[0], d[1]);
+        sts128(p + 2, d[2], d[3], d[4], d[5]);
+    } else {
+        sts128(p, d[0], d[1], d[2], d[3]);
+        sts64(p + 4, d[4], d[5]);
+    }
+}
+// 3-word bone record b of an 8-byte aligned AoS pose record (locations, projections, 3-channel targets)
+__device__ __forceinline__ V3 lds3(const float* pose, int b) {
+    const float* p = pose + 3 * b;
+    if (b & 1) {
+        const float x = p[0];
+        const float2 u = lds64(p + 1);
+        return V3{x, u.x, u.y};
+    }
+    const float2 u = lds64(p);
+    return V3{u.x, u.y, p[2]};
+}
+__device__ __forceinline__ void sts3(float* pose, int b, const V3& v) {
+    float* p = pose + 3 * b;
+    if (b & 1) {
+        p[0] = v.x;
+        sts64(p + 1, v.y, v.z);
+    } else {
+        sts64(p, v.x, v.y);
+        p[2] = v.z;
+    }
+}
 
-// BT / SL: bones and 32-pose slices per tile at compile time (0 = read from the arguments)
-template <int BT, int SL>
+// BT / SL: bones and 32-pose slices per tile at compile time (0 = read from the arguments); WORLD: a per-frame world
+// transform may be given (ZeroTrajectory, the only trajectory model of the reference, gives none)
+template <int BT, int SL, bool WORLD>
 __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) {
     extern __shared__ __align__(16) float smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NT = blockDim.x, W = NT >> 5;
-    const int B = BT ? BT : a.B, slices = SL ? SL : a.slices, npairs = B / 2;
+    const int B = BT ? BT : a.B, slices = SL ? SL : a.slices;
     const int B3 = B * 3, B6 = B * 6, B9 = B * 9, PS = 32 * slices, L = a.L;
-    const TilePlan sm = tile_plan(PS, B, npairs);
+    const TilePlan sm = tile_plan(PS, B, a.nlevels * a.tree_warps);
     float* D = smem + sm.d;
     float* G3 = smem + sm.g3;     // G3 and G2 are adjacent: together they hold the re-fetched 6-D records
     float* G2 = smem + sm.g2;
@@ -333,32 +419,34 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     int* ROW = reinterpret_cast<int*>(smem + sm.row);   // two buffers of PS
     float* red = smem + sm.red;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + sm.bars);   // [0] 6-D in, [1] targets in, [2] 6-D again
+    int4* DESC = reinterpret_cast<int4*>(smem + sm.desc);
+    int* CHILD = reinterpret_cast<int*>(smem + sm.child);
     float* TS = D;               // SoA scratch rows [0, 3B): t_b, later subtree sums of g x t
     float* GV = D + B3 * PS;     // SoA scratch rows [3B, 6B): g_b, later subtree sums of g
     const bool tma = tid == (W - 1) * 32;   // the thread that issues every bulk copy (a warp without tree work)
     const int TW = a.tree_warps;            // warps that walk the tree; the others skip to the next CTA barrier
-    const long total = (long)a.N * L;
-    const long ntiles = (total + a.P - 1) / a.P;
+    const int total = a.N * L;              // (the launcher keeps N*L*B*9 below 2^31 elements... offsets are size_t)
+    const int ntiles = (total + a.P - 1) / a.P;
 
-    auto load_d6 = [&](long tile) {
-        const long m0 = tile * a.P;
-        const uint32_t bytes = (uint32_t)((int)min((long)a.P, total - m0) * B6) * 4u;
+    auto load_d6 = [&](int tile) {
+        const int m0 = tile * a.P;
+        const uint32_t bytes = (uint32_t)(min(a.P, total - m0) * B6) * 4u;
         mbar_expect_tx(bars, bytes);
-        bulk_g2s(D, a.d6 + m0 * B6, bytes, bars);
+        bulk_g2s(D, a.d6 + (size_t)m0 * B6, bytes, bars);
     };
-    auto load_targets = [&](long tile) {
-        const long m0 = tile * a.P;
-        const uint32_t bytes = (uint32_t)((int)min((long)a.P, total - m0) * B3) * 4u;
+    auto load_targets = [&](int tile) {
+        const int m0 = tile * a.P;
+        const uint32_t bytes = (uint32_t)(min(a.P, total - m0) * B3) * 4u;
         mbar_expect_tx(bars + 1, 2u * bytes);
-        bulk_g2s(G3, a.gt3 + m0 * B3, bytes, bars + 1);
-        bulk_g2s(G2, a.gt2 + m0 * B3, bytes, bars + 1);
+        bulk_g2s(G3, a.gt3 + (size_t)m0 * B3, bytes, bars + 1);
+        bulk_g2s(G2, a.gt2 + (size_t)m0 * B3, bytes, bars + 1);
     };
-    auto fill_rows = [&](long tile, int buf) {   // skeleton-table row of every pose (lanes past the tile repeat its last)
-        const long m0 = tile * a.P;
-        const int np = (int)min((long)a.P, total - m0);
+    auto fill_rows = [&](int tile, int buf) {   // skeleton-table row of every pose (lanes past the tile repeat its last)
+        const int m0 = tile * a.P;
+        const int np = min(a.P, total - m0);
         for (int i = lane; i < PS; i += 32) {
-            const long clip = (m0 + min(i, np - 1)) / L;
-            ROW[buf * PS + i] = a.ref_index ? __ldg(a.ref_index + clip) : (int)clip;
+            const int clip = (m0 + min(i, np - 1)) / L;
+            ROW[buf * PS + i] = a.ref_index ? __ldg(a.ref_index + clip) : clip;
         }
     };
 
@@ -367,140 +455,219 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         mbar_init(bars + 1, 1);
         mbar_init(bars + 2, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        if ((long)blockIdx.x < ntiles) {
+        if ((int)blockIdx.x < ntiles) {
             load_d6(blockIdx.x);
             load_targets(blockIdx.x);
         }
     }
-    if (warp == 0 && (long)blockIdx.x < ntiles) fill_rows(blockIdx.x, 0);
+    if (warp == 0 && (int)blockIdx.x < ntiles) fill_rows(blockIdx.x, 0);
+    // task of every (tree level, tree warp): {bone or -1, parent, slice, child_begin | child_end << 8}; one task per
+    // warp and level (the launcher sizes TW to the widest level), so the level loops below need no table walks
+    for (int i = tid; i < a.nlevels * TW; i += NT) {
+        const int lv = i / TW, w = i - lv * TW;
+        const int s0 = a.lvl_start[lv], cnt = a.lvl_start[lv + 1] - s0;
+        int4 d = make_int4(-1, -1, 0, 0);
+        if (w < slices * cnt) {
+            d.z = w >= cnt ? 1 : 0;
+            d.x = a.order[s0 + w - d.z * cnt];
+            d.y = a.parent[d.x];
+            d.w = a.child_start[d.x] | (a.child_start[d.x + 1] << 8);
+        }
+        DESC[i] = d;
+    }
+    if (tid < B) CHILD[tid] = a.child_list[tid];
     __syncthreads();
 
-    const float k2 = a.w2 * 2.0f / (a.mask ? (float)__ldcg(a.count2) : (float)(total * B * 2));
+    float k2 = a.w2 * 2.0f / ((a.mask && !a.count_inline) ? (float)__ldcg(a.count2) : (float)total * (float)(B * 2));
+    __shared__ int cta_count;
+    __shared__ float k2_shared;
+    if (a.mask && a.count_inline) {
+        // utils/tensors.py:29-40: kept (joint, channel) pairs of this CTA's only tile, summed over the grid through
+        // one integer atomic per CTA (order independent); the loss pass waits for every CTA's part
+        if (tid == 0) cta_count = 0;
+        while (!mbar_try_wait(bars + 1, 0u)) {}
+        __syncthreads();
+        const int np0 = min(a.P, total - (int)blockIdx.x * a.P);
+        int c = 0;
+        for (int i = tid; i < np0 * B; i += NT) {
+            const int j = i % B;
+            const float* g = G2 + i * 3;
+            if (j == a.hips || (g[0] != 0.f && g[1] != 0.f)) c += 2;
+        }
+        c = __reduce_add_sync(FULL_MASK, c);
+        if (lane == 0 && c) atomicAdd(&cta_count, c);
+        __syncthreads();
+        if (tid == 0) {
+            if (cta_count) atomicAdd(a.count2, cta_count);
+            __threadfence();
+            atomicAdd(a.arrive, 1u);
+        }
+    }
     const float k3 = a.w3 * 2.0f / (float)a.count3;
     float s2 = 0.f, s3 = 0.f;
     unsigned it = 0;
 
-    for (long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-        const long m0 = tile * a.P, nxt = tile + gridDim.x;
-        const int np = (int)min((long)a.P, total - m0);
+    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
+        const int m0 = tile * a.P, nxt = tile + gridDim.x;
+        const int np = min(a.P, total - m0);
         const int* row = ROW + (it & 1) * PS;
+        TILE_CLOCK(0)
         while (!mbar_try_wait(bars, it & 1u)) {}
+        TILE_CLOCK(1)
         __syncthreads();   // #1 (first tile: the row table; later tiles: ordered by the barriers of the previous tile)
 
-        // ---- phase A: 6-D -> C[t] (rotation_6d_to_matrix), two bones per task
+        TILE_CLOCK(2)
+        // ---- phase A: 6-D -> C[t] (rotation_6d_to_matrix), one bone per task
         {
             float* dst = a.scan ? A : R;
-            const int nt = slices * npairs;
+            const int nt = slices * B;
+#pragma unroll 1
             for (int task = warp; task < nt; task += W) {
-                const int slice = task >= npairs ? 1 : 0, q = task - slice * npairs;
+                const int slice = task >= B ? 1 : 0, b = task - slice * B;
                 const int col = slice * 32 + lane, pl = min(col, np - 1);
-                const float4* dp = reinterpret_cast<const float4*>(D + pl * B6 + q * 12);
-                const float4 u0 = dp[0], u1 = dp[1], u2 = dp[2];
-                const float d[12] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w, u2.x, u2.y, u2.z, u2.w};
-                const GS r0 = gram_schmidt(d), r1 = gram_schmidt(d + 6);
-                if (col < np) {
-                    float2* o = reinterpret_cast<float2*>(dst + pl * B9 + q * 18);
-                    o[0] = make_float2(r0.b1.x, r0.b1.y); o[1] = make_float2(r0.b1.z, r0.b2.x);
-                    o[2] = make_float2(r0.b2.y, r0.b2.z); o[3] = make_float2(r0.b3.x, r0.b3.y);
-                    o[4] = make_float2(r0.b3.z, r1.b1.x); o[5] = make_float2(r1.b1.y, r1.b1.z);
-                    o[6] = make_float2(r1.b2.x, r1.b2.y); o[7] = make_float2(r1.b2.z, r1.b3.x);
-                    o[8] = make_float2(r1.b3.y, r1.b3.z);
-                }
+                float d[6];
+                lds6(D + pl * B6, b, d);
+                const GS r = gram_schmidt(d);
+                M3 C;
+                C.m[0] = r.b1.x; C.m[1] = r.b1.y; C.m[2] = r.b1.z;
+                C.m[3] = r.b2.x; C.m[4] = r.b2.y; C.m[5] = r.b2.z;
+                C.m[6] = r.b3.x; C.m[7] = r.b3.y; C.m[8] = r.b3.z;
+                if (col < np) sts9(dst + pl * B9, b, C);
             }
         }
         if (!a.scan) fence_async_smem();
         __syncthreads();   // #2
+        TILE_CLOCK(3)
         // ---- phase B: R[t] = C[t] . R[t-1] (p3d_pose.py:98-114 looped by layers/projection.py:190-193); one thread
         //      per (clip, bone, column of R), serial over the frames of the clip
         if (a.scan) {
             const int items = (np / L) * B3;
+#pragma unroll 1
             for (int idx = tid; idx < items; idx += NT) {
-                const int c = idx / B3, rem = idx - c * B3, b = rem / 3, j = rem - b * 3;
-                const float* rr = a.ref_rot + ((long)row[c * L] * B + b) * 9 + j;
+                const int cl = idx / B3, rem = idx - cl * B3, b = rem / 3, j = rem - b * 3;
+                const float* rr = a.ref_rot + ((size_t)row[cl * L] * B + b) * 9 + j;
                 float p0 = __ldg(rr), p1 = __ldg(rr + 3), p2 = __ldg(rr + 6);
-                const float* src = A + (c * L) * B9 + b * 9;
-                float* dst = R + (c * L) * B9 + b * 9 + j;
-#pragma unroll 4
-                for (int f = 0; f < L; ++f) {
-                    const float n0 = fmaf(src[2], p2, fmaf(src[1], p1, src[0] * p0));
-                    const float n1 = fmaf(src[5], p2, fmaf(src[4], p1, src[3] * p0));
-                    const float n2 = fmaf(src[8], p2, fmaf(src[7], p1, src[6] * p0));
+                const float* src = A + (cl * L) * B9 + b * 9;
+                float* dst = R + (cl * L) * B9 + b * 9 + j;
+                // two frames per trip; the records of the next two frames are in flight while these products run
+                float c[9], e[9];
+#pragma unroll
+                for (int i = 0; i < 9; ++i) c[i] = src[i];
+                int f = 0;
+#pragma unroll 1
+                for (; f + 2 <= L; f += 2) {
+#pragma unroll
+                    for (int i = 0; i < 9; ++i) e[i] = src[B9 + i];
+                    const float n0 = fmaf(c[2], p2, fmaf(c[1], p1, c[0] * p0));
+                    const float n1 = fmaf(c[5], p2, fmaf(c[4], p1, c[3] * p0));
+                    const float n2 = fmaf(c[8], p2, fmaf(c[7], p1, c[6] * p0));
                     dst[0] = n0; dst[3] = n1; dst[6] = n2;
-                    p0 = n0; p1 = n1; p2 = n2;
-                    src += B9;
-                    dst += B9;
+                    src += 2 * B9;
+                    if (f + 2 < L) {
+#pragma unroll
+                        for (int i = 0; i < 9; ++i) c[i] = src[i];
+                    }
+                    p0 = fmaf(e[2], n2, fmaf(e[1], n1, e[0] * n0));
+                    p1 = fmaf(e[5], n2, fmaf(e[4], n1, e[3] * n0));
+                    p2 = fmaf(e[8], n2, fmaf(e[7], n1, e[6] * n0));
+                    dst[B9] = p0; dst[B9 + 3] = p1; dst[B9 + 6] = p2;
+                    dst += 2 * B9;
+                }
+                if (f < L) {   // odd clip length: the last frame
+                    dst[0] = fmaf(c[2], p2, fmaf(c[1], p1, c[0] * p0));
+                    dst[3] = fmaf(c[5], p2, fmaf(c[4], p1, c[3] * p0));
+                    dst[6] = fmaf(c[8], p2, fmaf(c[7], p1, c[6] * p0));
                 }
             }
             fence_async_smem();
             __syncthreads();   // #3
+            TILE_CLOCK(4)
         }
         if (tma && a.rel_rot) {
-            bulk_s2g(a.rel_rot + m0 * B9, R, (uint32_t)(np * B9) * 4u);
+            bulk_s2g(a.rel_rot + (size_t)m0 * B9, R, (uint32_t)(np * B9) * 4u);
             bulk_commit();
         }
 
         // ---- phase C: FK, level by level (p3d_pose.py:116-184): A_b = R_b . A_parent, t_b = loc_b . A_parent + t_parent;
-        //      only the first TW warps take part (named barrier 1 between levels)
+        //      only the first TW warps take part (named barrier 1 between levels).  The task descriptor and the bone
+        //      offset of level lv+1 are fetched BEFORE the barrier that ends level lv.
         if (warp < TW) {
+            int4 d = DESC[warp];
+            int col = d.z * 32 + lane;
+            const float* rl = a.ref_loc + ((size_t)row[col] * B + max(d.x, 0)) * 3;
+            V3 loc{__ldg(rl), __ldg(rl + 1), __ldg(rl + 2)};
+#pragma unroll 1
             for (int lv = 0; lv < a.nlevels; ++lv) {
-                const int s0 = a.lvl_start[lv], cnt = a.lvl_start[lv + 1] - s0;
-                const int nt = slices * cnt;
-                for (int task = warp; task < nt; task += TW) {
-                    const int slice = task >= cnt ? 1 : 0, b = a.order[s0 + task - slice * cnt], par = a.parent[b];
-                    const int col = slice * 32 + lane, pl = min(col, np - 1);
-                    const M3 Rb = lds9(R + pl * B9, b);
-                    const float* rl = a.ref_loc + ((long)row[col] * B + b) * 3;
-                    const V3 loc{__ldg(rl), __ldg(rl + 1), __ldg(rl + 2)};
-                    M3 Ab = Rb;
+                if (d.x >= 0) {
+                    const int b = d.x, par = d.y, pl = min(col, np - 1);
+                    M3 Ab = lds9(R + pl * B9, b);
                     V3 tb = loc;
                     if (par >= 0) {
                         const M3 Ap = lds9(A + pl * B9, par);
                         const V3 q = v3_mul_m(loc, Ap);
                         tb = V3{q.x + TS[(par * 3) * PS + col], q.y + TS[(par * 3 + 1) * PS + col],
                                 q.z + TS[(par * 3 + 2) * PS + col]};
-                        Ab = m3_mul(Rb, Ap);
+                        Ab = m3_mul(Ab, Ap);
                     }
                     if (col < np) sts9(A + pl * B9, b, Ab);
                     TS[(b * 3) * PS + col] = tb.x;
                     TS[(b * 3 + 1) * PS + col] = tb.y;
                     TS[(b * 3 + 2) * PS + col] = tb.z;
                 }
+                TILE_CLOCK(16 + 3 * lv)
+                if (lv + 1 < a.nlevels) {
+                    d = DESC[(lv + 1) * TW + warp];
+                    col = d.z * 32 + lane;
+                    rl = a.ref_loc + ((size_t)row[col] * B + max(d.x, 0)) * 3;
+                    loc = V3{__ldg(rl), __ldg(rl + 1), __ldg(rl + 2)};
+                }
+                TILE_CLOCK(17 + 3 * lv)
                 named_barrier(1, TW * 32);
+                TILE_CLOCK(18 + 3 * lv)
             }
             // hips/neck shift and scale of every pose (extractor.py:23-36, hips_neck_extractor.py:6-13)
             if (a.normalize && warp < slices) {
-                const int col = warp * 32 + lane;
-                const long m = m0 + min(col, np - 1);
+                col = warp * 32 + lane;
+                const int m = m0 + min(col, np - 1);
                 const V3 th{TS[(a.hips * 3) * PS + col], TS[(a.hips * 3 + 1) * PS + col], TS[(a.hips * 3 + 2) * PS + col]};
                 const V3 tn{TS[(a.neck * 3) * PS + col], TS[(a.neck * 3 + 1) * PS + col], TS[(a.neck * 3 + 2) * PS + col]};
-                const Proj ph = project(a, th, m), pn = project(a, tn, m);
+                const Proj ph = project<WORLD>(a, th, m), pn = project<WORLD>(a, tn, m);
                 const float dx = pn.p.x - ph.p.x, dy = pn.p.y - ph.p.y;
-                const float scale = sqrtf(fmaf(dx, dx, dy * dy));
+                const float scale = fsqrt(fmaf(dx, dx, dy * dy));
                 NRM[col] = ph.p.x;
                 NRM[PS + col] = ph.p.y;
                 NRM[2 * PS + col] = dx;
                 NRM[3 * PS + col] = dy;
-                NRM[4 * PS + col] = __fdividef(1.0f, scale);
+                NRM[4 * PS + col] = frcp(scale);
                 NRM[5 * PS + col] = (scale > 0.f && scale <= 3.402823466e38f) ? 1.f : 0.f;
             }
             fence_async_smem();
         }
+        if (a.mask && a.count_inline && tid == 0) {
+            while (*reinterpret_cast<volatile unsigned int*>(a.arrive) < gridDim.x) {}
+            __threadfence();
+            k2_shared = a.w2 * 2.0f / (float)__ldcg(a.count2);
+        }
         __syncthreads();   // #4
+        if (a.mask && a.count_inline) k2 = k2_shared;
+        TILE_CLOCK(5)
         if (tma && a.abs_rot) {
-            bulk_s2g(a.abs_rot + m0 * B9, A, (uint32_t)(np * B9) * 4u);
+            bulk_s2g(a.abs_rot + (size_t)m0 * B9, A, (uint32_t)(np * B9) * 4u);
             bulk_commit();
         }
 
-        // ---- projection, normaliser, loss terms, dL/d abs_loc; two bones per task; abs_loc and projection records are
+        // ---- projection, normaliser, loss terms, dL/d abs_loc; one bone per task; abs_loc and projection records are
         //      written over the target records they were compared with
         while (!mbar_try_wait(bars + 1, it & 1u)) {}
+        TILE_CLOCK(6)
         {
-            const int nt = slices * npairs;
+            const int nt = slices * B;
+#pragma unroll 1
             for (int task = warp; task < nt; task += W) {
-                const int slice = task >= npairs ? 1 : 0, q = task - slice * npairs;
+                const int slice = task >= B ? 1 : 0, b = task - slice * B;
                 const int col = slice * 32 + lane, pl = min(col, np - 1);
                 const bool valid = col < np;
-                const long m = m0 + pl;
+                const int m = m0 + pl;
                 LossCtx cx;
                 cx.k2 = k2; cx.k3 = k3; cx.s2 = s2; cx.s3 = s3;
                 cx.sgx = cx.sgy = cx.sgn = 0.f;
@@ -508,62 +675,84 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 if (a.normalize) {
                     cx.sx = NRM[col]; cx.sy = NRM[PS + col]; cx.inv = NRM[4 * PS + col]; cx.okn = NRM[5 * PS + col] != 0.f;
                 }
-                float2* g3p = reinterpret_cast<float2*>(G3 + pl * B3 + q * 6);
-                float2* g2p = reinterpret_cast<float2*>(G2 + pl * B3 + q * 6);
-                const float2 h0 = g3p[0], h1 = g3p[1], h2 = g3p[2];
-                const float2 e0 = g2p[0], e1 = g2p[1], e2 = g2p[2];
-                const int b0 = 2 * q, b1 = 2 * q + 1;
-                const V3 t0{TS[(b0 * 3) * PS + col], TS[(b0 * 3 + 1) * PS + col], TS[(b0 * 3 + 2) * PS + col]};
-                const V3 t1{TS[(b1 * 3) * PS + col], TS[(b1 * 3 + 1) * PS + col], TS[(b1 * 3 + 2) * PS + col]};
-                V3 p0, p1, n0, n1;
-                const V3 ga = bone_loss(a, b0, t0, e0.x, e0.y, V3{h0.x, h0.y, h1.x}, m, valid, cx, p0, n0);
-                const V3 gb = bone_loss(a, b1, t1, e1.y, e2.x, V3{h1.y, h2.x, h2.y}, m, valid, cx, p1, n1);
+                const V3 g3 = lds3(G3 + pl * B3, b), g2 = lds3(G2 + pl * B3, b);
+                const V3 t{TS[(b * 3) * PS + col], TS[(b * 3 + 1) * PS + col], TS[(b * 3 + 2) * PS + col]};
+                V3 p, n;
+                const V3 g = bone_loss<WORLD>(a, b, t, g2.x, g2.y, g3, m, valid, cx, p, n);
                 s2 = cx.s2; s3 = cx.s3;
                 if (valid) {
-                    g3p[0] = make_float2(t0.x, t0.y); g3p[1] = make_float2(t0.z, t1.x); g3p[2] = make_float2(t1.y, t1.z);
-                    g2p[0] = make_float2(p0.x, p0.y); g2p[1] = make_float2(p0.z, p1.x); g2p[2] = make_float2(p1.y, p1.z);
+                    sts3(G3 + pl * B3, b, t);
+                    sts3(G2 + pl * B3, b, p);
                     if (a.proj_norm && a.normalize) {   // off the benchmark path: straight to global
-                        float* o = a.proj_norm + (m * B + b0) * 3;
-                        o[0] = n0.x; o[1] = n0.y; o[2] = n0.z; o[3] = n1.x; o[4] = n1.y; o[5] = n1.z;
+                        float* o = a.proj_norm + ((size_t)m * B + b) * 3;
+                        o[0] = n.x; o[1] = n.y; o[2] = n.z;
                     }
                 }
-                GV[(b0 * 3) * PS + col] = ga.x; GV[(b0 * 3 + 1) * PS + col] = ga.y; GV[(b0 * 3 + 2) * PS + col] = ga.z;
-                GV[(b1 * 3) * PS + col] = gb.x; GV[(b1 * 3 + 1) * PS + col] = gb.y; GV[(b1 * 3 + 2) * PS + col] = gb.z;
+                GV[(b * 3) * PS + col] = g.x; GV[(b * 3 + 1) * PS + col] = g.y; GV[(b * 3 + 2) * PS + col] = g.z;
                 if (a.normalize) {
-                    PART[(q * 3) * PS + col] = cx.sgx;
-                    PART[(q * 3 + 1) * PS + col] = cx.sgy;
-                    PART[(q * 3 + 2) * PS + col] = cx.sgn;
+                    PART[(b * 3) * PS + col] = cx.sgx;
+                    PART[(b * 3 + 1) * PS + col] = cx.sgy;
+                    PART[(b * 3 + 2) * PS + col] = cx.sgn;
                 }
             }
         }
         fence_async_smem();
         if (tma) bulk_wait_read_all();   // rel_rot / abs_rot stores have read R and A: A is about to take y_b
         __syncthreads();   // #5
+        TILE_CLOCK(7)
         if (tma) {
-            if (a.abs_loc) bulk_s2g(a.abs_loc + m0 * B3, G3, (uint32_t)(np * B3) * 4u);
-            if (a.proj) bulk_s2g(a.proj + m0 * B3, G2, (uint32_t)(np * B3) * 4u);
+            if (a.abs_loc) bulk_s2g(a.abs_loc + (size_t)m0 * B3, G3, (uint32_t)(np * B3) * 4u);
+            if (a.proj) bulk_s2g(a.proj + (size_t)m0 * B3, G2, (uint32_t)(np * B3) * 4u);
             bulk_commit();
             bulk_wait_read_all();
             // the 6-D records come back (L2 hot) over the two target regions; phase E waits for them
             mbar_expect_tx(bars + 2, (uint32_t)(np * B6) * 4u);
-            bulk_g2s(G3, a.d6 + m0 * B6, (uint32_t)(np * B6) * 4u, bars + 2);
+            bulk_g2s(G3, a.d6 + (size_t)m0 * B6, (uint32_t)(np * B6) * 4u, bars + 2);
         }
 
         // ---- torque backward, leaves first:  S_b = (g_b x t_b, g_b) + sum over children S_c  (in place over t_b, g_b),
-        //      m_b = S_b[0:3] - S_b[3:6] x t_b,  y_b = A_parent m_b  -> words 0..2 of slot b of the A records
+        //      m_b = S_b[0:3] - S_b[3:6] x t_b,  y_b = A_parent m_b  -> words 0..2 of slot b of the A records.
+        //      The own part of the next level's task (t_b, g_b with the normaliser terms of hips / neck, g_b x t_b) is
+        //      computed BEFORE the barrier that ends the level below it.
         if (warp < TW) {
-            for (int lv = a.nlevels - 1; lv >= 0; --lv) {
-                const int s0 = a.lvl_start[lv], cnt = a.lvl_start[lv + 1] - s0;
-                const int nt = slices * cnt;
-                for (int task = warp; task < nt; task += TW) {
-                    const int slice = task >= cnt ? 1 : 0, b = a.order[s0 + task - slice * cnt], par = a.parent[b];
-                    const int col = slice * 32 + lane, pl = min(col, np - 1);
-                    const V3 t{TS[(b * 3) * PS + col], TS[(b * 3 + 1) * PS + col], TS[(b * 3 + 2) * PS + col]};
-                    V3 g{GV[(b * 3) * PS + col], GV[(b * 3 + 1) * PS + col], GV[(b * 3 + 2) * PS + col]};
+            int4 d;
+            int col = 0, pl = 0;
+            float tx = 0.f, ty = 0.f, tz = 0.f, S0 = 0.f, S1 = 0.f, S2 = 0.f, S3 = 0.f, S4 = 0.f, S5 = 0.f;
+#pragma unroll 1
+            for (int lv = a.nlevels; lv >= 0; --lv) {
+                // dependent half of level lv (children sums are complete after the barrier below)
+                if (lv < a.nlevels && d.x >= 0) {
+                    const int b = d.x, par = d.y;
+                    for (int ci = d.w & 0xff; ci < (d.w >> 8); ++ci) {
+                        const int c = CHILD[ci];
+                        S0 += TS[(c * 3) * PS + col]; S1 += TS[(c * 3 + 1) * PS + col]; S2 += TS[(c * 3 + 2) * PS + col];
+                        S3 += GV[(c * 3) * PS + col]; S4 += GV[(c * 3 + 1) * PS + col]; S5 += GV[(c * 3 + 2) * PS + col];
+                    }
+                    const V3 mv{S0 - (S4 * tz - S5 * ty), S1 - (S5 * tx - S3 * tz), S2 - (S3 * ty - S4 * tx)};
+                    V3 yv = mv;
+                    if (par >= 0) {   // (the root's sums are not read by anyone)
+                        TS[(b * 3) * PS + col] = S0; TS[(b * 3 + 1) * PS + col] = S1; TS[(b * 3 + 2) * PS + col] = S2;
+                        GV[(b * 3) * PS + col] = S3; GV[(b * 3 + 1) * PS + col] = S4; GV[(b * 3 + 2) * PS + col] = S5;
+                        yv = v3_mul_mt(mv, lds9(A + pl * B9, par));
+                    }
+                    if (col < np) {
+                        float* o = A + pl * B9 + b * 9;
+                        o[0] = yv.x; o[1] = yv.y; o[2] = yv.z;
+                    }
+                }
+                if (lv == 0) break;
+                // independent half of level lv-1
+                d = DESC[(lv - 1) * TW + warp];
+                if (d.x >= 0) {
+                    const int b = d.x;
+                    col = d.z * 32 + lane;
+                    pl = min(col, np - 1);
+                    tx = TS[(b * 3) * PS + col]; ty = TS[(b * 3 + 1) * PS + col]; tz = TS[(b * 3 + 2) * PS + col];
+                    float gx = GV[(b * 3) * PS + col], gy = GV[(b * 3 + 1) * PS + col], gz = GV[(b * 3 + 2) * PS + col];
                     if (a.normalize && (b == a.hips || b == a.neck)) {
                         // normaliser backward through shift (hips) and scale (|neck - hips|): sums over all bones
                         float sgx = 0.f, sgy = 0.f, sgn = 0.f;
-                        for (int q = 0; q < npairs; ++q) {
+                        for (int q = 0; q < B; ++q) {
                             sgx += PART[(q * 3) * PS + col];
                             sgy += PART[(q * 3 + 1) * PS + col];
                             sgn += PART[(q * 3 + 2) * PS + col];
@@ -574,34 +763,20 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                         float cx = 0.f, cy = 0.f;
                         if (b == a.neck) { cx += kx; cy += ky; }
                         if (b == a.hips) { cx -= fmaf(sgx, inv, kx); cy -= fmaf(sgy, inv, ky); }
-                        const long m = m0 + pl;
-                        const V3 gp = project_bwd(a, project(a, t, m), cx, cy, m);
-                        g.x += gp.x; g.y += gp.y; g.z += gp.z;
+                        const int m = m0 + pl;
+                        const V3 t{tx, ty, tz};
+                        const V3 gp = project_bwd<WORLD>(a, project<WORLD>(a, t, m), cx, cy, m);
+                        gx += gp.x; gy += gp.y; gz += gp.z;
                     }
-                    float S[6] = {g.y * t.z - g.z * t.y, g.z * t.x - g.x * t.z, g.x * t.y - g.y * t.x, g.x, g.y, g.z};
-                    for (int ci = a.child_start[b]; ci < a.child_start[b + 1]; ++ci) {
-                        const int c = a.child_list[ci];
-                        S[0] += TS[(c * 3) * PS + col]; S[1] += TS[(c * 3 + 1) * PS + col]; S[2] += TS[(c * 3 + 2) * PS + col];
-                        S[3] += GV[(c * 3) * PS + col]; S[4] += GV[(c * 3 + 1) * PS + col]; S[5] += GV[(c * 3 + 2) * PS + col];
-                    }
-                    if (par >= 0) {   // the root's sums are not read by anyone
-                        TS[(b * 3) * PS + col] = S[0]; TS[(b * 3 + 1) * PS + col] = S[1]; TS[(b * 3 + 2) * PS + col] = S[2];
-                        GV[(b * 3) * PS + col] = S[3]; GV[(b * 3 + 1) * PS + col] = S[4]; GV[(b * 3 + 2) * PS + col] = S[5];
-                    }
-                    const V3 mv{S[0] - (S[4] * t.z - S[5] * t.y), S[1] - (S[5] * t.x - S[3] * t.z),
-                                S[2] - (S[3] * t.y - S[4] * t.x)};
-                    V3 yv = mv;
-                    if (par >= 0) yv = v3_mul_mt(mv, lds9(A + pl * B9, par));
-                    if (col < np) {
-                        float* o = A + pl * B9 + b * 9;
-                        o[0] = yv.x; o[1] = yv.y; o[2] = yv.z;
-                    }
+                    S0 = gy * tz - gz * ty; S1 = gz * tx - gx * tz; S2 = gx * ty - gy * tx;
+                    S3 = gx; S4 = gy; S5 = gz;
                 }
-                if (lv > 0) named_barrier(1, TW * 32);
+                if (lv < a.nlevels) named_barrier(1, TW * 32);
             }
             fence_async_smem();   // the scratch rows are about to be overwritten by the next tile's 6-D records (TMA)
         }
         __syncthreads();   // #6
+        TILE_CLOCK(8)
         if (nxt < ntiles) {   // the D region and the other row buffer are free: prefetch for the next tile
             if (tma) load_d6(nxt);
             if (warp == W - 1) fill_rows(nxt, (it + 1) & 1);
@@ -609,56 +784,54 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         // ---- phase D: z[t] = sum_{s >= t} y[s] per clip (the reverse-time scan in tangent form is a suffix sum)
         if (a.scan) {
             const int items = (np / L) * B3;
+#pragma unroll 1
             for (int idx = tid; idx < items; idx += NT) {
                 const int c = idx / B3, rem = idx - c * B3, b = rem / 3, j = rem - b * 3;
                 float* y = A + (c * L + L - 1) * B9 + b * 9 + j;
                 float acc = 0.f;
-#pragma unroll 4
-                for (int f = L - 1; f >= 0; --f) {
+                int f = L;
+#pragma unroll 1
+                for (; f >= 4; f -= 4) {   // four loads in flight per step of the chain
+                    const float y0 = y[0], y1 = y[-B9], y2 = y[-2 * B9], y3 = y[-3 * B9];
+                    const float a0 = acc + y0, a1 = a0 + y1, a2 = a1 + y2, a3 = a2 + y3;
+                    y[0] = a0; y[-B9] = a1; y[-2 * B9] = a2; y[-3 * B9] = a3;
+                    acc = a3;
+                    y -= 4 * B9;
+                }
+                for (; f > 0; --f) {
                     acc += *y;
                     *y = acc;
                     y -= B9;
                 }
             }
         }
+        TILE_CLOCK(9)
         while (!mbar_try_wait(bars + 2, it & 1u)) {}
+        TILE_CLOCK(10)
         __syncthreads();   // #7
-        // ---- phase E: omega[t] = R[t] z[t]; tangent-form Gram-Schmidt backward -> gradient records over the 6-D records
+        TILE_CLOCK(11)
+        // ---- phase E: omega[t] = R[t] z[t]; tangent-form Gram-Schmidt backward -> gradient records over the 6-D
+        //      records (which now live in the two target regions); one bone per task
         {
-            const int nt = slices * npairs;
+            const int nt = slices * B;
+#pragma unroll 1
             for (int task = warp; task < nt; task += W) {
-                const int slice = task >= npairs ? 1 : 0, q = task - slice * npairs;
+                const int slice = task >= B ? 1 : 0, b = task - slice * B;
                 const int col = slice * 32 + lane, pl = min(col, np - 1);
-                float4* dp = reinterpret_cast<float4*>(G3 + pl * B6 + q * 12);
-                const float4 u0 = dp[0], u1 = dp[1], u2 = dp[2];
-                const float d[12] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w, u2.x, u2.y, u2.z, u2.w};
-                const float2* rp = reinterpret_cast<const float2*>(R + pl * B9 + q * 18);
-                const float2 r0 = rp[0], r1 = rp[1], r2 = rp[2], r3 = rp[3], r4 = rp[4], r5 = rp[5], r6 = rp[6], r7 = rp[7],
-                             r8 = rp[8];
-                const float* zp = A + pl * B9 + q * 18;
-                const float2 z01 = *reinterpret_cast<const float2*>(zp);
-                const float z2 = zp[2], z3 = zp[9];
-                const float2 z45 = *reinterpret_cast<const float2*>(zp + 10);
-                M3 Ra, Rb;
-                Ra.m[0] = r0.x; Ra.m[1] = r0.y; Ra.m[2] = r1.x; Ra.m[3] = r1.y; Ra.m[4] = r2.x; Ra.m[5] = r2.y;
-                Ra.m[6] = r3.x; Ra.m[7] = r3.y; Ra.m[8] = r4.x;
-                Rb.m[0] = r4.y; Rb.m[1] = r5.x; Rb.m[2] = r5.y; Rb.m[3] = r6.x; Rb.m[4] = r6.y; Rb.m[5] = r7.x;
-                Rb.m[6] = r7.y; Rb.m[7] = r8.x; Rb.m[8] = r8.y;
-                const V3 oa = v3_mul_mt(V3{z01.x, z01.y, z2}, Ra), ob = v3_mul_mt(V3{z3, z45.x, z45.y}, Rb);
-                float o[12];
-                gram_schmidt_bwd_tangent(gram_schmidt(d), oa, o);
-                gram_schmidt_bwd_tangent(gram_schmidt(d + 6), ob, o + 6);
-                if (col < np) {
-                    dp[0] = make_float4(o[0], o[1], o[2], o[3]);
-                    dp[1] = make_float4(o[4], o[5], o[6], o[7]);
-                    dp[2] = make_float4(o[8], o[9], o[10], o[11]);
-                }
+                float d[6], o[6];
+                lds6(G3 + pl * B6, b, d);
+                const M3 Rb = lds9(R + pl * B9, b);
+                const V3 z = lds3(A + pl * B9 + 6 * b, b);   // words 0..2 of the 9-word slot b (3 b + 6 b = 9 b)
+                const V3 om = v3_mul_mt(z, Rb);
+                gram_schmidt_bwd_tangent(gram_schmidt(d), om, o);
+                if (col < np) sts6(G3 + pl * B6, b, o);
             }
         }
         fence_async_smem();
         __syncthreads();   // #8
+        TILE_CLOCK(12)
         if (tma) {
-            bulk_s2g(a.g_d6 + m0 * B6, G3, (uint32_t)(np * B6) * 4u);
+            bulk_s2g(a.g_d6 + (size_t)m0 * B6, G3, (uint32_t)(np * B6) * 4u);
             bulk_commit();
             bulk_wait_read_all();   // the gradient has left the target regions: the next tile's targets may land
             if (nxt < ntiles) load_targets(nxt);
@@ -701,6 +874,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             a.losses[7] = 0.f;
             *a.ticket = 0u;   // self-resetting workspace header: ready for the next launch
             *a.count2 = 0;
+            *a.arrive = 0u;
         }
     }
 }
@@ -757,11 +931,11 @@ bool tree_tables(const p2c_tree_t& t, TileArgs& a) {
 }
 
 struct TileLaunch {
-    int ok, P, PS, slices, threads, grid;
+    int ok, P, PS, slices, threads, tree_warps, grid, count_inline;
     size_t smem;
 };
 
-TileLaunch make_launch(const p2c_fused_step_t* p) {
+TileLaunch make_launch(const p2c_fused_step_t* p, const TileArgs& a) {   // a: tree tables filled in
     TileLaunch t{};
     const int B = p->tree.n_bones, L = p->clip_len;
     const long total = (long)p->n_clips * L;
@@ -776,25 +950,32 @@ TileLaunch make_launch(const p2c_fused_step_t* p) {
     // pose record is an even, not a multiple-of-four, count) and 16-byte aligned tensors; anything else takes the
     // bone-per-lane kernels of fused_fast.cu, which also copy cooperatively
     if ((t.P & 1) || (total & 1)) return t;
+    if (total > (1L << 30)) return t;   // pose indices are 32-bit inside the kernel
     const void* ptrs[] = {p->pose_in, p->gt_2d, p->gt_3d, p->g_pose_in, p->rel_rot, p->abs_rot, p->abs_loc, p->proj};
     for (const void* q : ptrs)
         if (reinterpret_cast<uintptr_t>(q) & 15) return t;
     t.PS = (t.P + 31) & ~31;
     t.slices = t.PS / 32;
-    t.smem = (size_t)tile_plan(t.PS, B, B / 2).total * sizeof(float);
-    const size_t cap = 227 * 1024;
-    if (t.smem + 1024 > cap) return t;
-    int warps = (B / 2) * t.slices;
+    const long ntiles = (total + t.P - 1) / t.P;
+    // many tiles: two bones per warp and two CTAs per SM; at most one tile per SM (the 256 x 16 step): one bone per
+    // warp, which halves the latency of the element-wise passes
+    const bool lone = ntiles <= sm_count();
+    int warps = (lone ? B : B / 2) * t.slices;
     if (warps < 4) warps = 4;
     if (warps > MAX_THREADS / 32) warps = MAX_THREADS / 32;
     t.threads = warps * 32;
+    t.tree_warps = a.tree_warps * t.slices;   // one task per tree warp and level
+    if (t.tree_warps > warps) return t;       // (very wide trees take the bone-per-lane kernels)
+    t.smem = (size_t)tile_plan(t.PS, B, a.nlevels * t.tree_warps).total * sizeof(float);
+    const size_t cap = 227 * 1024;
+    if (t.smem + 1024 > cap) return t;
     int per_sm = (int)((228 * 1024) / (t.smem + 1024));
-    if (per_sm * t.threads > 1664) per_sm = 1664 / t.threads;   // 78 registers per thread (launch bounds 832 x 1)
+    if (per_sm * t.threads > 896) per_sm = 896 / t.threads;   // 72 registers per thread (launch bounds 832 x 1)
     if (per_sm > 4) per_sm = 4;   // the workspace holds 2 x 592 loss partials
     if (per_sm < 1) per_sm = 1;
-    const long ntiles = (total + t.P - 1) / t.P;
     const long slots = (long)sm_count() * per_sm;
     t.grid = (int)(ntiles < slots ? ntiles : slots);
+    t.count_inline = lone ? 1 : 0;   // grid == ntiles <= SMs: every CTA is resident, the in-kernel wait cannot hang
     t.ok = 1;
     return t;
 }
@@ -816,20 +997,29 @@ extern "C" int p2c_fused_tile_supported(const p2c_fused_step_t* p) {
     if (p->gt_2d_channels != 3) return 0;   // the projection records replace the 2-D target records in place
     TileArgs a{};
     if (!tree_tables(p->tree, a)) return 0;
-    return make_launch(p).ok;
+    return make_launch(p, a).ok;
 }
 
-extern "C" int p2c_fused_tile_launches(const p2c_fused_step_t* p) { return p->mask_missing_joints ? 2 : 1; }
+// debug: the phase clocks recorded by CTA 0 (P2C_TILE_CLOCKS=1); host buffer of 32 values
+extern "C" int p2c_debug_tile_clocks(long long* out) {
+    return (int)cudaMemcpyFromSymbol(out, g_tile_clocks, sizeof(long long) * 64);
+}
+
+extern "C" int p2c_fused_tile_launches(const p2c_fused_step_t* p) {
+    TileArgs a{};
+    if (!tree_tables(p->tree, a)) return 1;
+    return (p->mask_missing_joints && !make_launch(p, a).count_inline) ? 2 : 1;
+}
 
 extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     TileArgs a{};
     if (!tree_tables(p->tree, a)) return P2C_E_UNSUPPORTED;
-    const TileLaunch t = make_launch(p);
+    const TileLaunch t = make_launch(p, a);
     if (!t.ok) return P2C_E_UNSUPPORTED;
     const int B = p->tree.n_bones;
     a.N = p->n_clips; a.L = p->clip_len; a.P = t.P; a.PS = t.PS; a.slices = t.slices;
-    a.tree_warps *= t.slices;
-    if (a.tree_warps > t.threads / 32) a.tree_warps = t.threads / 32;
+    a.tree_warps = t.tree_warps;
+    a.clocks = env_on("P2C_TILE_CLOCKS");
     a.scan = p->mode == P2C_MODE_POSE_CHANGES;
     a.hips = p->hips; a.neck = p->neck; a.normalize = p->normalize; a.mask = p->mask_missing_joints;
     a.d6 = p->pose_in; a.ref_loc = p->ref_loc; a.ref_rot = p->ref_rot; a.ref_index = p->ref_index;
@@ -839,21 +1029,25 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     a.proj_norm = p->proj_norm; a.g_d6 = p->g_pose_in;
     a.ticket = reinterpret_cast<unsigned int*>(p->workspace);
     a.count2 = reinterpret_cast<int*>(p->workspace) + 1;
+    a.arrive = reinterpret_cast<unsigned int*>(p->workspace) + 2;
+    a.count_inline = t.count_inline;
     a.partials = p->workspace + 16;
     a.losses = p->losses;
     const long total = (long)p->n_clips * p->clip_len;
     a.count3 = (double)total * B * 3;
     cudaStream_t st = (cudaStream_t)stream;
-    if (a.mask) {
+    if (a.mask && !a.count_inline) {
         long blocks = (total * B + 255) / 256;
         if (blocks > COUNT_BLOCKS) blocks = COUNT_BLOCKS;
         tile_count_kernel<<<(int)blocks, 256, 0, st>>>(p->gt_2d, total, B, p->gt_2d_channels, p->hips, a.count2);
         P2C_LAUNCH_CHECK();
     }
     typedef void (*kern_t)(const TileArgs);
-    const int ki = B == 26 ? (t.slices == 1 ? 0 : 1) : 2;   // CARLA_SKELETON gets compile-time bone and slice counts
-    const kern_t k = ki == 0 ? tile_kernel<26, 1> : ki == 1 ? tile_kernel<26, 2> : tile_kernel<0, 0>;
-    static bool configured[3] = {false, false, false};
+    const bool world = p->world_loc || p->world_rot;
+    const int ki = world ? 3 : B == 26 ? (t.slices == 1 ? 0 : 1) : 2;   // CARLA_SKELETON: compile-time bones and slices
+    const kern_t k = ki == 0 ? tile_kernel<26, 1, false> : ki == 1 ? tile_kernel<26, 2, false>
+                   : ki == 2 ? tile_kernel<0, 0, false> : tile_kernel<0, 0, true>;
+    static bool configured[4] = {false, false, false, false};
     if (!configured[ki]) {
         cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
         if (e != cudaSuccess) return (int)e;
