@@ -39,6 +39,7 @@ namespace {
 constexpr int MAX_LEVELS = 24;
 constexpr int COUNT_BLOCKS = 296;
 constexpr int MAX_THREADS = 832;
+constexpr int MAX_FK_DESC = 352;
 
 struct TileArgs {
     int N, L, B, P, PS, slices, scan;   // clips, frames per clip, bones, poses per tile, P rounded up to 32, PS/32
@@ -46,6 +47,8 @@ struct TileArgs {
     int tree_warps;   // warps that take part in the level-synchronous tree phases
     int count_inline; // every CTA owns exactly one tile: the mask count happens inside the kernel (no pre-pass)
     int clocks;       // debug (P2C_TILE_CLOCKS=1): CTA 0 records clock64() at every phase boundary of its second tile
+    int fk_rounds;    // rounds of W column tasks in the forward tree walk
+    uint16_t fk_desc[MAX_FK_DESC];
     int8_t parent[P2C_MAX_BONES];
     int8_t order[P2C_MAX_BONES];          // bones sorted by tree level
     int8_t lvl_start[MAX_LEVELS + 1];     // order[lvl_start[l] .. lvl_start[l+1]) = bones of level l
@@ -227,9 +230,9 @@ __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.a
 
 // shared-memory plan (floats); every region starts 16-byte aligned (PS is a multiple of 32)
 struct TilePlan {
-    int d, g3, g2, r, a, nrm, part, row, red, bars, desc, child, total;
+    int d, g3, g2, r, a, nrm, part, row, red, bars, total;
 };
-__device__ __host__ __forceinline__ TilePlan tile_plan(int PS, int B, int ndesc) {
+__device__ __host__ __forceinline__ TilePlan tile_plan(int PS, int B) {
     TilePlan s;
     int o = 0;
     s.d = o; o += PS * B * 6;
@@ -238,12 +241,10 @@ __device__ __host__ __forceinline__ TilePlan tile_plan(int PS, int B, int ndesc)
     s.r = o; o += PS * B * 9;
     s.a = o; o += PS * B * 9;
     s.nrm = o; o += 8 * PS;            // sx, sy, dx, dy, inv, ok per pose
-    s.part = o; o += B * 3 * PS;       // per bone: gx, gy, gx x + gy y per pose (normaliser backward)
+    s.part = o; o += B * 3 * PS;       // per bone: gx, gy, gx x + gy y per pose (normaliser backward), then Sx rows
     s.row = o; o += 2 * PS;            // skeleton-table row per pose, double buffered (next tile's rows prefetched)
     s.red = o; o += 2 * 32;            // loss partials per warp
     s.bars = o; o += 8;                // three 8-byte mbarriers
-    s.desc = o; o += 4 * ndesc;        // int4 task descriptor per (tree level, tree warp)
-    s.child = o; o += P2C_MAX_BONES;   // child lists
     s.total = o;
     return s;
 }
@@ -408,7 +409,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NT = blockDim.x, W = NT >> 5;
     const int B = BT ? BT : a.B, slices = SL ? SL : a.slices;
     const int B3 = B * 3, B6 = B * 6, B9 = B * 9, PS = 32 * slices, L = a.L;
-    const TilePlan sm = tile_plan(PS, B, a.nlevels * a.tree_warps);
+    const TilePlan sm = tile_plan(PS, B);
     float* D = smem + sm.d;
     float* G3 = smem + sm.g3;     // G3 and G2 are adjacent: together they hold the re-fetched 6-D records
     float* G2 = smem + sm.g2;
@@ -419,12 +420,9 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     int* ROW = reinterpret_cast<int*>(smem + sm.row);   // two buffers of PS
     float* red = smem + sm.red;
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + sm.bars);   // [0] 6-D in, [1] targets in, [2] 6-D again
-    int4* DESC = reinterpret_cast<int4*>(smem + sm.desc);
-    int* CHILD = reinterpret_cast<int*>(smem + sm.child);
     float* TS = D;               // SoA scratch rows [0, 3B): t_b, later subtree sums of g x t
     float* GV = D + B3 * PS;     // SoA scratch rows [3B, 6B): g_b, later subtree sums of g
     const bool tma = tid == (W - 1) * 32;   // the thread that issues every bulk copy (a warp without tree work)
-    const int TW = a.tree_warps;            // warps that walk the tree; the others skip to the next CTA barrier
     const int total = a.N * L;              // (the launcher keeps N*L*B*9 below 2^31 elements... offsets are size_t)
     const int ntiles = (total + a.P - 1) / a.P;
 
@@ -461,21 +459,6 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         }
     }
     if (warp == 0 && (int)blockIdx.x < ntiles) fill_rows(blockIdx.x, 0);
-    // task of every (tree level, tree warp): {bone or -1, parent, slice, child_begin | child_end << 8}; one task per
-    // warp and level (the launcher sizes TW to the widest level), so the level loops below need no table walks
-    for (int i = tid; i < a.nlevels * TW; i += NT) {
-        const int lv = i / TW, w = i - lv * TW;
-        const int s0 = a.lvl_start[lv], cnt = a.lvl_start[lv + 1] - s0;
-        int4 d = make_int4(-1, -1, 0, 0);
-        if (w < slices * cnt) {
-            d.z = w >= cnt ? 1 : 0;
-            d.x = a.order[s0 + w - d.z * cnt];
-            d.y = a.parent[d.x];
-            d.w = a.child_start[d.x] | (a.child_start[d.x + 1] << 8);
-        }
-        DESC[i] = d;
-    }
-    if (tid < B) CHILD[tid] = a.child_list[tid];
     __syncthreads();
 
     float k2 = a.w2 * 2.0f / ((a.mask && !a.count_inline) ? (float)__ldcg(a.count2) : (float)total * (float)(B * 2));
@@ -579,87 +562,96 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                     dst[6] = fmaf(c[8], p2, fmaf(c[7], p1, c[6] * p0));
                 }
             }
-            fence_async_smem();
-            __syncthreads();   // #3
-            TILE_CLOCK(4)
         }
+        // bone offsets of every pose's skeleton as SoA rows (row 3b+k, column = pose) in the upper half of the scratch
+        // region: the forward walk reads them conflict free instead of going to the table in global memory
+        {
+            const int busy = (a.scan && (np / L) * B3 <= 160 && NT >= 256) ? 160 : 0;   // threads that ran the scan
+            for (int i = tid - busy; i >= 0 && i < B3 * PS; i += NT - busy) {
+                const int k = i / PS, col = i - k * PS;
+                GV[i] = __ldg(a.ref_loc + (size_t)row[col] * B3 + k);
+            }
+        }
+        fence_async_smem();
+        __syncthreads();   // #3
+        TILE_CLOCK(4)
         if (tma && a.rel_rot) {
             bulk_s2g(a.rel_rot + (size_t)m0 * B9, R, (uint32_t)(np * B9) * 4u);
             bulk_commit();
         }
 
-        // ---- phase C: FK, level by level (p3d_pose.py:116-184): A_b = R_b . A_parent, t_b = loc_b . A_parent + t_parent;
-        //      only the first TW warps take part (named barrier 1 between levels).  The task descriptor and the bone
-        //      offset of level lv+1 are fetched BEFORE the barrier that ends level lv.
-        if (warp < TW) {
-            int4 d = DESC[warp];
-            int col = d.z * 32 + lane;
-            const float* rl = a.ref_loc + ((size_t)row[col] * B + max(d.x, 0)) * 3;
-            V3 loc{__ldg(rl), __ldg(rl + 1), __ldg(rl + 2)};
-#pragma unroll 1
-            for (int lv = 0; lv < a.nlevels; ++lv) {
-                if (d.x >= 0) {
-                    const int b = d.x, par = d.y, pl = min(col, np - 1);
-                    M3 Ab = lds9(R + pl * B9, b);
-                    V3 tb = loc;
-                    if (par >= 0) {
-                        const M3 Ap = lds9(A + pl * B9, par);
-                        const V3 q = v3_mul_m(loc, Ap);
-                        tb = V3{q.x + TS[(par * 3) * PS + col], q.y + TS[(par * 3 + 1) * PS + col],
-                                q.z + TS[(par * 3 + 2) * PS + col]};
-                        Ab = m3_mul(Ab, Ap);
-                    }
-                    if (col < np) sts9(A + pl * B9, b, Ab);
-                    TS[(b * 3) * PS + col] = tb.x;
-                    TS[(b * 3 + 1) * PS + col] = tb.y;
-                    TS[(b * 3 + 2) * PS + col] = tb.z;
+        // ---- phase C: FK (p3d_pose.py:116-184): A_b = R_b . A_parent, t_b = loc_b . A_parent + t_parent.
+        //      Column j of A_b and component j of t_b need only column j of the parent, so THREE warps per slice (one per
+        //      column) each walk the whole tree in bone order, reading back only what they wrote themselves: no
+        //      barrier between bones, and the parent's column stays in registers along chains (parent == b - 1).
+        if (warp < 3 * slices) {
+            const int jc = warp % 3, col = (warp / 3) * 32 + lane, pl = min(col, np - 1);
+            const bool valid = col < np;
+            const float* rb = R + pl * B9;
+            float* ab = A + pl * B9 + jc;
+            const float* lc = GV + col;
+            float* tr = TS + jc * PS + col;
+            float c0 = 0.f, c1 = 0.f, c2 = 0.f, ct = 0.f;   // column jc of A_{b-1}, component jc of t_{b-1}
+#pragma unroll 2
+            for (int b = 0; b < B; ++b) {
+                const int par = a.parent[b];
+                const float r0 = rb[0], r1 = rb[1], r2 = rb[2], r3 = rb[3], r4 = rb[4], r5 = rb[5], r6 = rb[6],
+                            r7 = rb[7], r8 = rb[8];
+                const float l0 = lc[0], l1 = lc[PS], l2 = lc[2 * PS];
+                float p0 = c0, p1 = c1, p2 = c2, tp = ct;
+                if (par >= 0 && par != b - 1) {
+                    const float* ap = A + pl * B9 + par * 9 + jc;
+                    p0 = ap[0]; p1 = ap[3]; p2 = ap[6];
+                    tp = TS[(par * 3 + jc) * PS + col];
                 }
-                TILE_CLOCK(16 + 3 * lv)
-                if (lv + 1 < a.nlevels) {
-                    d = DESC[(lv + 1) * TW + warp];
-                    col = d.z * 32 + lane;
-                    rl = a.ref_loc + ((size_t)row[col] * B + max(d.x, 0)) * 3;
-                    loc = V3{__ldg(rl), __ldg(rl + 1), __ldg(rl + 2)};
+                if (par < 0) {   // root: the parent transform is the identity
+                    p0 = jc == 0 ? 1.f : 0.f; p1 = jc == 1 ? 1.f : 0.f; p2 = jc == 2 ? 1.f : 0.f;
+                    tp = 0.f;
                 }
-                TILE_CLOCK(17 + 3 * lv)
-                named_barrier(1, TW * 32);
-                TILE_CLOCK(18 + 3 * lv)
-            }
-            // hips/neck shift and scale of every pose (extractor.py:23-36, hips_neck_extractor.py:6-13)
-            if (a.normalize && warp < slices) {
-                col = warp * 32 + lane;
-                const int m = m0 + min(col, np - 1);
-                const V3 th{TS[(a.hips * 3) * PS + col], TS[(a.hips * 3 + 1) * PS + col], TS[(a.hips * 3 + 2) * PS + col]};
-                const V3 tn{TS[(a.neck * 3) * PS + col], TS[(a.neck * 3 + 1) * PS + col], TS[(a.neck * 3 + 2) * PS + col]};
-                const Proj ph = project<WORLD>(a, th, m), pn = project<WORLD>(a, tn, m);
-                const float dx = pn.p.x - ph.p.x, dy = pn.p.y - ph.p.y;
-                const float scale = fsqrt(fmaf(dx, dx, dy * dy));
-                NRM[col] = ph.p.x;
-                NRM[PS + col] = ph.p.y;
-                NRM[2 * PS + col] = dx;
-                NRM[3 * PS + col] = dy;
-                NRM[4 * PS + col] = frcp(scale);
-                NRM[5 * PS + col] = (scale > 0.f && scale <= 3.402823466e38f) ? 1.f : 0.f;
+                c0 = fmaf(r2, p2, fmaf(r1, p1, r0 * p0));
+                c1 = fmaf(r5, p2, fmaf(r4, p1, r3 * p0));
+                c2 = fmaf(r8, p2, fmaf(r7, p1, r6 * p0));
+                ct = fmaf(l2, p2, fmaf(l1, p1, l0 * p0)) + tp;
+                if (valid) { ab[0] = c0; ab[3] = c1; ab[6] = c2; }
+                tr[0] = ct;
+                rb += 9; ab += 9; lc += 3 * PS; tr += 3 * PS;
             }
             fence_async_smem();
+        }
+        __syncthreads();   // #4
+        TILE_CLOCK(5)
+        if (tma && a.abs_rot) {
+            bulk_s2g(a.abs_rot + (size_t)m0 * B9, A, (uint32_t)(np * B9) * 4u);
+            bulk_commit();
+        }
+        // hips/neck shift and scale of every pose (extractor.py:23-36, hips_neck_extractor.py:6-13)
+        if (a.normalize && warp < slices) {
+            const int col = warp * 32 + lane;
+            const int m = m0 + min(col, np - 1);
+            const V3 th{TS[(a.hips * 3) * PS + col], TS[(a.hips * 3 + 1) * PS + col], TS[(a.hips * 3 + 2) * PS + col]};
+            const V3 tn{TS[(a.neck * 3) * PS + col], TS[(a.neck * 3 + 1) * PS + col], TS[(a.neck * 3 + 2) * PS + col]};
+            const Proj ph = project<WORLD>(a, th, m), pn = project<WORLD>(a, tn, m);
+            const float dx = pn.p.x - ph.p.x, dy = pn.p.y - ph.p.y;
+            const float scale = fsqrt(fmaf(dx, dx, dy * dy));
+            NRM[col] = ph.p.x;
+            NRM[PS + col] = ph.p.y;
+            NRM[2 * PS + col] = dx;
+            NRM[3 * PS + col] = dy;
+            NRM[4 * PS + col] = frcp(scale);
+            NRM[5 * PS + col] = (scale > 0.f && scale <= 3.402823466e38f) ? 1.f : 0.f;
         }
         if (a.mask && a.count_inline && tid == 0) {
             while (*reinterpret_cast<volatile unsigned int*>(a.arrive) < gridDim.x) {}
             __threadfence();
             k2_shared = a.w2 * 2.0f / (float)__ldcg(a.count2);
         }
-        __syncthreads();   // #4
+        while (!mbar_try_wait(bars + 1, it & 1u)) {}
+        __syncthreads();   // #4b
         if (a.mask && a.count_inline) k2 = k2_shared;
-        TILE_CLOCK(5)
-        if (tma && a.abs_rot) {
-            bulk_s2g(a.abs_rot + (size_t)m0 * B9, A, (uint32_t)(np * B9) * 4u);
-            bulk_commit();
-        }
+        TILE_CLOCK(6)
 
         // ---- projection, normaliser, loss terms, dL/d abs_loc; one bone per task; abs_loc and projection records are
         //      written over the target records they were compared with
-        while (!mbar_try_wait(bars + 1, it & 1u)) {}
-        TILE_CLOCK(6)
         {
             const int nt = slices * B;
 #pragma unroll 1
@@ -697,7 +689,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             }
         }
         fence_async_smem();
-        if (tma) bulk_wait_read_all();   // rel_rot / abs_rot stores have read R and A: A is about to take y_b
+        if (tma) bulk_wait_read_all();   // rel_rot / abs_rot stores have read R and A
         __syncthreads();   // #5
         TILE_CLOCK(7)
         if (tma) {
@@ -709,122 +701,117 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             mbar_expect_tx(bars + 2, (uint32_t)(np * B6) * 4u);
             bulk_g2s(G3, a.d6 + (size_t)m0 * B6, (uint32_t)(np * B6) * 4u, bars + 2);
         }
-
-        // ---- torque backward, leaves first:  S_b = (g_b x t_b, g_b) + sum over children S_c  (in place over t_b, g_b),
-        //      m_b = S_b[0:3] - S_b[3:6] x t_b,  y_b = A_parent m_b  -> words 0..2 of slot b of the A records.
-        //      The own part of the next level's task (t_b, g_b with the normaliser terms of hips / neck, g_b x t_b) is
-        //      computed BEFORE the barrier that ends the level below it.
-        if (warp < TW) {
-            int4 d;
-            int col = 0, pl = 0;
-            float tx = 0.f, ty = 0.f, tz = 0.f, S0 = 0.f, S1 = 0.f, S2 = 0.f, S3 = 0.f, S4 = 0.f, S5 = 0.f;
+        // ---- normaliser backward through shift (hips) and scale (|neck - hips|): it needs the sums over all bones, and
+        //      lands on g_hips and g_neck before the subtree sums are formed
+        if (a.normalize) {
+            if (warp < slices) {
+                const int col = warp * 32 + lane, pl = min(col, np - 1), m = m0 + pl;
+                float sgx = 0.f, sgy = 0.f, sgn = 0.f;
+#pragma unroll 2
+                for (int q = 0; q < B; ++q) {
+                    sgx += PART[(q * 3) * PS + col];
+                    sgy += PART[(q * 3 + 1) * PS + col];
+                    sgn += PART[(q * 3 + 2) * PS + col];
+                }
+                const float inv = NRM[5 * PS + col] != 0.f ? NRM[4 * PS + col] : 0.f;
+                const float gs = -sgn * inv * inv;   // dL/dscale . (1/scale)
+                const float kx = gs * NRM[2 * PS + col], ky = gs * NRM[3 * PS + col];
 #pragma unroll 1
-            for (int lv = a.nlevels; lv >= 0; --lv) {
-                // dependent half of level lv (children sums are complete after the barrier below)
-                if (lv < a.nlevels && d.x >= 0) {
-                    const int b = d.x, par = d.y;
-                    for (int ci = d.w & 0xff; ci < (d.w >> 8); ++ci) {
-                        const int c = CHILD[ci];
-                        S0 += TS[(c * 3) * PS + col]; S1 += TS[(c * 3 + 1) * PS + col]; S2 += TS[(c * 3 + 2) * PS + col];
-                        S3 += GV[(c * 3) * PS + col]; S4 += GV[(c * 3 + 1) * PS + col]; S5 += GV[(c * 3 + 2) * PS + col];
-                    }
-                    const V3 mv{S0 - (S4 * tz - S5 * ty), S1 - (S5 * tx - S3 * tz), S2 - (S3 * ty - S4 * tx)};
-                    V3 yv = mv;
-                    if (par >= 0) {   // (the root's sums are not read by anyone)
-                        TS[(b * 3) * PS + col] = S0; TS[(b * 3 + 1) * PS + col] = S1; TS[(b * 3 + 2) * PS + col] = S2;
-                        GV[(b * 3) * PS + col] = S3; GV[(b * 3 + 1) * PS + col] = S4; GV[(b * 3 + 2) * PS + col] = S5;
-                        yv = v3_mul_mt(mv, lds9(A + pl * B9, par));
-                    }
-                    if (col < np) {
-                        float* o = A + pl * B9 + b * 9;
-                        o[0] = yv.x; o[1] = yv.y; o[2] = yv.z;
-                    }
+                for (int which = 0; which < 2; ++which) {
+                    const int b = which ? a.neck : a.hips;
+                    float cx = 0.f, cy = 0.f;   // (hips == neck would get both terms)
+                    if (b == a.neck) { cx += kx; cy += ky; }
+                    if (b == a.hips) { cx -= fmaf(sgx, inv, kx); cy -= fmaf(sgy, inv, ky); }
+                    if (which && a.neck == a.hips) break;
+                    const V3 t{TS[(b * 3) * PS + col], TS[(b * 3 + 1) * PS + col], TS[(b * 3 + 2) * PS + col]};
+                    const V3 gp = project_bwd<WORLD>(a, project<WORLD>(a, t, m), cx, cy, m);
+                    GV[(b * 3) * PS + col] += gp.x; GV[(b * 3 + 1) * PS + col] += gp.y; GV[(b * 3 + 2) * PS + col] += gp.z;
                 }
-                if (lv == 0) break;
-                // independent half of level lv-1
-                d = DESC[(lv - 1) * TW + warp];
-                if (d.x >= 0) {
-                    const int b = d.x;
-                    col = d.z * 32 + lane;
-                    pl = min(col, np - 1);
-                    tx = TS[(b * 3) * PS + col]; ty = TS[(b * 3 + 1) * PS + col]; tz = TS[(b * 3 + 2) * PS + col];
-                    float gx = GV[(b * 3) * PS + col], gy = GV[(b * 3 + 1) * PS + col], gz = GV[(b * 3 + 2) * PS + col];
-                    if (a.normalize && (b == a.hips || b == a.neck)) {
-                        // normaliser backward through shift (hips) and scale (|neck - hips|): sums over all bones
-                        float sgx = 0.f, sgy = 0.f, sgn = 0.f;
-                        for (int q = 0; q < B; ++q) {
-                            sgx += PART[(q * 3) * PS + col];
-                            sgy += PART[(q * 3 + 1) * PS + col];
-                            sgn += PART[(q * 3 + 2) * PS + col];
-                        }
-                        const float inv = NRM[5 * PS + col] != 0.f ? NRM[4 * PS + col] : 0.f;
-                        const float gs = -sgn * inv * inv;   // dL/dscale . (1/scale)
-                        const float kx = gs * NRM[2 * PS + col], ky = gs * NRM[3 * PS + col];
-                        float cx = 0.f, cy = 0.f;
-                        if (b == a.neck) { cx += kx; cy += ky; }
-                        if (b == a.hips) { cx -= fmaf(sgx, inv, kx); cy -= fmaf(sgy, inv, ky); }
-                        const int m = m0 + pl;
-                        const V3 t{tx, ty, tz};
-                        const V3 gp = project_bwd<WORLD>(a, project<WORLD>(a, t, m), cx, cy, m);
-                        gx += gp.x; gy += gp.y; gz += gp.z;
-                    }
-                    S0 = gy * tz - gz * ty; S1 = gz * tx - gx * tz; S2 = gx * ty - gy * tx;
-                    S3 = gx; S4 = gy; S5 = gz;
-                }
-                if (lv < a.nlevels) named_barrier(1, TW * 32);
             }
-            fence_async_smem();   // the scratch rows are about to be overwritten by the next tile's 6-D records (TMA)
+            __syncthreads();   // #5b
         }
+
+        // ---- subtree sums, leaves first (the bone order has parents before children, so a walk in reverse bone order
+        //      meets every child before its parent):  Sx_b = sum_{d in subtree(b)} g_d x t_d (rows XR, the former
+        //      partial-sum rows), Sg_b = sum g_d (in place over g_b).  The six components are independent: one warp
+        //      each per slice, no barrier inside the walk, the running value stays in a register along chains.
+        float* XR = PART;
+        if (warp < 6 * slices) {
+            const int k = warp % 6, col = (warp / 6) * 32 + lane;
+            // own parts g_b x t_b first (they read g_b, which the Sg walks are about to overwrite): 78 rows over 6 warps
+            for (int rw = k; rw < B3; rw += 6) {
+                const int b = rw / 3, c = rw - 3 * b, c1 = c == 2 ? 0 : c + 1, c2 = c == 0 ? 2 : c - 1;
+                const float* g = GV + (b * 3) * PS + col;
+                const float* t = TS + (b * 3) * PS + col;
+                XR[rw * PS + col] = g[c1 * PS] * t[c2 * PS] - g[c2 * PS] * t[c1 * PS];
+            }
+            named_barrier(1, 6 * slices * 32);
+            float* rowp = (k < 3 ? XR + k * PS : GV + (k - 3) * PS) + col;
+            float carry = 0.f;
+            bool have = false;
+#pragma unroll 1
+            for (int c = B - 1; c >= 1; --c) {
+                float v = rowp[c * 3 * PS];
+                if (have) {
+                    v += carry;
+                    rowp[c * 3 * PS] = v;
+                }
+                const int par = a.parent[c];
+                if (par == c - 1) {
+                    carry = v;
+                    have = true;
+                } else {
+                    rowp[par * 3 * PS] += v;
+                    have = false;
+                }
+            }
+            if (have) rowp[0] += carry;
+        }
+        while (!mbar_try_wait(bars + 2, it & 1u)) {}
         __syncthreads();   // #6
         TILE_CLOCK(8)
-        if (nxt < ntiles) {   // the D region and the other row buffer are free: prefetch for the next tile
-            if (tma) load_d6(nxt);
-            if (warp == W - 1) fill_rows(nxt, (it + 1) & 1);
-        }
-        // ---- phase D: z[t] = sum_{s >= t} y[s] per clip (the reverse-time scan in tangent form is a suffix sum)
-        if (a.scan) {
-            const int items = (np / L) * B3;
-#pragma unroll 1
-            for (int idx = tid; idx < items; idx += NT) {
-                const int c = idx / B3, rem = idx - c * B3, b = rem / 3, j = rem - b * 3;
-                float* y = A + (c * L + L - 1) * B9 + b * 9 + j;
-                float acc = 0.f;
-                int f = L;
-#pragma unroll 1
-                for (; f >= 4; f -= 4) {   // four loads in flight per step of the chain
-                    const float y0 = y[0], y1 = y[-B9], y2 = y[-2 * B9], y3 = y[-3 * B9];
-                    const float a0 = acc + y0, a1 = a0 + y1, a2 = a1 + y2, a3 = a2 + y3;
-                    y[0] = a0; y[-B9] = a1; y[-2 * B9] = a2; y[-3 * B9] = a3;
-                    acc = a3;
-                    y -= 4 * B9;
-                }
-                for (; f > 0; --f) {
-                    acc += *y;
-                    *y = acc;
-                    y -= B9;
-                }
-            }
-        }
-        TILE_CLOCK(9)
-        while (!mbar_try_wait(bars + 2, it & 1u)) {}
-        TILE_CLOCK(10)
-        __syncthreads();   // #7
-        TILE_CLOCK(11)
-        // ---- phase E: omega[t] = R[t] z[t]; tangent-form Gram-Schmidt backward -> gradient records over the 6-D
-        //      records (which now live in the two target regions); one bone per task
+        if (nxt < ntiles && warp == W - 1) fill_rows(nxt, (it + 1) & 1);
+        // ---- per bone, all independent:  m_b = Sx_b - Sg_b x t_b,  y_b = A_parent m_b,  z[t] = sum_{s >= t} y[s] over
+        //      the frames of the clip (lanes are frames: a segmented suffix scan over shuffles),  omega = R[t] z[t],
+        //      tangent-form Gram-Schmidt backward -> gradient records over the 6-D records (which now live in the two
+        //      target regions)
         {
-            const int nt = slices * B;
 #pragma unroll 1
-            for (int task = warp; task < nt; task += W) {
-                const int slice = task >= B ? 1 : 0, b = task - slice * B;
-                const int col = slice * 32 + lane, pl = min(col, np - 1);
-                float d[6], o[6];
-                lds6(G3 + pl * B6, b, d);
-                const M3 Rb = lds9(R + pl * B9, b);
-                const V3 z = lds3(A + pl * B9 + 6 * b, b);   // words 0..2 of the 9-word slot b (3 b + 6 b = 9 b)
-                const V3 om = v3_mul_mt(z, Rb);
-                gram_schmidt_bwd_tangent(gram_schmidt(d), om, o);
-                if (col < np) sts6(G3 + pl * B6, b, o);
+            for (int b = warp; b < B; b += W) {
+                const int par = a.parent[b];
+                V3 later{0.f, 0.f, 0.f};   // sum over the later slice of the same clip (clips longer than 32 frames)
+#pragma unroll 1
+                for (int sl = slices - 1; sl >= 0; --sl) {
+                    const int col = sl * 32 + lane, pl = min(col, np - 1);
+                    const bool valid = col < np;
+                    const V3 sx{XR[(b * 3) * PS + col], XR[(b * 3 + 1) * PS + col], XR[(b * 3 + 2) * PS + col]};
+                    const V3 sg{GV[(b * 3) * PS + col], GV[(b * 3 + 1) * PS + col], GV[(b * 3 + 2) * PS + col]};
+                    const V3 t{TS[(b * 3) * PS + col], TS[(b * 3 + 1) * PS + col], TS[(b * 3 + 2) * PS + col]};
+                    const V3 mv{sx.x - (sg.y * t.z - sg.z * t.y), sx.y - (sg.z * t.x - sg.x * t.z),
+                                sx.z - (sg.x * t.y - sg.y * t.x)};
+                    V3 z = mv;
+                    if (par >= 0) z = v3_mul_mt(mv, lds9(A + pl * B9, par));
+                    if (!valid) z = V3{0.f, 0.f, 0.f};
+                    if (a.scan) {
+                        const int fr = slices == 1 ? col % L : col;   // frame of this lane within its clip
+#pragma unroll
+                        for (int off = 1; off < 32; off <<= 1) {
+                            const float vx = __shfl_down_sync(FULL_MASK, z.x, off), vy = __shfl_down_sync(FULL_MASK, z.y, off),
+                                        vz = __shfl_down_sync(FULL_MASK, z.z, off);
+                            if (lane + off < 32 && fr + off < L) { z.x += vx; z.y += vy; z.z += vz; }
+                        }
+                        if (slices > 1) {
+                            z.x += later.x; z.y += later.y; z.z += later.z;
+                            later = V3{__shfl_sync(FULL_MASK, z.x, 0), __shfl_sync(FULL_MASK, z.y, 0),
+                                       __shfl_sync(FULL_MASK, z.z, 0)};
+                        }
+                    }
+                    float d[6], o[6];
+                    lds6(G3 + pl * B6, b, d);
+                    const V3 om = v3_mul_mt(z, lds9(R + pl * B9, b));
+                    gram_schmidt_bwd_tangent(gram_schmidt(d), om, o);
+                    if (valid) sts6(G3 + pl * B6, b, o);
+                }
             }
         }
         fence_async_smem();
@@ -833,7 +820,8 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         if (tma) {
             bulk_s2g(a.g_d6 + (size_t)m0 * B6, G3, (uint32_t)(np * B6) * 4u);
             bulk_commit();
-            bulk_wait_read_all();   // the gradient has left the target regions: the next tile's targets may land
+            if (nxt < ntiles) load_d6(nxt);   // the scratch region is free
+            bulk_wait_read_all();             // the gradient has left the target regions: the next tile's targets may land
             if (nxt < ntiles) load_targets(nxt);
         }
     }
@@ -930,6 +918,29 @@ bool tree_tables(const p2c_tree_t& t, TileArgs& a) {
     return true;
 }
 
+// forward-walk schedule: per level 3 * bones * slices column tasks, laid out in rounds of W warps
+int build_fk(TileArgs& a, int W, int slices, bool fill) {
+    int rounds = 0;
+    for (int l = 0; l < a.nlevels; ++l) {
+        const int s0 = a.lvl_start[l], cnt = a.lvl_start[l + 1] - s0, tasks = cnt * 3 * slices;
+        const int nr = (tasks + W - 1) / W;
+        if ((rounds + nr) * W > MAX_FK_DESC) return -1;
+        if (fill) {
+            for (int i = 0; i < nr * W; ++i) {
+                unsigned e = 0;
+                if (i < tasks) {   // task order: slice, bone of the level, column
+                    const int slice = i / (cnt * 3), rem = i - slice * cnt * 3, b = a.order[s0 + rem / 3], j = rem % 3;
+                    e = (unsigned)b | ((unsigned)(a.parent[b] + 1) << 5) | ((unsigned)j << 11) | ((unsigned)slice << 13) | 0x4000u;
+                }
+                if (i / W == nr - 1) e |= 0x8000u;
+                a.fk_desc[(rounds + i / W) * W + i % W] = (uint16_t)e;
+            }
+        }
+        rounds += nr;
+    }
+    return rounds;
+}
+
 struct TileLaunch {
     int ok, P, PS, slices, threads, tree_warps, grid, count_inline;
     size_t smem;
@@ -964,15 +975,16 @@ TileLaunch make_launch(const p2c_fused_step_t* p, const TileArgs& a) {   // a: t
     if (warps < 4) warps = 4;
     if (warps > MAX_THREADS / 32) warps = MAX_THREADS / 32;
     t.threads = warps * 32;
-    t.tree_warps = a.tree_warps * t.slices;   // one task per tree warp and level
-    if (t.tree_warps > warps) return t;       // (very wide trees take the bone-per-lane kernels)
-    t.smem = (size_t)tile_plan(t.PS, B, a.nlevels * t.tree_warps).total * sizeof(float);
+    if (warps < 6 * t.slices) return t;   // the subtree-sum walks take six warps per slice (tiny trees: other kernels)
+    t.tree_warps = 6 * t.slices;
+    t.smem = (size_t)tile_plan(t.PS, B).total * sizeof(float);
     const size_t cap = 227 * 1024;
     if (t.smem + 1024 > cap) return t;
     int per_sm = (int)((228 * 1024) / (t.smem + 1024));
     if (per_sm * t.threads > 896) per_sm = 896 / t.threads;   // 72 registers per thread (launch bounds 832 x 1)
     if (per_sm > 4) per_sm = 4;   // the workspace holds 2 x 592 loss partials
     if (per_sm < 1) per_sm = 1;
+    if (getenv("P2C_TILE_ONE_CTA") && getenv("P2C_TILE_ONE_CTA")[0] == '1') per_sm = 1;   // debug: no co-resident CTA
     const long slots = (long)sm_count() * per_sm;
     t.grid = (int)(ntiles < slots ? ntiles : slots);
     t.count_inline = lone ? 1 : 0;   // grid == ntiles <= SMs: every CTA is resident, the in-kernel wait cannot hang
