@@ -37,7 +37,6 @@
 namespace {
 
 constexpr int MAX_LEVELS = 24;
-constexpr int COUNT_BLOCKS = 296;
 constexpr int MAX_THREADS = 832;
 constexpr int MAX_FK_DESC = 352;
 
@@ -176,17 +175,14 @@ __device__ __forceinline__ void sts9(float* pose, int b, const M3& a) {
 }
 
 // utils/tensors.py:29-40 count of kept (joint, channel) pairs of the 2-D targets (integer => order independent)
-__global__ void __launch_bounds__(256) tile_count_kernel(const float* __restrict__ gt2, long poses, int B, int gt_c,
-                                                        int hips, int* __restrict__ count) {
+__global__ void __launch_bounds__(256) tile_count_kernel(const float* __restrict__ gt2, unsigned joints, unsigned B,
+                                                        unsigned gt_c, unsigned hips, int* __restrict__ count) {
     int c = 0;
-    const long n = poses * B;
-    for (long i = (long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long)gridDim.x * 256) {
-        const int j = (int)(i % B);
-        const float* g = gt2 + i * gt_c;
-        if (j == hips || (__ldg(g) != 0.f && __ldg(g + 1) != 0.f)) c += 2;
+    for (unsigned i = blockIdx.x * 256u + threadIdx.x; i < joints; i += gridDim.x * 256u) {
+        const float* g = gt2 + (size_t)i * gt_c;
+        if (i % B == hips || (__ldg(g) != 0.f && __ldg(g + 1) != 0.f)) c += 2;
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(FULL_MASK, c, o);
+    c = __reduce_add_sync(FULL_MASK, c);
     __shared__ int sh[8];
     if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = c;
     __syncthreads();
@@ -240,7 +236,7 @@ __device__ __host__ __forceinline__ TilePlan tile_plan(int PS, int B) {
     s.g2 = o; o += PS * B * 3;
     s.r = o; o += PS * B * 9;
     s.a = o; o += PS * B * 9;
-    s.nrm = o; o += 8 * PS;            // sx, sy, dx, dy, inv, ok per pose
+    s.nrm = o; o += 10 * PS;           // sx, sy, dx, dy, inv, ok, then the three normaliser sums, per pose
     s.part = o; o += B * 3 * PS;       // per bone: gx, gy, gx x + gy y per pose (normaliser backward), then Sx rows
     s.row = o; o += 2 * PS;            // skeleton-table row per pose, double buffered (next tile's rows prefetched)
     s.red = o; o += 2 * 32;            // loss partials per warp
@@ -592,29 +588,46 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             const float* lc = GV + col;
             float* tr = TS + jc * PS + col;
             float c0 = 0.f, c1 = 0.f, c2 = 0.f, ct = 0.f;   // column jc of A_{b-1}, component jc of t_{b-1}
-#pragma unroll 2
-            for (int b = 0; b < B; ++b) {
-                const int par = a.parent[b];
-                const float r0 = rb[0], r1 = rb[1], r2 = rb[2], r3 = rb[3], r4 = rb[4], r5 = rb[5], r6 = rb[6],
-                            r7 = rb[7], r8 = rb[8];
-                const float l0 = lc[0], l1 = lc[PS], l2 = lc[2 * PS];
+            // two bones per trip (B is even); the inputs of the next bone (its rel_rot record, its offset, its parent)
+            // are fetched into the other register set while this one is computed
+            float u[12], w[12];
+            int pu, pw;
+            auto fetch = [&](float* x, int b) {
+#pragma unroll
+                for (int i = 0; i < 9; ++i) x[i] = rb[9 * b + i];
+                x[9] = lc[(3 * b) * PS]; x[10] = lc[(3 * b + 1) * PS]; x[11] = lc[(3 * b + 2) * PS];
+            };
+            auto bone = [&](const float* x, int b, int par) {
                 float p0 = c0, p1 = c1, p2 = c2, tp = ct;
-                if (par >= 0 && par != b - 1) {
-                    const float* ap = A + pl * B9 + par * 9 + jc;
-                    p0 = ap[0]; p1 = ap[3]; p2 = ap[6];
-                    tp = TS[(par * 3 + jc) * PS + col];
+                if (par != b - 1 || par < 0) {
+                    if (par >= 0) {
+                        const float* ap = A + pl * B9 + par * 9 + jc;
+                        p0 = ap[0]; p1 = ap[3]; p2 = ap[6];
+                        tp = TS[(par * 3 + jc) * PS + col];
+                    } else {   // root: the parent transform is the identity
+                        p0 = jc == 0 ? 1.f : 0.f; p1 = jc == 1 ? 1.f : 0.f; p2 = jc == 2 ? 1.f : 0.f;
+                        tp = 0.f;
+                    }
                 }
-                if (par < 0) {   // root: the parent transform is the identity
-                    p0 = jc == 0 ? 1.f : 0.f; p1 = jc == 1 ? 1.f : 0.f; p2 = jc == 2 ? 1.f : 0.f;
-                    tp = 0.f;
+                c0 = fmaf(x[2], p2, fmaf(x[1], p1, x[0] * p0));
+                c1 = fmaf(x[5], p2, fmaf(x[4], p1, x[3] * p0));
+                c2 = fmaf(x[8], p2, fmaf(x[7], p1, x[6] * p0));
+                ct = fmaf(x[11], p2, fmaf(x[10], p1, x[9] * p0)) + tp;
+                if (valid) { ab[9 * b] = c0; ab[9 * b + 3] = c1; ab[9 * b + 6] = c2; }
+                tr[(3 * b) * PS] = ct;
+            };
+            fetch(u, 0);
+            pu = a.parent[0];
+#pragma unroll 1
+            for (int b = 0; b < B; b += 2) {
+                fetch(w, b + 1);
+                pw = a.parent[b + 1];
+                bone(u, b, pu);
+                if (b + 2 < B) {
+                    fetch(u, b + 2);
+                    pu = a.parent[b + 2];
                 }
-                c0 = fmaf(r2, p2, fmaf(r1, p1, r0 * p0));
-                c1 = fmaf(r5, p2, fmaf(r4, p1, r3 * p0));
-                c2 = fmaf(r8, p2, fmaf(r7, p1, r6 * p0));
-                ct = fmaf(l2, p2, fmaf(l1, p1, l0 * p0)) + tp;
-                if (valid) { ab[0] = c0; ab[3] = c1; ab[6] = c2; }
-                tr[0] = ct;
-                rb += 9; ab += 9; lc += 3 * PS; tr += 3 * PS;
+                bone(w, b + 1, pw);
             }
             fence_async_smem();
         }
@@ -701,62 +714,72 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             mbar_expect_tx(bars + 2, (uint32_t)(np * B6) * 4u);
             bulk_g2s(G3, a.d6 + (size_t)m0 * B6, (uint32_t)(np * B6) * 4u, bars + 2);
         }
-        // ---- normaliser backward through shift (hips) and scale (|neck - hips|): it needs the sums over all bones, and
-        //      lands on g_hips and g_neck before the subtree sums are formed
+        // ---- normaliser backward through shift (hips) and scale (|neck - hips|): it needs the sums over all bones
+        //      (three warps per slice, one per sum), and lands on g_hips and g_neck before the subtree sums are formed
         if (a.normalize) {
-            if (warp < slices) {
-                const int col = warp * 32 + lane, pl = min(col, np - 1), m = m0 + pl;
-                float sgx = 0.f, sgy = 0.f, sgn = 0.f;
-#pragma unroll 2
-                for (int q = 0; q < B; ++q) {
-                    sgx += PART[(q * 3) * PS + col];
-                    sgy += PART[(q * 3 + 1) * PS + col];
-                    sgn += PART[(q * 3 + 2) * PS + col];
-                }
-                const float inv = NRM[5 * PS + col] != 0.f ? NRM[4 * PS + col] : 0.f;
-                const float gs = -sgn * inv * inv;   // dL/dscale . (1/scale)
-                const float kx = gs * NRM[2 * PS + col], ky = gs * NRM[3 * PS + col];
+            if (warp < 3 * slices) {
+                const int k = warp % 3, col = (warp / 3) * 32 + lane;
+                float s0_ = 0.f, s1_ = 0.f;
 #pragma unroll 1
-                for (int which = 0; which < 2; ++which) {
-                    const int b = which ? a.neck : a.hips;
-                    float cx = 0.f, cy = 0.f;   // (hips == neck would get both terms)
+                for (int q = 0; q + 1 < B; q += 2) {
+                    s0_ += PART[(q * 3 + k) * PS + col];
+                    s1_ += PART[(q * 3 + 3 + k) * PS + col];
+                }
+                NRM[(6 + k) * PS + col] = s0_ + s1_;   // (B is even)
+            }
+            __syncthreads();   // #5a
+        }
+        // ---- own parts of the subtree sums, one bone per task: g_b x t_b -> rows XR (the former partial-sum rows)
+        float* XR = PART;
+        {
+            const int nt = slices * B;
+#pragma unroll 1
+            for (int task = warp; task < nt; task += W) {
+                const int slice = task >= B ? 1 : 0, b = task - slice * B;
+                const int col = slice * 32 + lane;
+                const V3 t{TS[(b * 3) * PS + col], TS[(b * 3 + 1) * PS + col], TS[(b * 3 + 2) * PS + col]};
+                V3 g{GV[(b * 3) * PS + col], GV[(b * 3 + 1) * PS + col], GV[(b * 3 + 2) * PS + col]};
+                if (a.normalize && (b == a.hips || b == a.neck)) {
+                    const int m = m0 + min(col, np - 1);
+                    const float sgx = NRM[6 * PS + col], sgy = NRM[7 * PS + col], sgn = NRM[8 * PS + col];
+                    const float inv = NRM[5 * PS + col] != 0.f ? NRM[4 * PS + col] : 0.f;
+                    const float gs = -sgn * inv * inv;   // dL/dscale . (1/scale)
+                    const float kx = gs * NRM[2 * PS + col], ky = gs * NRM[3 * PS + col];
+                    float cx = 0.f, cy = 0.f;
                     if (b == a.neck) { cx += kx; cy += ky; }
                     if (b == a.hips) { cx -= fmaf(sgx, inv, kx); cy -= fmaf(sgy, inv, ky); }
-                    if (which && a.neck == a.hips) break;
-                    const V3 t{TS[(b * 3) * PS + col], TS[(b * 3 + 1) * PS + col], TS[(b * 3 + 2) * PS + col]};
                     const V3 gp = project_bwd<WORLD>(a, project<WORLD>(a, t, m), cx, cy, m);
-                    GV[(b * 3) * PS + col] += gp.x; GV[(b * 3 + 1) * PS + col] += gp.y; GV[(b * 3 + 2) * PS + col] += gp.z;
+                    g.x += gp.x; g.y += gp.y; g.z += gp.z;
+                    GV[(b * 3) * PS + col] = g.x; GV[(b * 3 + 1) * PS + col] = g.y; GV[(b * 3 + 2) * PS + col] = g.z;
                 }
+                XR[(b * 3) * PS + col] = g.y * t.z - g.z * t.y;
+                XR[(b * 3 + 1) * PS + col] = g.z * t.x - g.x * t.z;
+                XR[(b * 3 + 2) * PS + col] = g.x * t.y - g.y * t.x;
             }
-            __syncthreads();   // #5b
         }
+        __syncthreads();   // #5b
 
         // ---- subtree sums, leaves first (the bone order has parents before children, so a walk in reverse bone order
-        //      meets every child before its parent):  Sx_b = sum_{d in subtree(b)} g_d x t_d (rows XR, the former
-        //      partial-sum rows), Sg_b = sum g_d (in place over g_b).  The six components are independent: one warp
-        //      each per slice, no barrier inside the walk, the running value stays in a register along chains.
-        float* XR = PART;
+        //      meets every child before its parent):  Sx_b = sum_{d in subtree(b)} g_d x t_d (rows XR), Sg_b = sum g_d
+        //      (in place over g_b).  The six components are independent: one warp each per slice, no barrier inside
+        //      the walk, the running value stays in a register along chains.
         if (warp < 6 * slices) {
             const int k = warp % 6, col = (warp / 6) * 32 + lane;
-            // own parts g_b x t_b first (they read g_b, which the Sg walks are about to overwrite): 78 rows over 6 warps
-            for (int rw = k; rw < B3; rw += 6) {
-                const int b = rw / 3, c = rw - 3 * b, c1 = c == 2 ? 0 : c + 1, c2 = c == 0 ? 2 : c - 1;
-                const float* g = GV + (b * 3) * PS + col;
-                const float* t = TS + (b * 3) * PS + col;
-                XR[rw * PS + col] = g[c1 * PS] * t[c2 * PS] - g[c2 * PS] * t[c1 * PS];
-            }
-            named_barrier(1, 6 * slices * 32);
             float* rowp = (k < 3 ? XR + k * PS : GV + (k - 3) * PS) + col;
             float carry = 0.f;
             bool have = false;
+            float nv = rowp[(B - 1) * 3 * PS];
+            int npar = a.parent[B - 1];
 #pragma unroll 1
             for (int c = B - 1; c >= 1; --c) {
-                float v = rowp[c * 3 * PS];
+                float v = nv;
+                const int par = npar;
+                nv = rowp[(c - 1) * 3 * PS];   // (row c-1 is not touched in this trip unless it is the parent; see below)
+                npar = a.parent[c - 1];
                 if (have) {
                     v += carry;
                     rowp[c * 3 * PS] = v;
                 }
-                const int par = a.parent[c];
                 if (par == c - 1) {
                     carry = v;
                     have = true;
@@ -765,7 +788,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                     have = false;
                 }
             }
-            if (have) rowp[0] += carry;
+            if (have) rowp[0] = nv + carry;
         }
         while (!mbar_try_wait(bars + 2, it & 1u)) {}
         __syncthreads();   // #6
@@ -796,6 +819,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                         const int fr = slices == 1 ? col % L : col;   // frame of this lane within its clip
 #pragma unroll
                         for (int off = 1; off < 32; off <<= 1) {
+                            if (off >= L) break;
                             const float vx = __shfl_down_sync(FULL_MASK, z.x, off), vy = __shfl_down_sync(FULL_MASK, z.y, off),
                                         vz = __shfl_down_sync(FULL_MASK, z.z, off);
                             if (lane + off < 32 && fr + off < L) { z.x += vx; z.y += vy; z.z += vz; }
@@ -961,7 +985,7 @@ TileLaunch make_launch(const p2c_fused_step_t* p, const TileArgs& a) {   // a: t
     // pose record is an even, not a multiple-of-four, count) and 16-byte aligned tensors; anything else takes the
     // bone-per-lane kernels of fused_fast.cu, which also copy cooperatively
     if ((t.P & 1) || (total & 1)) return t;
-    if (total > (1L << 30)) return t;   // pose indices are 32-bit inside the kernel
+    if (total > (1L << 26)) return t;   // pose and joint indices are 32-bit inside the kernels
     const void* ptrs[] = {p->pose_in, p->gt_2d, p->gt_3d, p->g_pose_in, p->rel_rot, p->abs_rot, p->abs_loc, p->proj};
     for (const void* q : ptrs)
         if (reinterpret_cast<uintptr_t>(q) & 15) return t;
@@ -1050,8 +1074,9 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     cudaStream_t st = (cudaStream_t)stream;
     if (a.mask && !a.count_inline) {
         long blocks = (total * B + 255) / 256;
-        if (blocks > COUNT_BLOCKS) blocks = COUNT_BLOCKS;
-        tile_count_kernel<<<(int)blocks, 256, 0, st>>>(p->gt_2d, total, B, p->gt_2d_channels, p->hips, a.count2);
+        if (blocks > 4 * 148 * 8) blocks = 4 * 148 * 8;
+        tile_count_kernel<<<(int)blocks, 256, 0, st>>>(p->gt_2d, (unsigned)(total * B), (unsigned)B,
+                                                       (unsigned)p->gt_2d_channels, (unsigned)p->hips, a.count2);
         P2C_LAUNCH_CHECK();
     }
     typedef void (*kern_t)(const TileArgs);

@@ -15,7 +15,7 @@ lib = _lib.load()
 lib.p2c_debug_tile_clocks.argtypes = [ctypes.c_void_p]
 assert lib.p2c_debug_tile_clocks(buf) == 0
 names = ['top', 'd6 landed', 'bar1', 'A done(bar2)', 'B done(bar3)', 'FK done(bar4)', 'shift/scale + targets(bar4b)',
-         'loss done(bar5)', 'subtree sums done(bar6)', 'E done(bar8)']
+         'loss done(bar5)', 'norm bwd + subtree sums(bar6)', 'E done(bar8)']
 v = list(buf)
 v = v[:9] + [v[12]]
 for i in range(1, 10):
