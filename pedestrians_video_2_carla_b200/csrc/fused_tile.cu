@@ -794,27 +794,42 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         __syncthreads();   // #6
         TILE_CLOCK(8)
         if (nxt < ntiles && warp == W - 1) fill_rows(nxt, (it + 1) & 1);
-        // ---- per bone, all independent:  m_b = Sx_b - Sg_b x t_b,  y_b = A_parent m_b,  z[t] = sum_{s >= t} y[s] over
-        //      the frames of the clip (lanes are frames: a segmented suffix scan over shuffles),  omega = R[t] z[t],
-        //      tangent-form Gram-Schmidt backward -> gradient records over the 6-D records (which now live in the two
-        //      target regions)
+        // ---- per bone, all independent:  m_b = Sx_b - Sg_b x t_b,  y_b = A_parent m_b  (in place over Sx_b).  After this
+        //      pass the scratch rows (t, Sg) and the abs_rot records are dead, so the next tile's 6-D records can start
+        //      their way in while the gradient pass runs.
+        {
+            const int nt = slices * B;
+#pragma unroll 1
+            for (int task = warp; task < nt; task += W) {
+                const int sl = task >= B ? 1 : 0, b = task - sl * B, par = a.parent[b];
+                const int col = sl * 32 + lane, pl = min(col, np - 1);
+                const V3 sx{XR[(b * 3) * PS + col], XR[(b * 3 + 1) * PS + col], XR[(b * 3 + 2) * PS + col]};
+                const V3 sg{GV[(b * 3) * PS + col], GV[(b * 3 + 1) * PS + col], GV[(b * 3 + 2) * PS + col]};
+                const V3 t{TS[(b * 3) * PS + col], TS[(b * 3 + 1) * PS + col], TS[(b * 3 + 2) * PS + col]};
+                const V3 mv{sx.x - (sg.y * t.z - sg.z * t.y), sx.y - (sg.z * t.x - sg.x * t.z),
+                            sx.z - (sg.x * t.y - sg.y * t.x)};
+                V3 y = mv;
+                if (par >= 0) y = v3_mul_mt(mv, lds9(A + pl * B9, par));
+                if (col >= np) y = V3{0.f, 0.f, 0.f};
+                XR[(b * 3) * PS + col] = y.x; XR[(b * 3 + 1) * PS + col] = y.y; XR[(b * 3 + 2) * PS + col] = y.z;
+            }
+        }
+        fence_async_smem();   // (the scratch rows are about to be overwritten by TMA)
+        __syncthreads();   // #7
+        TILE_CLOCK(9)
+        if (tma && nxt < ntiles) load_d6(nxt);
+        // ---- z[t] = sum_{s >= t} y[s] over the frames of the clip (lanes are frames: a segmented suffix scan over
+        //      shuffles),  omega = R[t] z[t],  tangent-form Gram-Schmidt backward -> gradient records over the 6-D
+        //      records (which now live in the two target regions)
         {
 #pragma unroll 1
             for (int b = warp; b < B; b += W) {
-                const int par = a.parent[b];
                 V3 later{0.f, 0.f, 0.f};   // sum over the later slice of the same clip (clips longer than 32 frames)
 #pragma unroll 1
                 for (int sl = slices - 1; sl >= 0; --sl) {
                     const int col = sl * 32 + lane, pl = min(col, np - 1);
                     const bool valid = col < np;
-                    const V3 sx{XR[(b * 3) * PS + col], XR[(b * 3 + 1) * PS + col], XR[(b * 3 + 2) * PS + col]};
-                    const V3 sg{GV[(b * 3) * PS + col], GV[(b * 3 + 1) * PS + col], GV[(b * 3 + 2) * PS + col]};
-                    const V3 t{TS[(b * 3) * PS + col], TS[(b * 3 + 1) * PS + col], TS[(b * 3 + 2) * PS + col]};
-                    const V3 mv{sx.x - (sg.y * t.z - sg.z * t.y), sx.y - (sg.z * t.x - sg.x * t.z),
-                                sx.z - (sg.x * t.y - sg.y * t.x)};
-                    V3 z = mv;
-                    if (par >= 0) z = v3_mul_mt(mv, lds9(A + pl * B9, par));
-                    if (!valid) z = V3{0.f, 0.f, 0.f};
+                    V3 z{XR[(b * 3) * PS + col], XR[(b * 3 + 1) * PS + col], XR[(b * 3 + 2) * PS + col]};
                     if (a.scan) {
                         const int fr = slices == 1 ? col % L : col;   // frame of this lane within its clip
 #pragma unroll
@@ -844,7 +859,6 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         if (tma) {
             bulk_s2g(a.g_d6 + (size_t)m0 * B6, G3, (uint32_t)(np * B6) * 4u);
             bulk_commit();
-            if (nxt < ntiles) load_d6(nxt);   // the scratch region is free
             bulk_wait_read_all();             // the gradient has left the target regions: the next tile's targets may land
             if (nxt < ntiles) load_targets(nxt);
         }

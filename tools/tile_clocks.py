@@ -1,6 +1,6 @@
 """Phase timeline of the tile kernel (CTA 0, second tile): P2C_TILE_CLOCKS=1 python tools/tile_clocks.py N L"""
 import ctypes, os, sys
-os.environ['P2C_TILE_CLOCKS'] = '1'
+os.environ.setdefault('P2C_TILE_CLOCKS', '2')
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import bench
@@ -15,9 +15,9 @@ lib = _lib.load()
 lib.p2c_debug_tile_clocks.argtypes = [ctypes.c_void_p]
 assert lib.p2c_debug_tile_clocks(buf) == 0
 names = ['top', 'd6 landed', 'bar1', 'A done(bar2)', 'B done(bar3)', 'FK done(bar4)', 'shift/scale + targets(bar4b)',
-         'loss done(bar5)', 'norm bwd + subtree sums(bar6)', 'E done(bar8)']
+         'loss done(bar5)', 'norm bwd + subtree sums(bar6)', 'y done(bar7)', 'E done(bar8)']
 v = list(buf)
-v = v[:9] + [v[12]]
-for i in range(1, 10):
+v = v[:10] + [v[12]]
+for i in range(1, 11):
     print('%-30s +%6d cycles' % (names[i], v[i] - v[i - 1]))
-print('tile total %d cycles' % (v[9] - v[0]))
+print('tile total %d cycles' % (v[10] - v[0]))
