@@ -45,7 +45,7 @@ struct TileArgs {
     int hips, neck, normalize, mask, nlevels, npairs;
     int tree_warps;   // warps that take part in the level-synchronous tree phases
     int count_inline; // every CTA owns exactly one tile: the mask count happens inside the kernel (no pre-pass)
-    int clocks;       // debug (P2C_TILE_CLOCKS=1): CTA 0 records clock64() at every phase boundary of its second tile
+    int clocks;       // debug (P2C_TILE_CLOCKS=n): CTA 0 records clock64() at every phase boundary of its n-th tile
     int fk_rounds;    // rounds of W column tasks in the forward tree walk
     uint16_t fk_desc[MAX_FK_DESC];
     int8_t parent[P2C_MAX_BONES];
@@ -144,21 +144,13 @@ __device__ __forceinline__ float2 lds64(const float* p) {
 __device__ __forceinline__ void sts64(float* p, float x, float y) {
     asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(smem_u32(p)), "f"(x), "f"(y) : "memory");
 }
-// 9-word bone record b of an AoS pose record whose base is 8-byte aligned: 64-bit accesses around the odd word
+// 9-word bone record b of an AoS pose record, read with scalar loads: the 64-bit form needs both parities of b
+// spelled out under predicates, which costs more issue slots than the 2-way bank conflicts of the scalar form
 __device__ __forceinline__ M3 lds9(const float* pose, int b) {
     const float* p = pose + 9 * b;
     M3 r;
-    if (b & 1) {
-        r.m[0] = p[0];
-        const float2 x0 = lds64(p + 1), x1 = lds64(p + 3), x2 = lds64(p + 5), x3 = lds64(p + 7);
-        r.m[1] = x0.x; r.m[2] = x0.y; r.m[3] = x1.x; r.m[4] = x1.y;
-        r.m[5] = x2.x; r.m[6] = x2.y; r.m[7] = x3.x; r.m[8] = x3.y;
-    } else {
-        const float2 x0 = lds64(p), x1 = lds64(p + 2), x2 = lds64(p + 4), x3 = lds64(p + 6);
-        r.m[0] = x0.x; r.m[1] = x0.y; r.m[2] = x1.x; r.m[3] = x1.y;
-        r.m[4] = x2.x; r.m[5] = x2.y; r.m[6] = x3.x; r.m[7] = x3.y;
-        r.m[8] = p[8];
-    }
+#pragma unroll
+    for (int i = 0; i < 9; ++i) r.m[i] = p[i];
     return r;
 }
 __device__ __forceinline__ void sts9(float* pose, int b, const M3& a) {
@@ -177,6 +169,9 @@ __device__ __forceinline__ void sts9(float* pose, int b, const M3& a) {
 // utils/tensors.py:29-40 count of kept (joint, channel) pairs of the 2-D targets (integer => order independent)
 __global__ void __launch_bounds__(256) tile_count_kernel(const float* __restrict__ gt2, unsigned joints, unsigned B,
                                                         unsigned gt_c, unsigned hips, int* __restrict__ count) {
+    // programmatic dependent launch: the step kernel may start its prologue, input loads and forward phases now; it
+    // executes griddepcontrol.wait (= this grid complete and flushed) before it reads the count
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     int c = 0;
     for (unsigned i = blockIdx.x * 256u + threadIdx.x; i < joints; i += gridDim.x * 256u) {
         const float* g = gt2 + (size_t)i * gt_c;
@@ -336,7 +331,7 @@ __device__ __forceinline__ V3 bone_loss(const TileArgs& a, int b, const V3& t, f
 
 __device__ long long g_tile_clocks[64];
 #define TILE_CLOCK(k)                                                              \
-    if (a.clocks && blockIdx.x == 0 && it == 1 && tid == 0) g_tile_clocks[k] = clock64();
+    if (a.clocks && blockIdx.x == 0 && (int)it == a.clocks - 1 && tid == 0) g_tile_clocks[k] = clock64();
 
 __device__ __forceinline__ void named_barrier(int id, int threads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
@@ -378,13 +373,7 @@ __device__ __forceinline__ void sts6(float* pose, int b, const float* d) {
 // 3-word bone record b of an 8-byte aligned AoS pose record (locations, projections, 3-channel targets)
 __device__ __forceinline__ V3 lds3(const float* pose, int b) {
     const float* p = pose + 3 * b;
-    if (b & 1) {
-        const float x = p[0];
-        const float2 u = lds64(p + 1);
-        return V3{x, u.x, u.y};
-    }
-    const float2 u = lds64(p);
-    return V3{u.x, u.y, p[2]};
+    return V3{p[0], p[1], p[2]};
 }
 __device__ __forceinline__ void sts3(float* pose, int b, const V3& v) {
     float* p = pose + 3 * b;
@@ -457,7 +446,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     if (warp == 0 && (int)blockIdx.x < ntiles) fill_rows(blockIdx.x, 0);
     __syncthreads();
 
-    float k2 = a.w2 * 2.0f / ((a.mask && !a.count_inline) ? (float)__ldcg(a.count2) : (float)total * (float)(B * 2));
+    float k2 = a.w2 * 2.0f / ((float)total * (float)(B * 2));   // (mask on: replaced below once the count is known)
     __shared__ int cta_count;
     __shared__ float k2_shared;
     if (a.mask && a.count_inline) {
@@ -485,11 +474,13 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     const float k3 = a.w3 * 2.0f / (float)a.count3;
     float s2 = 0.f, s3 = 0.f;
     unsigned it = 0;
+    const int clips_full = a.P / L;
 
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
         const int m0 = tile * a.P, nxt = tile + gridDim.x;
         const int np = min(a.P, total - m0);
         const int* row = ROW + (it & 1) * PS;
+        const int tile_clips = np == a.P ? clips_full : np / L;   // (only the last tile can be short)
         TILE_CLOCK(0)
         while (!mbar_try_wait(bars, it & 1u)) {}
         TILE_CLOCK(1)
@@ -520,7 +511,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         // ---- phase B: R[t] = C[t] . R[t-1] (p3d_pose.py:98-114 looped by layers/projection.py:190-193); one thread
         //      per (clip, bone, column of R), serial over the frames of the clip
         if (a.scan) {
-            const int items = (np / L) * B3;
+            const int items = tile_clips * B3;
 #pragma unroll 1
             for (int idx = tid; idx < items; idx += NT) {
                 const int cl = idx / B3, rem = idx - cl * B3, b = rem / 3, j = rem - b * 3;
@@ -562,7 +553,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         // bone offsets of every pose's skeleton as SoA rows (row 3b+k, column = pose) in the upper half of the scratch
         // region: the forward walk reads them conflict free instead of going to the table in global memory
         {
-            const int busy = (a.scan && (np / L) * B3 <= 160 && NT >= 256) ? 160 : 0;   // threads that ran the scan
+            const int busy = (a.scan && tile_clips * B3 <= 160 && NT >= 256) ? 160 : 0;   // threads that ran the scan
             for (int i = tid - busy; i >= 0 && i < B3 * PS; i += NT - busy) {
                 const int k = i / PS, col = i - k * PS;
                 GV[i] = __ldg(a.ref_loc + (size_t)row[col] * B3 + k);
@@ -661,6 +652,10 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         while (!mbar_try_wait(bars + 1, it & 1u)) {}
         __syncthreads();   // #4b
         if (a.mask && a.count_inline) k2 = k2_shared;
+        if (a.mask && !a.count_inline && it == 0) {
+            asm volatile("griddepcontrol.wait;" ::: "memory");   // the count pre-pass (launched just before) is complete
+            k2 = a.w2 * 2.0f / (float)__ldcg(a.count2);
+        }
         TILE_CLOCK(6)
 
         // ---- projection, normaliser, loss terms, dL/d abs_loc; one bone per task; abs_loc and projection records are
@@ -1069,7 +1064,7 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     const int B = p->tree.n_bones;
     a.N = p->n_clips; a.L = p->clip_len; a.P = t.P; a.PS = t.PS; a.slices = t.slices;
     a.tree_warps = t.tree_warps;
-    a.clocks = env_on("P2C_TILE_CLOCKS");
+    a.clocks = getenv("P2C_TILE_CLOCKS") ? atoi(getenv("P2C_TILE_CLOCKS")) : 0;   // n: record the n-th tile of CTA 0
     a.scan = p->mode == P2C_MODE_POSE_CHANGES;
     a.hips = p->hips; a.neck = p->neck; a.normalize = p->normalize; a.mask = p->mask_missing_joints;
     a.d6 = p->pose_in; a.ref_loc = p->ref_loc; a.ref_rot = p->ref_rot; a.ref_index = p->ref_index;
@@ -1104,7 +1099,18 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
         if (e != cudaSuccess) return (int)e;
         configured[ki] = true;
     }
-    k<<<t.grid, t.threads, t.smem, st>>>(a);
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(t.grid);
+    cfg.blockDim = dim3(t.threads);
+    cfg.dynamicSmemBytes = t.smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = (a.mask && !a.count_inline) ? 1 : 0;   // overlap with the count pre-pass only
+    cudaError_t le = cudaLaunchKernelEx(&cfg, k, a);
+    if (le != cudaSuccess) return (int)le;
     P2C_LAUNCH_CHECK();
     return 0;
 }
