@@ -330,6 +330,8 @@ __device__ __forceinline__ V3 bone_loss(const TileArgs& a, int b, const V3& t, f
 }
 
 __device__ long long g_tile_clocks[64];
+#define CTA_CLOCK(k) \
+    if (a.clocks && blockIdx.x == 0 && threadIdx.x == 0) g_tile_clocks[k] = clock64();
 #define TILE_CLOCK(k)                                                              \
     if (a.clocks && blockIdx.x == 0 && (int)it == a.clocks - 1 && tid == 0) g_tile_clocks[k] = clock64();
 
@@ -395,6 +397,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     const int B = BT ? BT : a.B, slices = SL ? SL : a.slices;
     const int B3 = B * 3, B6 = B * 6, B9 = B * 9, PS = 32 * slices, L = a.L;
     const TilePlan sm = tile_plan(PS, B);
+    CTA_CLOCK(16)
     float* D = smem + sm.d;
     float* G3 = smem + sm.g3;     // G3 and G2 are adjacent: together they hold the re-fetched 6-D records
     float* G2 = smem + sm.g2;
@@ -444,36 +447,49 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         }
     }
     if (warp == 0 && (int)blockIdx.x < ntiles) fill_rows(blockIdx.x, 0);
+    __shared__ int cta_count;
+    __shared__ float k2_shared;
+    if (tid == 0) cta_count = 0;
     __syncthreads();
 
     float k2 = a.w2 * 2.0f / ((float)total * (float)(B * 2));   // (mask on: replaced below once the count is known)
-    __shared__ int cta_count;
-    __shared__ float k2_shared;
-    if (a.mask && a.count_inline) {
-        // utils/tensors.py:29-40: kept (joint, channel) pairs of this CTA's only tile, summed over the grid through
-        // one integer atomic per CTA (order independent); the loss pass waits for every CTA's part
-        if (tid == 0) cta_count = 0;
-        while (!mbar_try_wait(bars + 1, 0u)) {}
-        __syncthreads();
-        const int np0 = min(a.P, total - (int)blockIdx.x * a.P);
-        int c = 0;
-        for (int i = tid; i < np0 * B; i += NT) {
-            const int j = i % B;
-            const float* g = G2 + i * 3;
-            if (j == a.hips || (g[0] != 0.f && g[1] != 0.f)) c += 2;
-        }
-        c = __reduce_add_sync(FULL_MASK, c);
-        if (lane == 0 && c) atomicAdd(&cta_count, c);
-        __syncthreads();
-        if (tid == 0) {
-            if (cta_count) atomicAdd(a.count2, cta_count);
+    // ---- loss sums: per-CTA partials in fixed order; the last CTA to take a ticket folds them (one warp; called once
+    //      per CTA, after the loss pass of its last tile, while the backward phases run on the other warps)
+    auto publish = [&](float x, float y) {
+        bool lastw = false;
+        if (lane == 0) {
+            a.partials[blockIdx.x * 2] = x;
+            a.partials[blockIdx.x * 2 + 1] = y;
             __threadfence();
-            atomicAdd(a.arrive, 1u);
+            lastw = atomicAdd(a.ticket, 1u) == gridDim.x - 1;
         }
-    }
+        if (!__shfl_sync(FULL_MASK, lastw, 0)) return;
+        __threadfence();
+        double d2 = 0.0, d3 = 0.0;
+        for (int i = lane; i < (int)gridDim.x; i += 32) {
+            d2 += (double)__ldcg(a.partials + i * 2);
+            d3 += (double)__ldcg(a.partials + i * 2 + 1);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            d2 += __shfl_xor_sync(FULL_MASK, d2, o);
+            d3 += __shfl_xor_sync(FULL_MASK, d3, o);
+        }
+        if (lane == 0) {
+            const double c2 = a.mask ? (double)__ldcg(a.count2) : (double)total * B * 2;
+            const float l2 = (float)(d2 / c2), l3 = (float)(d3 / a.count3);
+            a.losses[0] = l2; a.losses[1] = l3; a.losses[2] = a.w2 * l2 + a.w3 * l3;
+            a.losses[3] = (float)d2; a.losses[4] = (float)c2; a.losses[5] = (float)d3; a.losses[6] = (float)a.count3;
+            a.losses[7] = 0.f;
+            *a.ticket = 0u;   // self-resetting workspace header: ready for the next launch
+            *a.count2 = 0;
+            *a.arrive = 0u;
+        }
+    };
     const float k3 = a.w3 * 2.0f / (float)a.count3;
     float s2 = 0.f, s3 = 0.f;
     unsigned it = 0;
+    CTA_CLOCK(17)
     const int clips_full = a.P / L;
 
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
@@ -621,6 +637,32 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 bone(w, b + 1, pw);
             }
             fence_async_smem();
+        } else if (a.mask && a.count_inline) {
+            // utils/tensors.py:29-40 (one tile per CTA): the warps without a column count the kept (joint, channel)
+            // pairs of this CTA's tile meanwhile; the grid total goes through one integer atomic per CTA (order
+            // independent) and the loss pass waits for every CTA's part
+            const int nc = NT - 3 * slices * 32, ci = tid - 3 * slices * 32;
+            while (!mbar_try_wait(bars + 1, it & 1u)) {}
+            int c = 0;
+            for (int i = ci; i < np * B; i += nc) {
+                const int j = i % B;
+                const float* g = G2 + i * 3;
+                if (j == a.hips || (g[0] != 0.f && g[1] != 0.f)) c += 2;
+            }
+            c = __reduce_add_sync(FULL_MASK, c);
+            if (lane == 0 && c) atomicAdd(&cta_count, c);
+            named_barrier(1, nc);
+            if (ci == 0) {
+                // count (low word) and arrivals (high word) travel in one 64-bit atomic; this lane then polls until
+                // every CTA of the grid has arrived (all CTAs are resident: one tile each, at most one CTA per SM)
+                unsigned long long* cw = reinterpret_cast<unsigned long long*>(a.count2);
+                atomicAdd(cw, (1ull << 32) | (unsigned long long)(unsigned)cta_count);
+                unsigned long long v;
+                do {
+                    v = *reinterpret_cast<volatile unsigned long long*>(cw);
+                } while ((unsigned)(v >> 32) < gridDim.x);
+                k2_shared = a.w2 * 2.0f / (float)(unsigned)(v & 0xffffffffull);
+            }
         }
         __syncthreads();   // #4
         TILE_CLOCK(5)
@@ -643,11 +685,6 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             NRM[3 * PS + col] = dy;
             NRM[4 * PS + col] = frcp(scale);
             NRM[5 * PS + col] = (scale > 0.f && scale <= 3.402823466e38f) ? 1.f : 0.f;
-        }
-        if (a.mask && a.count_inline && tid == 0) {
-            while (*reinterpret_cast<volatile unsigned int*>(a.arrive) < gridDim.x) {}
-            __threadfence();
-            k2_shared = a.w2 * 2.0f / (float)__ldcg(a.count2);
         }
         while (!mbar_try_wait(bars + 1, it & 1u)) {}
         __syncthreads();   // #4b
@@ -695,6 +732,11 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                     PART[(b * 3 + 2) * PS + col] = cx.sgn;
                 }
             }
+        }
+        if (nxt >= ntiles) {   // this CTA's last tile: its loss sums are complete
+            s2 = warp_sum(s2);
+            s3 = warp_sum(s3);
+            if (lane == 0) { red[warp * 2] = s2; red[warp * 2 + 1] = s3; }
         }
         fence_async_smem();
         if (tma) bulk_wait_read_all();   // rel_rot / abs_rot stores have read R and A
@@ -785,6 +827,12 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             }
             if (have) rowp[0] = nv + carry;
         }
+        if (nxt >= ntiles && warp == W - 2) {   // (a warp without a column when W >= 6 slices + 2: off the critical path)
+            float x = 0.f, y = 0.f;
+            if (lane == 0)
+                for (int w = 0; w < W; ++w) { x += red[w * 2]; y += red[w * 2 + 1]; }
+            publish(x, y);
+        }
         while (!mbar_try_wait(bars + 2, it & 1u)) {}
         __syncthreads();   // #6
         TILE_CLOCK(8)
@@ -858,46 +906,12 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             if (nxt < ntiles) load_targets(nxt);
         }
     }
+    CTA_CLOCK(18)
     if (tma) bulk_wait_all();
+    CTA_CLOCK(19)
 
-    // ---- loss sums: fixed-order reduction, the last CTA to finish folds the per-CTA partials
-    s2 = warp_sum(s2);
-    s3 = warp_sum(s3);
-    if (lane == 0) { red[warp * 2] = s2; red[warp * 2 + 1] = s3; }
-    __syncthreads();
-    __shared__ bool last;
-    if (tid == 0) {
-        float x = 0.f, y = 0.f;
-        for (int w = 0; w < W; ++w) { x += red[w * 2]; y += red[w * 2 + 1]; }
-        a.partials[blockIdx.x * 2] = x;
-        a.partials[blockIdx.x * 2 + 1] = y;
-        __threadfence();
-        last = (atomicAdd(a.ticket, 1u) == gridDim.x - 1);
-    }
-    __syncthreads();
-    if (last && warp == 0) {
-        __threadfence();
-        double d2 = 0.0, d3 = 0.0;
-        for (int i = lane; i < (int)gridDim.x; i += 32) {
-            d2 += (double)__ldcg(a.partials + i * 2);
-            d3 += (double)__ldcg(a.partials + i * 2 + 1);
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            d2 += __shfl_xor_sync(FULL_MASK, d2, o);
-            d3 += __shfl_xor_sync(FULL_MASK, d3, o);
-        }
-        if (lane == 0) {
-            const double c2 = a.mask ? (double)*a.count2 : (double)total * B * 2;
-            const float l2 = (float)(d2 / c2), l3 = (float)(d3 / a.count3);
-            a.losses[0] = l2; a.losses[1] = l3; a.losses[2] = a.w2 * l2 + a.w3 * l3;
-            a.losses[3] = (float)d2; a.losses[4] = (float)c2; a.losses[5] = (float)d3; a.losses[6] = (float)a.count3;
-            a.losses[7] = 0.f;
-            *a.ticket = 0u;   // self-resetting workspace header: ready for the next launch
-            *a.count2 = 0;
-            *a.arrive = 0u;
-        }
-    }
+    if (it == 0 && warp == W - 2) publish(0.f, 0.f);   // (a CTA without a tile still takes its ticket)
+    CTA_CLOCK(20)
 }
 
 int g_sms = 0;
@@ -998,6 +1012,7 @@ TileLaunch make_launch(const p2c_fused_step_t* p, const TileArgs& a) {   // a: t
     const void* ptrs[] = {p->pose_in, p->gt_2d, p->gt_3d, p->g_pose_in, p->rel_rot, p->abs_rot, p->abs_loc, p->proj};
     for (const void* q : ptrs)
         if (reinterpret_cast<uintptr_t>(q) & 15) return t;
+    if (reinterpret_cast<uintptr_t>(p->workspace) & 7) return t;   // (64-bit counter word in the header)
     t.PS = (t.P + 31) & ~31;
     t.slices = t.PS / 32;
     const long ntiles = (total + t.P - 1) / t.P;
@@ -1073,8 +1088,8 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     a.rel_rot = p->rel_rot; a.abs_rot = p->abs_rot; a.abs_loc = p->abs_loc; a.proj = p->proj;
     a.proj_norm = p->proj_norm; a.g_d6 = p->g_pose_in;
     a.ticket = reinterpret_cast<unsigned int*>(p->workspace);
-    a.count2 = reinterpret_cast<int*>(p->workspace) + 1;
-    a.arrive = reinterpret_cast<unsigned int*>(p->workspace) + 2;
+    a.count2 = reinterpret_cast<int*>(p->workspace) + 2;             // (8-byte aligned: count2 and arrive are also
+    a.arrive = reinterpret_cast<unsigned int*>(p->workspace) + 3;    //  updated together as one 64-bit word)
     a.count_inline = t.count_inline;
     a.partials = p->workspace + 16;
     a.losses = p->losses;

@@ -21,3 +21,7 @@ v = v[:10] + [v[12]]
 for i in range(1, 11):
     print('%-30s +%6d cycles' % (names[i], v[i] - v[i - 1]))
 print('tile total %d cycles' % (v[10] - v[0]))
+w = list(buf)
+if w[16]:
+    print('CTA 0: entry -> tile loop %d, tile loop %d, store drain %d, loss fold + ticket %d cycles' % (
+        w[17] - w[16], w[18] - w[17], w[19] - w[18], w[20] - w[19]))
