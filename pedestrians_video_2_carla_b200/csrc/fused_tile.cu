@@ -36,23 +36,14 @@
 
 namespace {
 
-constexpr int MAX_LEVELS = 24;
 constexpr int MAX_THREADS = 832;
-constexpr int MAX_FK_DESC = 352;
 
 struct TileArgs {
     int N, L, B, P, PS, slices, scan;   // clips, frames per clip, bones, poses per tile, P rounded up to 32, PS/32
-    int hips, neck, normalize, mask, nlevels, npairs;
-    int tree_warps;   // warps that take part in the level-synchronous tree phases
+    int hips, neck, normalize, mask;
     int count_inline; // every CTA owns exactly one tile: the mask count happens inside the kernel (no pre-pass)
     int clocks;       // debug (P2C_TILE_CLOCKS=n): CTA 0 records clock64() at every phase boundary of its n-th tile
-    int fk_rounds;    // rounds of W column tasks in the forward tree walk
-    uint16_t fk_desc[MAX_FK_DESC];
     int8_t parent[P2C_MAX_BONES];
-    int8_t order[P2C_MAX_BONES];          // bones sorted by tree level
-    int8_t lvl_start[MAX_LEVELS + 1];     // order[lvl_start[l] .. lvl_start[l+1]) = bones of level l
-    int8_t child_start[P2C_MAX_BONES + 1];
-    int8_t child_list[P2C_MAX_BONES];
     const float* d6;
     const float* ref_loc;
     const float* ref_rot;
@@ -441,6 +432,14 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         mbar_init(bars + 1, 1);
         mbar_init(bars + 2, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (a.count_inline) {
+        // (one tile per CTA) everything in global memory may come from the previous kernel of the stream: wait for it,
+        // then let the next kernel's CTAs take the SMs as this grid's CTAs retire
+        asm volatile("griddepcontrol.wait;" ::: "memory");
+        asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    }
+    if (tma) {
         if ((int)blockIdx.x < ntiles) {
             load_d6(blockIdx.x);
             load_targets(blockIdx.x);
@@ -637,6 +636,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 bone(w, b + 1, pw);
             }
             fence_async_smem();
+            if (a.clocks && blockIdx.x == 0 && tid == 0) g_tile_clocks[21] = clock64();
         } else if (a.mask && a.count_inline) {
             // utils/tensors.py:29-40 (one tile per CTA): the warps without a column count the kept (joint, channel)
             // pairs of this CTA's tile meanwhile; the grid total goes through one integer atomic per CTA (order
@@ -662,6 +662,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                     v = *reinterpret_cast<volatile unsigned long long*>(cw);
                 } while ((unsigned)(v >> 32) < gridDim.x);
                 k2_shared = a.w2 * 2.0f / (float)(unsigned)(v & 0xffffffffull);
+                if (a.clocks && blockIdx.x == 0) g_tile_clocks[22] = clock64();
             }
         }
         __syncthreads();   // #4
@@ -927,69 +928,20 @@ int sm_count() {
     return g_sms;
 }
 
-// level order + child lists of the bone tree (parents precede children: pose.py:41-47)
+// parents of the bone tree (parents precede children: pose.py:41-47)
 bool tree_tables(const p2c_tree_t& t, TileArgs& a) {
     const int B = t.n_bones;
     if (B < 2 || B > P2C_MAX_BONES || (B & 1)) return false;   // AoS records must be even word counts
-    int level[P2C_MAX_BONES], maxl = 0;
     if (t.parent[0] != -1) return false;
-    level[0] = 0;
-    for (int b = 1; b < B; ++b) {
-        const int p = t.parent[b];
-        if (p < 0 || p >= b) return false;
-        level[b] = level[p] + 1;
-        if (level[b] > maxl) maxl = level[b];
-    }
-    if (maxl + 1 > MAX_LEVELS) return false;
-    a.nlevels = maxl + 1;
-    int n = 0;
-    for (int l = 0; l <= maxl; ++l) {
-        a.lvl_start[l] = (int8_t)n;
-        for (int b = 0; b < B; ++b)
-            if (level[b] == l) a.order[n++] = (int8_t)b;
-    }
-    a.lvl_start[maxl + 1] = (int8_t)n;
-    a.tree_warps = 1;   // widest level (x slices, set by the launcher)
-    for (int l = 0; l <= maxl; ++l)
-        if (a.lvl_start[l + 1] - a.lvl_start[l] > a.tree_warps) a.tree_warps = a.lvl_start[l + 1] - a.lvl_start[l];
-    n = 0;
-    for (int b = 0; b < B; ++b) {
-        a.parent[b] = (int8_t)t.parent[b];
-        a.child_start[b] = (int8_t)n;
-        for (int c = b + 1; c < B; ++c)
-            if (t.parent[c] == b) a.child_list[n++] = (int8_t)c;
-    }
-    a.child_start[B] = (int8_t)n;
+    for (int b = 1; b < B; ++b)
+        if (t.parent[b] < 0 || t.parent[b] >= b) return false;
+    for (int b = 0; b < B; ++b) a.parent[b] = (int8_t)t.parent[b];
     a.B = B;
-    a.npairs = B / 2;
     return true;
 }
 
-// forward-walk schedule: per level 3 * bones * slices column tasks, laid out in rounds of W warps
-int build_fk(TileArgs& a, int W, int slices, bool fill) {
-    int rounds = 0;
-    for (int l = 0; l < a.nlevels; ++l) {
-        const int s0 = a.lvl_start[l], cnt = a.lvl_start[l + 1] - s0, tasks = cnt * 3 * slices;
-        const int nr = (tasks + W - 1) / W;
-        if ((rounds + nr) * W > MAX_FK_DESC) return -1;
-        if (fill) {
-            for (int i = 0; i < nr * W; ++i) {
-                unsigned e = 0;
-                if (i < tasks) {   // task order: slice, bone of the level, column
-                    const int slice = i / (cnt * 3), rem = i - slice * cnt * 3, b = a.order[s0 + rem / 3], j = rem % 3;
-                    e = (unsigned)b | ((unsigned)(a.parent[b] + 1) << 5) | ((unsigned)j << 11) | ((unsigned)slice << 13) | 0x4000u;
-                }
-                if (i / W == nr - 1) e |= 0x8000u;
-                a.fk_desc[(rounds + i / W) * W + i % W] = (uint16_t)e;
-            }
-        }
-        rounds += nr;
-    }
-    return rounds;
-}
-
 struct TileLaunch {
-    int ok, P, PS, slices, threads, tree_warps, grid, count_inline;
+    int ok, P, PS, slices, threads, grid, count_inline;
     size_t smem;
 };
 
@@ -1024,7 +976,6 @@ TileLaunch make_launch(const p2c_fused_step_t* p, const TileArgs& a) {   // a: t
     if (warps > MAX_THREADS / 32) warps = MAX_THREADS / 32;
     t.threads = warps * 32;
     if (warps < 6 * t.slices) return t;   // the subtree-sum walks take six warps per slice (tiny trees: other kernels)
-    t.tree_warps = 6 * t.slices;
     t.smem = (size_t)tile_plan(t.PS, B).total * sizeof(float);
     const size_t cap = 227 * 1024;
     if (t.smem + 1024 > cap) return t;
@@ -1078,7 +1029,6 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     if (!t.ok) return P2C_E_UNSUPPORTED;
     const int B = p->tree.n_bones;
     a.N = p->n_clips; a.L = p->clip_len; a.P = t.P; a.PS = t.PS; a.slices = t.slices;
-    a.tree_warps = t.tree_warps;
     a.clocks = getenv("P2C_TILE_CLOCKS") ? atoi(getenv("P2C_TILE_CLOCKS")) : 0;   // n: record the n-th tile of CTA 0
     a.scan = p->mode == P2C_MODE_POSE_CHANGES;
     a.hips = p->hips; a.neck = p->neck; a.normalize = p->normalize; a.mask = p->mask_missing_joints;
@@ -1123,7 +1073,10 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = (a.mask && !a.count_inline) ? 1 : 0;   // overlap with the count pre-pass only
+    // programmatic dependent launch: with the count pre-pass in front, this kernel overlaps it up to the loss pass; with
+    // one tile per CTA (no pre-pass) the CTAs may be placed while the previous kernel of the stream drains, and wait
+    // (griddepcontrol.wait, before their first global access) until it is complete and flushed
+    cfg.numAttrs = ((a.mask && !a.count_inline) || a.count_inline) ? 1 : 0;
     cudaError_t le = cudaLaunchKernelEx(&cfg, k, a);
     if (le != cudaSuccess) return (int)le;
     P2C_LAUNCH_CHECK();

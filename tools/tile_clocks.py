@@ -25,3 +25,5 @@ w = list(buf)
 if w[16]:
     print('CTA 0: entry -> tile loop %d, tile loop %d, store drain %d, loss fold + ticket %d cycles' % (
         w[17] - w[16], w[18] - w[17], w[19] - w[18], w[20] - w[19]))
+if w[21]:
+    print('forward walk done %d, count poll done %d cycles after barrier 3' % (w[21] - w[4], w[22] - w[4]))
