@@ -42,6 +42,7 @@ struct TileArgs {
     int N, L, B, P, PS, slices, scan;   // clips, frames per clip, bones, poses per tile, P rounded up to 32, PS/32
     int hips, neck, normalize, mask;
     int count_inline; // every CTA owns exactly one tile: the mask count happens inside the kernel (no pre-pass)
+    int clock_cta;    // debug (P2C_TILE_CTA=k): the CTA that records (default 0)
     int clocks;       // debug (P2C_TILE_CLOCKS=n): CTA 0 records clock64() at every phase boundary of its n-th tile
     int8_t parent[P2C_MAX_BONES];
     const float* d6;
@@ -60,10 +61,14 @@ struct TileArgs {
     float* proj;
     float* proj_norm;
     float* g_d6;
-    float* partials;       // gridDim.x x 2
+    float* partials;       // tiles x 2
     unsigned int* ticket;  // self-resetting
     int* count2;           // self-resetting, filled by count_kernel when mask is on
     unsigned int* arrive;  // self-resetting: CTAs that have added their part of count2 (count_inline)
+    unsigned int* next;    // self-resetting: tiles handed out beyond the first of every CTA (dynamic)
+    int fk_groups;         // CARLA tree: limb groups of the forward walk (1, 3 or 5: one warp per slice each; 0: column warps)
+    int warp_fold;         // few tiles: the loss partials are folded by one warp inside the tile loop
+    int dynamic;           // more tiles than CTAs: tiles beyond a CTA's first are drawn from `next`
     float* losses;
     double count3;
 };
@@ -320,12 +325,28 @@ __device__ __forceinline__ V3 bone_loss(const TileArgs& a, int b, const V3& t, f
     return V3{fmaf(cx.k3, e.x, gp.x), fmaf(cx.k3, e.y, gp.y), fmaf(cx.k3, e.z, gp.z)};
 }
 
-__device__ long long g_tile_clocks[64];
-#define CTA_CLOCK(k) \
-    if (a.clocks && blockIdx.x == 0 && threadIdx.x == 0) g_tile_clocks[k] = clock64();
-#define TILE_CLOCK(k)                                                              \
-    if (a.clocks && blockIdx.x == 0 && (int)it == a.clocks - 1 && tid == 0) g_tile_clocks[k] = clock64();
+// CARLA_SKELETON parents (the reference's skeleton table, utils/unreal.py: crl_root, hips, spine, spine01, left arm,
+// neck/head/eyes, right arm, right leg, left leg); folds to a constant in the fully unrolled walks of the BT == 26
+// kernels, which the launcher only picks when the call's tree equals this table
+__host__ __device__ __forceinline__ constexpr int carla_parent(int b) {
+    return b == 0 ? -1 : b == 8 || b == 12 ? 3 : b == 11 ? 9 : b == 16 || b == 21 ? 1 : b - 1;
+}
 
+__device__ long long g_tile_clocks[64];
+__device__ unsigned long long g_cta_times[2 * 1024];   // debug (P2C_TILE_CLOCKS): globaltimer at entry / exit of every CTA
+__device__ __forceinline__ unsigned long long globaltimer() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+#define CTA_CLOCK(k) \
+    if (a.clocks && (int)blockIdx.x == a.clock_cta && threadIdx.x == 0) g_tile_clocks[k] = clock64();
+#define TILE_CLOCK(k)                                                              \
+    if (a.clocks && (int)blockIdx.x == a.clock_cta && (int)it == a.clocks - 1 && tid == 0) g_tile_clocks[k] = clock64();
+
+__device__ __forceinline__ void named_arrive(int id, int threads) {
+    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
 __device__ __forceinline__ void named_barrier(int id, int threads) {
     asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
 }
@@ -389,6 +410,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     const int B3 = B * 3, B6 = B * 6, B9 = B * 9, PS = 32 * slices, L = a.L;
     const TilePlan sm = tile_plan(PS, B);
     CTA_CLOCK(16)
+    if (a.clocks && threadIdx.x == 0 && blockIdx.x < 1024) g_cta_times[blockIdx.x * 2] = globaltimer();
     float* D = smem + sm.d;
     float* G3 = smem + sm.g3;     // G3 and G2 are adjacent: together they hold the re-fetched 6-D records
     float* G2 = smem + sm.g2;
@@ -452,47 +474,64 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     __syncthreads();
 
     float k2 = a.w2 * 2.0f / ((float)total * (float)(B * 2));   // (mask on: replaced below once the count is known)
-    // ---- loss sums: per-CTA partials in fixed order; the last CTA to take a ticket folds them (one warp; called once
-    //      per CTA, after the loss pass of its last tile, while the backward phases run on the other warps)
-    auto publish = [&](float x, float y) {
+    // ---- loss sums: one partial pair per TILE (fixed order inside the tile), so the totals do not depend on which
+    //      CTA ran which tile; the last CTA to take a ticket folds them in tile order at the end of the kernel
+    __shared__ int next_s[2];
+    __shared__ int last_s;
+    if (tid == 0) last_s = 0;
+    auto finish = [&](double d2, double d3) {   // one thread of the last CTA
+        const double c2 = a.mask ? (double)__ldcg(a.count2) : (double)total * B * 2;
+        const float l2 = (float)(d2 / c2), l3 = (float)(d3 / a.count3);
+        a.losses[0] = l2; a.losses[1] = l3; a.losses[2] = a.w2 * l2 + a.w3 * l3;
+        a.losses[3] = (float)d2; a.losses[4] = (float)c2; a.losses[5] = (float)d3; a.losses[6] = (float)a.count3;
+        a.losses[7] = 0.f;
+        *a.ticket = 0u;   // self-resetting workspace header: ready for the next launch
+        *a.count2 = 0;
+        *a.arrive = 0u;
+        *a.next = 0u;
+    };
+    // few tiles (a.warp_fold): the warp that stored this CTA's last partial waits for its ticket and, if it is the
+    // grid's last, folds right there, behind the backward phases of the other warps
+    auto ticket_and_fold = [&]() {
         bool lastw = false;
         if (lane == 0) {
-            a.partials[blockIdx.x * 2] = x;
-            a.partials[blockIdx.x * 2 + 1] = y;
             __threadfence();
             lastw = atomicAdd(a.ticket, 1u) == gridDim.x - 1;
         }
         if (!__shfl_sync(FULL_MASK, lastw, 0)) return;
         __threadfence();
         double d2 = 0.0, d3 = 0.0;
-        for (int i = lane; i < (int)gridDim.x; i += 32) {
-            d2 += (double)__ldcg(a.partials + i * 2);
-            d3 += (double)__ldcg(a.partials + i * 2 + 1);
+        for (int i = lane; i < ntiles; i += 32) {
+            const float2 v = __ldcg(reinterpret_cast<const float2*>(a.partials) + i);
+            d2 += (double)v.x;
+            d3 += (double)v.y;
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             d2 += __shfl_xor_sync(FULL_MASK, d2, o);
             d3 += __shfl_xor_sync(FULL_MASK, d3, o);
         }
-        if (lane == 0) {
-            const double c2 = a.mask ? (double)__ldcg(a.count2) : (double)total * B * 2;
-            const float l2 = (float)(d2 / c2), l3 = (float)(d3 / a.count3);
-            a.losses[0] = l2; a.losses[1] = l3; a.losses[2] = a.w2 * l2 + a.w3 * l3;
-            a.losses[3] = (float)d2; a.losses[4] = (float)c2; a.losses[5] = (float)d3; a.losses[6] = (float)a.count3;
-            a.losses[7] = 0.f;
-            *a.ticket = 0u;   // self-resetting workspace header: ready for the next launch
-            *a.count2 = 0;
-            *a.arrive = 0u;
-        }
+        if (lane == 0) finish(d2, d3);
+    };
+    unsigned my_ticket = 0xffffffffu;   // (drawn by one lane after this CTA's last partial store, looked at on exit)
+    auto take_ticket = [&]() {
+        __threadfence();
+        my_ticket = atomicAdd(a.ticket, 1u);
     };
     const float k3 = a.w3 * 2.0f / (float)a.count3;
-    float s2 = 0.f, s3 = 0.f;
     unsigned it = 0;
     CTA_CLOCK(17)
     const int clips_full = a.P / L;
 
-    for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-        const int m0 = tile * a.P, nxt = tile + gridDim.x;
+    // tiles beyond the first come from a grid-wide counter (SMs do not run at one speed: up to a quarter between the
+    // fastest and the slowest CTA under a static split); the ticket is drawn at the top of a tile and first needed
+    // after the forward phases
+    int nxt = ntiles;
+    for (int tile = blockIdx.x; tile < ntiles; tile = nxt, ++it) {
+        const int m0 = tile * a.P;
+        unsigned drawn = 0;
+        if (tma && a.dynamic) drawn = atomicAdd(a.next, 1u);
+        float s2 = 0.f, s3 = 0.f;
         const int np = min(a.P, total - m0);
         const int* row = ROW + (it & 1) * PS;
         const int tile_clips = np == a.P ? clips_full : np / L;   // (only the last tile can be short)
@@ -502,6 +541,14 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         __syncthreads();   // #1 (first tile: the row table; later tiles: ordered by the barriers of the previous tile)
 
         TILE_CLOCK(2)
+        // the reference rotations that start the scan of this thread's first (clip, bone, column) item: asked for now,
+        // used after phase A (an L2 round trip on the SMs far from the table's slice)
+        float q0 = 0.f, q1 = 0.f, q2 = 0.f;
+        if (a.scan && tid < tile_clips * B3) {
+            const int cl = tid / B3, rem = tid - cl * B3;
+            const float* rr = a.ref_rot + (size_t)row[cl * L] * B9 + (rem / 3) * 9 + rem % 3;
+            q0 = __ldg(rr); q1 = __ldg(rr + 3); q2 = __ldg(rr + 6);
+        }
         // ---- phase A: 6-D -> C[t] (rotation_6d_to_matrix), one bone per task
         {
             float* dst = a.scan ? A : R;
@@ -530,8 +577,11 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
 #pragma unroll 1
             for (int idx = tid; idx < items; idx += NT) {
                 const int cl = idx / B3, rem = idx - cl * B3, b = rem / 3, j = rem - b * 3;
-                const float* rr = a.ref_rot + ((size_t)row[cl * L] * B + b) * 9 + j;
-                float p0 = __ldg(rr), p1 = __ldg(rr + 3), p2 = __ldg(rr + 6);
+                float p0 = q0, p1 = q1, p2 = q2;
+                if (idx != tid) {
+                    const float* rr = a.ref_rot + ((size_t)row[cl * L] * B + b) * 9 + j;
+                    p0 = __ldg(rr); p1 = __ldg(rr + 3); p2 = __ldg(rr + 6);
+                }
                 const float* src = A + (cl * L) * B9 + b * 9;
                 float* dst = R + (cl * L) * B9 + b * 9 + j;
                 // two frames per trip; the records of the next two frames are in flight while these products run
@@ -573,6 +623,28 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 const int k = i / PS, col = i - k * PS;
                 GV[i] = __ldg(a.ref_loc + (size_t)row[col] * B3 + k);
             }
+            if (a.mask && a.count_inline) {
+                // utils/tensors.py:29-40 (one tile per CTA): the threads without a scan item count the kept (joint,
+                // channel) pairs of this CTA's tile; the grid total goes through one 64-bit atomic per CTA (count in
+                // the low word, arrivals in the high word; integer => order independent), sent now and read back
+                // during the forward walk
+                const int nc = NT - busy, ci = tid - busy;
+                if (ci >= 0) {
+                    while (!mbar_try_wait(bars + 1, it & 1u)) {}
+                    int c = 0;
+                    for (int i = ci; i < np * B; i += nc) {
+                        const int j = i % B;
+                        const float* g = G2 + i * 3;
+                        if (j == a.hips || (g[0] != 0.f && g[1] != 0.f)) c += 2;
+                    }
+                    c = __reduce_add_sync(FULL_MASK, c);
+                    if (lane == 0 && c) atomicAdd(&cta_count, c);
+                    named_barrier(1, nc);
+                    if (ci == 0)
+                        atomicAdd(reinterpret_cast<unsigned long long*>(a.count2),
+                                  (1ull << 32) | (unsigned long long)(unsigned)cta_count);
+                }
+            }
         }
         fence_async_smem();
         __syncthreads();   // #3
@@ -581,12 +653,115 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             bulk_s2g(a.rel_rot + (size_t)m0 * B9, R, (uint32_t)(np * B9) * 4u);
             bulk_commit();
         }
+        if (tma) next_s[it & 1] = a.dynamic ? (int)min(drawn + gridDim.x, (unsigned)ntiles) : ntiles;
 
         // ---- phase C: FK (p3d_pose.py:116-184): A_b = R_b . A_parent, t_b = loc_b . A_parent + t_parent.
-        //      Column j of A_b and component j of t_b need only column j of the parent, so THREE warps per slice (one per
-        //      column) each walk the whole tree in bone order, reading back only what they wrote themselves: no
-        //      barrier between bones, and the parent's column stays in registers along chains (parent == b - 1).
-        if (warp < 3 * slices) {
+        //      The phase is bound by shared-memory wavefronts, so every record is read once: with the CARLA tree (known at
+        //      compile time: straight-line code, immediate offsets, 64-bit conflict-free record accesses) ONE warp per
+        //      slice and limb group forms the full 3x3 products; the trunk-and-left-arm group signals (bar.arrive, it
+        //      never waits) when hips and spine01 are done and the groups that hang off them wait on those named
+        //      barriers.  Any other tree, and one tile per CTA (latency counts, not wavefronts: three short instruction
+        //      streams beat one long one): three warps per slice, one per column of A (a column needs only the same
+        //      column of the parent), each walking the whole tree in bone order.
+        const bool limbs = BT == 26 && a.fk_groups > 0;
+        const int fk_warps = limbs ? a.fk_groups * slices : 3 * slices;
+        if (limbs && warp < fk_warps) {
+            const int grp = warp / slices, col = (warp - grp * slices) * 32 + lane, pl = min(col, np - 1);
+            const bool valid = col < np;
+            const float* rb = R + pl * B9;
+            float* ab = A + pl * B9;
+            float P[9], tp[3];   // A and t of the previous bone of the run
+            auto rec_ld = [&](const float* base, int b, float* x) {   // 9-word record b of an even-word pose record
+                const float* q = base + 9 * b;
+                if (b & 1) {
+                    x[0] = q[0];
+                    const float2 v0 = lds64(q + 1), v1 = lds64(q + 3), v2 = lds64(q + 5), v3 = lds64(q + 7);
+                    x[1] = v0.x; x[2] = v0.y; x[3] = v1.x; x[4] = v1.y; x[5] = v2.x; x[6] = v2.y; x[7] = v3.x; x[8] = v3.y;
+                } else {
+                    const float2 v0 = lds64(q), v1 = lds64(q + 2), v2 = lds64(q + 4), v3 = lds64(q + 6);
+                    x[0] = v0.x; x[1] = v0.y; x[2] = v1.x; x[3] = v1.y; x[4] = v2.x; x[5] = v2.y; x[6] = v3.x; x[7] = v3.y;
+                    x[8] = q[8];
+                }
+            };
+            auto rec_st = [&](float* base, int b, const float* x) {
+                float* q = base + 9 * b;
+                if (b & 1) {
+                    q[0] = x[0];
+                    sts64(q + 1, x[1], x[2]); sts64(q + 3, x[3], x[4]); sts64(q + 5, x[5], x[6]); sts64(q + 7, x[7], x[8]);
+                } else {
+                    sts64(q, x[0], x[1]); sts64(q + 2, x[2], x[3]); sts64(q + 4, x[4], x[5]); sts64(q + 6, x[6], x[7]);
+                    q[8] = x[8];
+                }
+            };
+            auto bone = [&](int b, int par, bool head) {
+                if (head || par != b - 1) {
+                    if (par >= 0) {
+                        rec_ld(ab, par, P);
+                        tp[0] = TS[(par * 3) * PS + col]; tp[1] = TS[(par * 3 + 1) * PS + col];
+                        tp[2] = TS[(par * 3 + 2) * PS + col];
+                    } else {   // root: the parent transform is the identity
+#pragma unroll
+                        for (int i = 0; i < 9; ++i) P[i] = (i == 0 || i == 4 || i == 8) ? 1.f : 0.f;
+                        tp[0] = tp[1] = tp[2] = 0.f;
+                    }
+                }
+                float x[9], n[9];
+                rec_ld(rb, b, x);
+                const float l0 = GV[(3 * b) * PS + col], l1 = GV[(3 * b + 1) * PS + col], l2 = GV[(3 * b + 2) * PS + col];
+#pragma unroll
+                for (int i = 0; i < 3; ++i)
+#pragma unroll
+                    for (int j = 0; j < 3; ++j)
+                        n[3 * i + j] = fmaf(x[3 * i + 2], P[6 + j], fmaf(x[3 * i + 1], P[3 + j], x[3 * i] * P[j]));
+#pragma unroll
+                for (int j = 0; j < 3; ++j) tp[j] = fmaf(l2, P[6 + j], fmaf(l1, P[3 + j], l0 * P[j])) + tp[j];
+#pragma unroll
+                for (int i = 0; i < 9; ++i) P[i] = n[i];
+                if (valid) rec_st(ab, b, n);
+                TS[(3 * b) * PS + col] = tp[0]; TS[(3 * b + 1) * PS + col] = tp[1]; TS[(3 * b + 2) * PS + col] = tp[2];
+            };
+#define P2C_RUN(B0, B1) \
+    _Pragma("unroll") for (int b = B0; b < B1; ++b) bone(b, carla_parent(b), b == B0);
+            const int g = a.fk_groups;
+            if (g == 1) {
+                P2C_RUN(0, 26)
+            } else if (grp == 0) {
+                const int waiters = (g == 3 ? 2 : 3) * slices * 32;
+                if (a.clocks && (int)blockIdx.x == a.clock_cta && tid == 0) g_tile_clocks[27] = clock64();
+                P2C_RUN(0, 2)
+                named_arrive(3, waiters);   // hips
+                if (a.clocks && (int)blockIdx.x == a.clock_cta && tid == 0) g_tile_clocks[28] = clock64();
+                P2C_RUN(2, 4)
+                named_arrive(4, waiters);   // spine01
+                if (a.clocks && (int)blockIdx.x == a.clock_cta && tid == 0) g_tile_clocks[29] = clock64();
+                P2C_RUN(4, 8)               // left arm
+            } else if (g == 3) {
+                if (grp == 1) {
+                    named_barrier(4, 2 * slices * 32);
+                    P2C_RUN(8, 16)          // neck, head, eyes, right arm
+                } else {
+                    named_barrier(3, 2 * slices * 32);
+                    P2C_RUN(16, 26)         // legs
+                }
+            } else {
+                if (grp == 1) {
+                    named_barrier(4, 3 * slices * 32);
+                    P2C_RUN(8, 12)          // neck, head, eyes
+                } else if (grp == 2) {
+                    named_barrier(4, 3 * slices * 32);
+                    P2C_RUN(12, 16)         // right arm
+                } else if (grp == 3) {
+                    named_barrier(3, 3 * slices * 32);
+                    P2C_RUN(16, 21)         // right leg
+                } else {
+                    named_barrier(3, 3 * slices * 32);
+                    P2C_RUN(21, 26)         // left leg
+                }
+            }
+#undef P2C_RUN
+            fence_async_smem();
+            if (a.clocks && (int)blockIdx.x == a.clock_cta && tid == 0) g_tile_clocks[21] = clock64();
+        } else if (!limbs && warp < fk_warps) {
             const int jc = warp % 3, col = (warp / 3) * 32 + lane, pl = min(col, np - 1);
             const bool valid = col < np;
             const float* rb = R + pl * B9;
@@ -622,50 +797,40 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 if (valid) { ab[9 * b] = c0; ab[9 * b + 3] = c1; ab[9 * b + 6] = c2; }
                 tr[(3 * b) * PS] = ct;
             };
-            fetch(u, 0);
-            pu = a.parent[0];
-#pragma unroll 1
-            for (int b = 0; b < B; b += 2) {
-                fetch(w, b + 1);
-                pw = a.parent[b + 1];
-                bone(u, b, pu);
-                if (b + 2 < B) {
-                    fetch(u, b + 2);
-                    pu = a.parent[b + 2];
+            if (BT == 26) {   // (one tile per CTA: latency matters, three short instruction streams beat one long one)
+#pragma unroll
+                for (int b = 0; b < 26; ++b) {
+                    fetch(u, b);
+                    bone(u, b, carla_parent(b));
                 }
-                bone(w, b + 1, pw);
+            } else {
+                fetch(u, 0);
+                pu = a.parent[0];
+    #pragma unroll 1
+                for (int b = 0; b < B; b += 2) {
+                    fetch(w, b + 1);
+                    pw = a.parent[b + 1];
+                    bone(u, b, pu);
+                    if (b + 2 < B) {
+                        fetch(u, b + 2);
+                        pu = a.parent[b + 2];
+                    }
+                    bone(w, b + 1, pw);
+                }
             }
             fence_async_smem();
-            if (a.clocks && blockIdx.x == 0 && tid == 0) g_tile_clocks[21] = clock64();
-        } else if (a.mask && a.count_inline) {
-            // utils/tensors.py:29-40 (one tile per CTA): the warps without a column count the kept (joint, channel)
-            // pairs of this CTA's tile meanwhile; the grid total goes through one integer atomic per CTA (order
-            // independent) and the loss pass waits for every CTA's part
-            const int nc = NT - 3 * slices * 32, ci = tid - 3 * slices * 32;
-            while (!mbar_try_wait(bars + 1, it & 1u)) {}
-            int c = 0;
-            for (int i = ci; i < np * B; i += nc) {
-                const int j = i % B;
-                const float* g = G2 + i * 3;
-                if (j == a.hips || (g[0] != 0.f && g[1] != 0.f)) c += 2;
-            }
-            c = __reduce_add_sync(FULL_MASK, c);
-            if (lane == 0 && c) atomicAdd(&cta_count, c);
-            named_barrier(1, nc);
-            if (ci == 0) {
-                // count (low word) and arrivals (high word) travel in one 64-bit atomic; this lane then polls until
-                // every CTA of the grid has arrived (all CTAs are resident: one tile each, at most one CTA per SM)
-                unsigned long long* cw = reinterpret_cast<unsigned long long*>(a.count2);
-                atomicAdd(cw, (1ull << 32) | (unsigned long long)(unsigned)cta_count);
-                unsigned long long v;
-                do {
-                    v = *reinterpret_cast<volatile unsigned long long*>(cw);
-                } while ((unsigned)(v >> 32) < gridDim.x);
-                k2_shared = a.w2 * 2.0f / (float)(unsigned)(v & 0xffffffffull);
-                if (a.clocks && blockIdx.x == 0) g_tile_clocks[22] = clock64();
-            }
+        } else if (a.mask && a.count_inline && tid == fk_warps * 32) {
+            // one lane of a warp without a column polls until every CTA of the grid has sent its count (all CTAs are
+            // resident: one tile each, at most one CTA per SM)
+            unsigned long long v;
+            do {
+                v = *reinterpret_cast<volatile unsigned long long*>(a.count2);
+            } while ((unsigned)(v >> 32) < gridDim.x);
+            k2_shared = a.w2 * 2.0f / (float)(unsigned)(v & 0xffffffffull);
+            if (a.clocks && (int)blockIdx.x == a.clock_cta) g_tile_clocks[22] = clock64();
         }
         __syncthreads();   // #4
+        nxt = next_s[it & 1];
         TILE_CLOCK(5)
         if (tma && a.abs_rot) {
             bulk_s2g(a.abs_rot + (size_t)m0 * B9, A, (uint32_t)(np * B9) * 4u);
@@ -734,11 +899,9 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 }
             }
         }
-        if (nxt >= ntiles) {   // this CTA's last tile: its loss sums are complete
-            s2 = warp_sum(s2);
-            s3 = warp_sum(s3);
-            if (lane == 0) { red[warp * 2] = s2; red[warp * 2 + 1] = s3; }
-        }
+        s2 = warp_sum(s2);
+        s3 = warp_sum(s3);
+        if (lane == 0) { red[warp * 2] = s2; red[warp * 2 + 1] = s3; }
         fence_async_smem();
         if (tma) bulk_wait_read_all();   // rel_rot / abs_rot stores have read R and A
         __syncthreads();   // #5
@@ -804,40 +967,65 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         if (warp < 6 * slices) {
             const int k = warp % 6, col = (warp / 6) * 32 + lane;
             float* rowp = (k < 3 ? XR + k * PS : GV + (k - 3) * PS) + col;
-            float carry = 0.f;
-            bool have = false;
-            float nv = rowp[(B - 1) * 3 * PS];
-            int npar = a.parent[B - 1];
-#pragma unroll 1
-            for (int c = B - 1; c >= 1; --c) {
-                float v = nv;
-                const int par = npar;
-                nv = rowp[(c - 1) * 3 * PS];   // (row c-1 is not touched in this trip unless it is the parent; see below)
-                npar = a.parent[c - 1];
-                if (have) {
-                    v += carry;
-                    rowp[c * 3 * PS] = v;
+            if (BT == 26) {
+                float carry = 0.f;
+#pragma unroll
+                for (int c = 25; c >= 0; --c) {
+                    const bool have = c + 1 < 26 && carla_parent(c + 1) == c;   // the next bone is this one's child
+                    float v = rowp[c * 3 * PS];
+                    if (have) {
+                        v += carry;
+                        rowp[c * 3 * PS] = v;
+                    }
+                    if (c > 0) {
+                        if (carla_parent(c) == c - 1) carry = v;
+                        else rowp[carla_parent(c) * 3 * PS] += v;
+                    }
                 }
-                if (par == c - 1) {
-                    carry = v;
-                    have = true;
-                } else {
-                    rowp[par * 3 * PS] += v;
-                    have = false;
+            } else {
+                float carry = 0.f;
+                bool have = false;
+                float nv = rowp[(B - 1) * 3 * PS];
+                int npar = a.parent[B - 1];
+    #pragma unroll 1
+                for (int c = B - 1; c >= 1; --c) {
+                    float v = nv;
+                    const int par = npar;
+                    nv = rowp[(c - 1) * 3 * PS];   // (row c-1 is not touched in this trip unless it is the parent; see below)
+                    npar = a.parent[c - 1];
+                    if (have) {
+                        v += carry;
+                        rowp[c * 3 * PS] = v;
+                    }
+                    if (par == c - 1) {
+                        carry = v;
+                        have = true;
+                    } else {
+                        rowp[par * 3 * PS] += v;
+                        have = false;
+                    }
                 }
+                if (have) rowp[0] = nv + carry;
             }
-            if (have) rowp[0] = nv + carry;
         }
-        if (nxt >= ntiles && warp == W - 2) {   // (a warp without a column when W >= 6 slices + 2: off the critical path)
-            float x = 0.f, y = 0.f;
-            if (lane == 0)
+        if (a.clocks && (int)blockIdx.x == a.clock_cta && tid == 0) g_tile_clocks[23] = clock64();
+        // (two warps without a column when W >= 6 slices + 2: both jobs wait on global memory, off the critical path)
+        if (nxt < ntiles && warp == W - 1) fill_rows(nxt, (it + 1) & 1);
+        if (warp == W - 2) {
+            if (lane == 0) {
+                float x = 0.f, y = 0.f;
                 for (int w = 0; w < W; ++w) { x += red[w * 2]; y += red[w * 2 + 1]; }
-            publish(x, y);
+                a.partials[tile * 2] = x;
+                a.partials[tile * 2 + 1] = y;
+            }
+            if (nxt >= ntiles) {   // this CTA's last tile
+                if (a.warp_fold) ticket_and_fold();
+                else if (lane == 0) take_ticket();
+            }
         }
         while (!mbar_try_wait(bars + 2, it & 1u)) {}
         __syncthreads();   // #6
         TILE_CLOCK(8)
-        if (nxt < ntiles && warp == W - 1) fill_rows(nxt, (it + 1) & 1);
         // ---- per bone, all independent:  m_b = Sx_b - Sg_b x t_b,  y_b = A_parent m_b  (in place over Sx_b).  After this
         //      pass the scratch rows (t, Sg) and the abs_rot records are dead, so the next tile's 6-D records can start
         //      their way in while the gradient pass runs.
@@ -858,6 +1046,8 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 XR[(b * 3) * PS + col] = y.x; XR[(b * 3 + 1) * PS + col] = y.y; XR[(b * 3 + 2) * PS + col] = y.z;
             }
         }
+        if (a.clocks && (int)blockIdx.x == a.clock_cta && tid == 0) g_tile_clocks[25] = clock64();
+        if (a.clocks && (int)blockIdx.x == a.clock_cta && tid == NT - 64) g_tile_clocks[26] = clock64();
         fence_async_smem();   // (the scratch rows are about to be overwritten by TMA)
         __syncthreads();   // #7
         TILE_CLOCK(9)
@@ -911,8 +1101,37 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     if (tma) bulk_wait_all();
     CTA_CLOCK(19)
 
-    if (it == 0 && warp == W - 2) publish(0.f, 0.f);   // (a CTA without a tile still takes its ticket)
+    if (it == 0 && warp == 0) {   // (a CTA without a tile still takes its ticket)
+        if (a.warp_fold) ticket_and_fold();
+        else if (lane == 0) take_ticket();
+    }
+    if (my_ticket == gridDim.x - 1) last_s = 1;
+    __syncthreads();
+    if (last_s) {
+        // every CTA has stored its partials and taken its ticket: fold them in tile order, in double, all threads
+        __threadfence();
+        double d2 = 0.0, d3 = 0.0;
+        for (int i = tid; i < ntiles; i += NT) {
+            const float2 v = __ldcg(reinterpret_cast<const float2*>(a.partials) + i);
+            d2 += (double)v.x;
+            d3 += (double)v.y;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            d2 += __shfl_xor_sync(FULL_MASK, d2, o);
+            d3 += __shfl_xor_sync(FULL_MASK, d3, o);
+        }
+        double* dred = reinterpret_cast<double*>(R);   // (no bulk copy still reads the relative-rotation region)
+        if (lane == 0) { dred[warp * 2] = d2; dred[warp * 2 + 1] = d3; }
+        __syncthreads();
+        if (tid == 0) {
+            d2 = 0.0; d3 = 0.0;
+            for (int w = 0; w < W; ++w) { d2 += dred[w * 2]; d3 += dred[w * 2 + 1]; }
+            finish(d2, d3);
+        }
+    }
     CTA_CLOCK(20)
+    if (a.clocks && threadIdx.x == 0 && blockIdx.x < 1024) g_cta_times[blockIdx.x * 2 + 1] = globaltimer();
 }
 
 int g_sms = 0;
@@ -941,7 +1160,7 @@ bool tree_tables(const p2c_tree_t& t, TileArgs& a) {
 }
 
 struct TileLaunch {
-    int ok, P, PS, slices, threads, grid, count_inline;
+    int ok, P, PS, slices, threads, grid, count_inline, dynamic;
     size_t smem;
 };
 
@@ -981,11 +1200,12 @@ TileLaunch make_launch(const p2c_fused_step_t* p, const TileArgs& a) {   // a: t
     if (t.smem + 1024 > cap) return t;
     int per_sm = (int)((228 * 1024) / (t.smem + 1024));
     if (per_sm * t.threads > 896) per_sm = 896 / t.threads;   // 72 registers per thread (launch bounds 832 x 1)
-    if (per_sm > 4) per_sm = 4;   // the workspace holds 2 x 592 loss partials
+    if (per_sm > 4) per_sm = 4;
     if (per_sm < 1) per_sm = 1;
     if (getenv("P2C_TILE_ONE_CTA") && getenv("P2C_TILE_ONE_CTA")[0] == '1') per_sm = 1;   // debug: no co-resident CTA
     const long slots = (long)sm_count() * per_sm;
     t.grid = (int)(ntiles < slots ? ntiles : slots);
+    t.dynamic = ntiles > t.grid ? 1 : 0;
     t.count_inline = lone ? 1 : 0;   // grid == ntiles <= SMs: every CTA is resident, the in-kernel wait cannot hang
     t.ok = 1;
     return t;
@@ -1012,6 +1232,9 @@ extern "C" int p2c_fused_tile_supported(const p2c_fused_step_t* p) {
 }
 
 // debug: the phase clocks recorded by CTA 0 (P2C_TILE_CLOCKS=1); host buffer of 32 values
+extern "C" int p2c_debug_cta_times(unsigned long long* out) {
+    return (int)cudaMemcpyFromSymbol(out, g_cta_times, sizeof(unsigned long long) * 2048);
+}
 extern "C" int p2c_debug_tile_clocks(long long* out) {
     return (int)cudaMemcpyFromSymbol(out, g_tile_clocks, sizeof(long long) * 64);
 }
@@ -1029,6 +1252,7 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     if (!t.ok) return P2C_E_UNSUPPORTED;
     const int B = p->tree.n_bones;
     a.N = p->n_clips; a.L = p->clip_len; a.P = t.P; a.PS = t.PS; a.slices = t.slices;
+    a.clock_cta = getenv("P2C_TILE_CTA") ? atoi(getenv("P2C_TILE_CTA")) : 0;
     a.clocks = getenv("P2C_TILE_CLOCKS") ? atoi(getenv("P2C_TILE_CLOCKS")) : 0;   // n: record the n-th tile of CTA 0
     a.scan = p->mode == P2C_MODE_POSE_CHANGES;
     a.hips = p->hips; a.neck = p->neck; a.normalize = p->normalize; a.mask = p->mask_missing_joints;
@@ -1040,7 +1264,17 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     a.ticket = reinterpret_cast<unsigned int*>(p->workspace);
     a.count2 = reinterpret_cast<int*>(p->workspace) + 2;             // (8-byte aligned: count2 and arrive are also
     a.arrive = reinterpret_cast<unsigned int*>(p->workspace) + 3;    //  updated together as one 64-bit word)
+    a.next = reinterpret_cast<unsigned int*>(p->workspace) + 4;
     a.count_inline = t.count_inline;
+    a.dynamic = t.dynamic;
+    a.warp_fold = ((long)p->n_clips * p->clip_len + t.P - 1) / t.P <= 1024;
+    {   // forward-walk groups: all five limbs apart when the warps are there (and four are left for the mask count)
+        const int w = t.threads / 32;
+        a.fk_groups = t.count_inline ? 0 : w > 5 * t.slices ? 5 : w > 3 * t.slices ? 3 : 1;   // 0: column warps
+        if (getenv("P2C_TILE_FK_GROUPS")) a.fk_groups = atoi(getenv("P2C_TILE_FK_GROUPS"));   // debug
+    }
+    // one partial pair per tile: at most n_poses floats, inside the scratch area every caller provides
+    // (p2c_fused_step_workspace_floats: 16 header words, then >= 6 * n_bones * n_poses floats of scratch)
     a.partials = p->workspace + 16;
     a.losses = p->losses;
     const long total = (long)p->n_clips * p->clip_len;
@@ -1055,7 +1289,9 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     }
     typedef void (*kern_t)(const TileArgs);
     const bool world = p->world_loc || p->world_rot;
-    const int ki = world ? 3 : B == 26 ? (t.slices == 1 ? 0 : 1) : 2;   // CARLA_SKELETON: compile-time bones and slices
+    bool carla = B == 26;
+    for (int b = 0; b < B && carla; ++b) carla = p->tree.parent[b] == carla_parent(b);
+    const int ki = world ? 3 : carla ? (t.slices == 1 ? 0 : 1) : 2;   // CARLA_SKELETON: compile-time tree and slices
     const kern_t k = ki == 0 ? tile_kernel<26, 1, false> : ki == 1 ? tile_kernel<26, 2, false>
                    : ki == 2 ? tile_kernel<0, 0, false> : tile_kernel<0, 0, true>;
     static bool configured[4] = {false, false, false, false};
