@@ -140,13 +140,20 @@ __device__ __forceinline__ float2 lds64(const float* p) {
 __device__ __forceinline__ void sts64(float* p, float x, float y) {
     asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(smem_u32(p)), "f"(x), "f"(y) : "memory");
 }
-// 9-word bone record b of an AoS pose record, read with scalar loads: the 64-bit form needs both parities of b
-// spelled out under predicates, which costs more issue slots than the 2-way bank conflicts of the scalar form
+// 9-word bone record b of an AoS pose record (b is warp-uniform at every call site: the parity branch does not diverge)
+// (64-bit accesses: half the wavefronts of scalar ones; the pose stride, 117 x 8 bytes, is conflict free)
 __device__ __forceinline__ M3 lds9(const float* pose, int b) {
     const float* p = pose + 9 * b;
     M3 r;
-#pragma unroll
-    for (int i = 0; i < 9; ++i) r.m[i] = p[i];
+    if (b & 1) {
+        r.m[0] = p[0];
+        const float2 v0 = lds64(p + 1), v1 = lds64(p + 3), v2 = lds64(p + 5), v3 = lds64(p + 7);
+        r.m[1] = v0.x; r.m[2] = v0.y; r.m[3] = v1.x; r.m[4] = v1.y; r.m[5] = v2.x; r.m[6] = v2.y; r.m[7] = v3.x; r.m[8] = v3.y;
+    } else {
+        const float2 v0 = lds64(p), v1 = lds64(p + 2), v2 = lds64(p + 4), v3 = lds64(p + 6);
+        r.m[0] = v0.x; r.m[1] = v0.y; r.m[2] = v1.x; r.m[3] = v1.y; r.m[4] = v2.x; r.m[5] = v2.y; r.m[6] = v3.x; r.m[7] = v3.y;
+        r.m[8] = p[8];
+    }
     return r;
 }
 __device__ __forceinline__ void sts9(float* pose, int b, const M3& a) {
@@ -522,6 +529,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     unsigned it = 0;
     CTA_CLOCK(17)
     const int clips_full = a.P / L;
+    const int lane_frame = lane % L;   // (one slice: whole clips side by side in the lanes)
 
     // tiles beyond the first come from a grid-wide counter (SMs do not run at one speed: up to a quarter between the
     // fastest and the slowest CTA under a static split); the ticket is drawn at the top of a tile and first needed
@@ -1065,7 +1073,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                     const bool valid = col < np;
                     V3 z{XR[(b * 3) * PS + col], XR[(b * 3 + 1) * PS + col], XR[(b * 3 + 2) * PS + col]};
                     if (a.scan) {
-                        const int fr = slices == 1 ? col % L : col;   // frame of this lane within its clip
+                        const int fr = slices == 1 ? lane_frame : col;   // frame of this lane within its clip
 #pragma unroll
                         for (int off = 1; off < 32; off <<= 1) {
                             if (off >= L) break;
