@@ -349,12 +349,18 @@ def measured_peak():
         return 6650.0, 'B200_PROFILING.md fallback 6.65 TB/s (of fallback)'
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum of the step kernel, one launch, from the committed `ncu --set full`
+# captures (profiles/r01_tile_<clips>x<len>.txt); writes still in L2 when the kernel ends are not in it
+NCU_DRAM_BYTES = {(256, 16): 5.227e6, (8192, 16): 164.17e6 + 353.15e6, (4096, 64): 327.93e6 + 760.38e6}
+
+
 def roofline_of(poses, clip_len, ms_per_step, note):
     peak, src = measured_peak()
     bpp = algorithmic_bytes_per_pose(clip_len)
     achieved = poses * bpp / (ms_per_step * 1e-3) / 1e9
     return {'bound': 'hbm', 'achieved': round(achieved, 1), 'peak': peak, 'unit': 'GB/s',
-            'frac': round(achieved / peak, 4), 'traffic': None, 'bytes_per_pose': bpp, 'peak_source': src,
+            'frac': round(achieved / peak, 4), 'traffic': NCU_DRAM_BYTES.get((poses // clip_len, clip_len)),
+            'traffic_unit': 'bytes per launch (ncu, profiles/r01_tile_*)', 'bytes_per_pose': bpp, 'peak_source': src,
             'kernel': note}
 
 

@@ -66,7 +66,6 @@ struct TileArgs {
     int* count2;           // self-resetting, filled by count_kernel when mask is on
     unsigned int* arrive;  // self-resetting: CTAs that have added their part of count2 (count_inline)
     unsigned int* next;    // self-resetting: tiles handed out beyond the first of every CTA (dynamic)
-    int fk_groups;         // CARLA tree: limb groups of the forward walk (1, 3 or 5: one warp per slice each; 0: column warps)
     int warp_fold;         // few tiles: the loss partials are folded by one warp inside the tile loop
     int dynamic;           // more tiles than CTAs: tiles beyond a CTA's first are drawn from `next`
     float* losses;
@@ -407,9 +406,56 @@ __device__ __forceinline__ void sts3(float* pose, int b, const V3& v) {
     }
 }
 
+// ---- loss totals (rarely executed, kept out of line: the double-precision divisions are long instruction sequences)
+struct FoldArgs {   // (by value: a reference to the kernel parameters would force a local copy of all of them)
+    float* losses;
+    const float* partials;
+    unsigned int* header;   // ticket, -, count2, arrive, next
+    double count3, all2;
+    float w2, w3;
+    int mask;
+};
+__device__ __noinline__ void finish_losses(const FoldArgs a, double d2, double d3) {   // one thread
+    const double c2 = a.mask ? (double)__ldcg(reinterpret_cast<const int*>(a.header) + 2) : a.all2;
+    const float l2 = (float)(d2 / c2), l3 = (float)(d3 / a.count3);
+    a.losses[0] = l2; a.losses[1] = l3; a.losses[2] = a.w2 * l2 + a.w3 * l3;
+    a.losses[3] = (float)d2; a.losses[4] = (float)c2; a.losses[5] = (float)d3; a.losses[6] = (float)a.count3;
+    a.losses[7] = 0.f;
+    a.header[0] = 0u;   // self-resetting workspace header: ready for the next launch
+    a.header[2] = 0u;
+    a.header[3] = 0u;
+    a.header[4] = 0u;
+}
+// few tiles (a.warp_fold): the warp that stored this CTA's last partial waits for its ticket and, if it is the grid's
+// last, folds right there, behind the backward phases of the other warps
+__device__ __noinline__ void warp_ticket_and_fold(const FoldArgs a, int ntiles) {
+    const int lane = threadIdx.x & 31;
+    bool lastw = false;
+    if (lane == 0) {
+        __threadfence();
+        lastw = atomicAdd(a.header, 1u) == gridDim.x - 1;
+    }
+    if (!__shfl_sync(FULL_MASK, lastw, 0)) return;
+    __threadfence();
+    double d2 = 0.0, d3 = 0.0;
+    for (int i = lane; i < ntiles; i += 32) {
+        const float2 v = __ldcg(reinterpret_cast<const float2*>(a.partials) + i);
+        d2 += (double)v.x;
+        d3 += (double)v.y;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        d2 += __shfl_xor_sync(FULL_MASK, d2, o);
+        d3 += __shfl_xor_sync(FULL_MASK, d3, o);
+    }
+    if (lane == 0) finish_losses(a, d2, d3);
+}
+
 // BT / SL: bones and 32-pose slices per tile at compile time (0 = read from the arguments); WORLD: a per-frame world
-// transform may be given (ZeroTrajectory, the only trajectory model of the reference, gives none)
-template <int BT, int SL, bool WORLD>
+// transform may be given (ZeroTrajectory, the only trajectory model of the reference, gives none); LONE: the launch
+// has at most one tile per CTA (only selects which forward walk is compiled in: the straight-line walks are most of
+// the code, and a kernel that runs every phase once per launch pays for its size in instruction fetches)
+template <int BT, int SL, bool WORLD, bool LONE>
 __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) {
     extern __shared__ __align__(16) float smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NT = blockDim.x, W = NT >> 5;
@@ -486,40 +532,14 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     __shared__ int next_s[2];
     __shared__ int last_s;
     if (tid == 0) last_s = 0;
-    auto finish = [&](double d2, double d3) {   // one thread of the last CTA
-        const double c2 = a.mask ? (double)__ldcg(a.count2) : (double)total * B * 2;
-        const float l2 = (float)(d2 / c2), l3 = (float)(d3 / a.count3);
-        a.losses[0] = l2; a.losses[1] = l3; a.losses[2] = a.w2 * l2 + a.w3 * l3;
-        a.losses[3] = (float)d2; a.losses[4] = (float)c2; a.losses[5] = (float)d3; a.losses[6] = (float)a.count3;
-        a.losses[7] = 0.f;
-        *a.ticket = 0u;   // self-resetting workspace header: ready for the next launch
-        *a.count2 = 0;
-        *a.arrive = 0u;
-        *a.next = 0u;
+    auto fold_args = [&]() {
+        FoldArgs f;
+        f.losses = a.losses; f.partials = a.partials; f.header = a.ticket;
+        f.count3 = a.count3; f.all2 = (double)total * B * 2; f.w2 = a.w2; f.w3 = a.w3; f.mask = a.mask;
+        return f;
     };
-    // few tiles (a.warp_fold): the warp that stored this CTA's last partial waits for its ticket and, if it is the
-    // grid's last, folds right there, behind the backward phases of the other warps
-    auto ticket_and_fold = [&]() {
-        bool lastw = false;
-        if (lane == 0) {
-            __threadfence();
-            lastw = atomicAdd(a.ticket, 1u) == gridDim.x - 1;
-        }
-        if (!__shfl_sync(FULL_MASK, lastw, 0)) return;
-        __threadfence();
-        double d2 = 0.0, d3 = 0.0;
-        for (int i = lane; i < ntiles; i += 32) {
-            const float2 v = __ldcg(reinterpret_cast<const float2*>(a.partials) + i);
-            d2 += (double)v.x;
-            d3 += (double)v.y;
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            d2 += __shfl_xor_sync(FULL_MASK, d2, o);
-            d3 += __shfl_xor_sync(FULL_MASK, d3, o);
-        }
-        if (lane == 0) finish(d2, d3);
-    };
+    auto finish = [&](double d2, double d3) { finish_losses(fold_args(), d2, d3); };
+    auto ticket_and_fold = [&]() { warp_ticket_and_fold(fold_args(), ntiles); };
     unsigned my_ticket = 0xffffffffu;   // (drawn by one lane after this CTA's last partial store, looked at on exit)
     auto take_ticket = [&]() {
         __threadfence();
@@ -671,8 +691,8 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         //      barriers.  Any other tree, and one tile per CTA (latency counts, not wavefronts: three short instruction
         //      streams beat one long one): three warps per slice, one per column of A (a column needs only the same
         //      column of the parent), each walking the whole tree in bone order.
-        const bool limbs = BT == 26 && a.fk_groups > 0;
-        const int fk_warps = limbs ? a.fk_groups * slices : 3 * slices;
+        constexpr bool limbs = BT == 26 && !LONE;
+        const int fk_warps = limbs ? 5 * slices : 3 * slices;
         if (limbs && warp < fk_warps) {
             const int grp = warp / slices, col = (warp - grp * slices) * 32 + lane, pl = min(col, np - 1);
             const bool valid = col < np;
@@ -730,41 +750,24 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             };
 #define P2C_RUN(B0, B1) \
     _Pragma("unroll") for (int b = B0; b < B1; ++b) bone(b, carla_parent(b), b == B0);
-            const int g = a.fk_groups;
-            if (g == 1) {
-                P2C_RUN(0, 26)
-            } else if (grp == 0) {
-                const int waiters = (g == 3 ? 2 : 3) * slices * 32;
-                if (a.clocks && (int)blockIdx.x == a.clock_cta && tid == 0) g_tile_clocks[27] = clock64();
+            if (grp == 0) {
                 P2C_RUN(0, 2)
-                named_arrive(3, waiters);   // hips
-                if (a.clocks && (int)blockIdx.x == a.clock_cta && tid == 0) g_tile_clocks[28] = clock64();
+                named_arrive(3, 3 * slices * 32);   // hips
                 P2C_RUN(2, 4)
-                named_arrive(4, waiters);   // spine01
-                if (a.clocks && (int)blockIdx.x == a.clock_cta && tid == 0) g_tile_clocks[29] = clock64();
+                named_arrive(4, 3 * slices * 32);   // spine01
                 P2C_RUN(4, 8)               // left arm
-            } else if (g == 3) {
-                if (grp == 1) {
-                    named_barrier(4, 2 * slices * 32);
-                    P2C_RUN(8, 16)          // neck, head, eyes, right arm
-                } else {
-                    named_barrier(3, 2 * slices * 32);
-                    P2C_RUN(16, 26)         // legs
-                }
+            } else if (grp == 1) {
+                named_barrier(4, 3 * slices * 32);
+                P2C_RUN(8, 12)              // neck, head, eyes
+            } else if (grp == 2) {
+                named_barrier(4, 3 * slices * 32);
+                P2C_RUN(12, 16)             // right arm
+            } else if (grp == 3) {
+                named_barrier(3, 3 * slices * 32);
+                P2C_RUN(16, 21)             // right leg
             } else {
-                if (grp == 1) {
-                    named_barrier(4, 3 * slices * 32);
-                    P2C_RUN(8, 12)          // neck, head, eyes
-                } else if (grp == 2) {
-                    named_barrier(4, 3 * slices * 32);
-                    P2C_RUN(12, 16)         // right arm
-                } else if (grp == 3) {
-                    named_barrier(3, 3 * slices * 32);
-                    P2C_RUN(16, 21)         // right leg
-                } else {
-                    named_barrier(3, 3 * slices * 32);
-                    P2C_RUN(21, 26)         // left leg
-                }
+                named_barrier(3, 3 * slices * 32);
+                P2C_RUN(21, 26)             // left leg
             }
 #undef P2C_RUN
             fence_async_smem();
@@ -1016,15 +1019,17 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 if (have) rowp[0] = nv + carry;
             }
         }
-        if (a.clocks && (int)blockIdx.x == a.clock_cta && tid == 0) g_tile_clocks[23] = clock64();
         // (two warps without a column when W >= 6 slices + 2: both jobs wait on global memory, off the critical path)
         if (nxt < ntiles && warp == W - 1) fill_rows(nxt, (it + 1) & 1);
         if (warp == W - 2) {
-            if (lane == 0) {
-                float x = 0.f, y = 0.f;
-                for (int w = 0; w < W; ++w) { x += red[w * 2]; y += red[w * 2 + 1]; }
-                a.partials[tile * 2] = x;
-                a.partials[tile * 2 + 1] = y;
+            {   // (a fixed shuffle tree over the per-warp sums: W <= 32)
+                float x = lane < W ? red[lane * 2] : 0.f, y = lane < W ? red[lane * 2 + 1] : 0.f;
+                x = warp_sum(x);
+                y = warp_sum(y);
+                if (lane == 0) {
+                    a.partials[tile * 2] = x;
+                    a.partials[tile * 2 + 1] = y;
+                }
             }
             if (nxt >= ntiles) {   // this CTA's last tile
                 if (a.warp_fold) ticket_and_fold();
@@ -1041,7 +1046,8 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             const int nt = slices * B;
 #pragma unroll 1
             for (int task = warp; task < nt; task += W) {
-                const int sl = task >= B ? 1 : 0, b = task - sl * B, par = a.parent[b];
+                const int sl = task >= B ? 1 : 0, b = task - sl * B;
+                const int par = BT == 26 ? carla_parent(b) : a.parent[b];   // (arithmetic: no cold constant-bank read)
                 const int col = sl * 32 + lane, pl = min(col, np - 1);
                 const V3 sx{XR[(b * 3) * PS + col], XR[(b * 3 + 1) * PS + col], XR[(b * 3 + 2) * PS + col]};
                 const V3 sg{GV[(b * 3) * PS + col], GV[(b * 3 + 1) * PS + col], GV[(b * 3 + 2) * PS + col]};
@@ -1054,8 +1060,6 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 XR[(b * 3) * PS + col] = y.x; XR[(b * 3 + 1) * PS + col] = y.y; XR[(b * 3 + 2) * PS + col] = y.z;
             }
         }
-        if (a.clocks && (int)blockIdx.x == a.clock_cta && tid == 0) g_tile_clocks[25] = clock64();
-        if (a.clocks && (int)blockIdx.x == a.clock_cta && tid == NT - 64) g_tile_clocks[26] = clock64();
         fence_async_smem();   // (the scratch rows are about to be overwritten by TMA)
         __syncthreads();   // #7
         TILE_CLOCK(9)
@@ -1276,11 +1280,6 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     a.count_inline = t.count_inline;
     a.dynamic = t.dynamic;
     a.warp_fold = ((long)p->n_clips * p->clip_len + t.P - 1) / t.P <= 1024;
-    {   // forward-walk groups: all five limbs apart when the warps are there (and four are left for the mask count)
-        const int w = t.threads / 32;
-        a.fk_groups = t.count_inline ? 0 : w > 5 * t.slices ? 5 : w > 3 * t.slices ? 3 : 1;   // 0: column warps
-        if (getenv("P2C_TILE_FK_GROUPS")) a.fk_groups = atoi(getenv("P2C_TILE_FK_GROUPS"));   // debug
-    }
     // one partial pair per tile: at most n_poses floats, inside the scratch area every caller provides
     // (p2c_fused_step_workspace_floats: 16 header words, then >= 6 * n_bones * n_poses floats of scratch)
     a.partials = p->workspace + 16;
@@ -1299,10 +1298,16 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     const bool world = p->world_loc || p->world_rot;
     bool carla = B == 26;
     for (int b = 0; b < B && carla; ++b) carla = p->tree.parent[b] == carla_parent(b);
-    const int ki = world ? 3 : carla ? (t.slices == 1 ? 0 : 1) : 2;   // CARLA_SKELETON: compile-time tree and slices
-    const kern_t k = ki == 0 ? tile_kernel<26, 1, false> : ki == 1 ? tile_kernel<26, 2, false>
-                   : ki == 2 ? tile_kernel<0, 0, false> : tile_kernel<0, 0, true>;
-    static bool configured[4] = {false, false, false, false};
+    // CARLA_SKELETON: compile-time tree and slices, one instance per launch shape (limb walk needs 5 warps per slice)
+    const bool limb_ok = t.threads / 32 > 5 * t.slices;
+    const int ki = world ? 5 : !carla ? 4 : t.count_inline ? (t.slices == 1 ? 2 : 3) : !limb_ok ? 4 : (t.slices == 1 ? 0 : 1);
+    const kern_t k = ki == 0   ? tile_kernel<26, 1, false, false>
+                     : ki == 1 ? tile_kernel<26, 2, false, false>
+                     : ki == 2 ? tile_kernel<26, 1, false, true>
+                     : ki == 3 ? tile_kernel<26, 2, false, true>
+                     : ki == 4 ? tile_kernel<0, 0, false, false>
+                               : tile_kernel<0, 0, true, false>;
+    static bool configured[6] = {false, false, false, false, false, false};
     if (!configured[ki]) {
         cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
         if (e != cudaSuccess) return (int)e;

@@ -27,9 +27,6 @@ if w[16]:
         w[17] - w[16], w[18] - w[17], w[19] - w[18], w[20] - w[19]))
 if w[21]:
     print('forward walk done %d, count poll done %d cycles after barrier 3' % (w[21] - w[4], w[22] - w[4]))
-if w[23]:
-    print('after loss barrier: subtree walk done %d, partials published %d; after barrier 6: y task of warp 0 done %d, '
-          'of warp W-2 %d' % (w[23] - w[7], w[24] - w[7], w[25] - w[8], w[26] - w[8]))
 ct = (ctypes.c_ulonglong * 2048)()
 lib.p2c_debug_cta_times.argtypes = [ctypes.c_void_p]
 assert lib.p2c_debug_cta_times(ct) == 0
@@ -48,6 +45,3 @@ tt = np.array(list(ct), dtype=np.int64).reshape(-1, 2)
 k = int(os.environ.get('P2C_TILE_CTA', '0'))
 print('CTA %d: %d cycles in %.1f us => SM clock %.3f GHz' % (k, w[20] - w[16], (tt[k, 1] - tt[k, 0]) / 1e3,
                                                            (w[20] - w[16]) / float(tt[k, 1] - tt[k, 0])))
-if w[27]:
-    print('forward walk, group 0 after barrier 3: start %d, hips done %d, spine01 done %d, arm done %d' % (
-        w[27] - w[4], w[28] - w[4], w[29] - w[4], w[21] - w[4]))
