@@ -105,7 +105,7 @@ class Shard(object):
     """One rank's shard of the workload: `n_sets` rotating buffer sets (their footprint together exceeds L2, so every
     timed step streams its inputs from HBM), each with a prebuilt C-ABI argument struct and a captured CUDA graph."""
 
-    def __init__(self, dev, n_clips, clip_len, seed, want_bytes=192 << 20, max_sets=16, capture=True):
+    def __init__(self, dev, n_clips, clip_len, seed, want_bytes=192 << 20, max_sets=16, capture=True, world=1):
         import oracle as O  # checker-side data only: reference skeleton table + camera constants (init, untimed)
         from pedestrians_video_2_carla_b200 import _lib, ops
         self.lib, self.cdll, self.ops, self.dev = _lib, _lib.load(), ops, dev
@@ -147,6 +147,8 @@ class Shard(object):
             s['args'].workspace = _lib.ptr(ws)
         self.launches_per_step = int(self.cdll.p2c_fused_step_launches(self.sets[0]['args']))
         self.graphs = None
+        self.world = world
+        self.allreduce = 'none (1 rank)' if world == 1 else 'eager, after every step graph'
         if capture:
             self._capture()
 
@@ -168,12 +170,19 @@ class Shard(object):
         """Enqueue step i on the current stream (direct C-ABI call; no torch ops)."""
         self.lib.check(self.cdll.p2c_fused_step(self.sets[i % self.n_sets]['args'], self.lib.stream()), 'fused_step')
 
+    def _reduce(self, i):
+        """The path's only exchange: the four loss sums of step i, summed over the ranks (NCCL)."""
+        import torch.distributed as dist
+        return dist.all_reduce(self.sets[i % self.n_sets]['losses'][3:7], async_op=True)
+
     def _capture(self):
         st = torch.cuda.Stream(device=self.dev)
         st.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(st):
             for i in range(self.n_sets):
                 self.launch(i)
+                if self.world > 1:
+                    self._reduce(i).wait()
         torch.cuda.current_stream().wait_stream(st)
         torch.cuda.synchronize()
         self.graphs = []
@@ -183,20 +192,40 @@ class Shard(object):
                 self.launch(i)
             self.graphs.append(gr)
         self.round = torch.cuda.CUDAGraph()   # one replay = n_sets consecutive steps (one per buffer set)
-        with torch.cuda.graph(self.round):
-            for i in range(self.n_sets):
-                self.launch(i)
+        if self.world == 1:
+            with torch.cuda.graph(self.round):
+                for i in range(self.n_sets):
+                    self.launch(i)
+        else:
+            # N > 1: the all-reduce of every step is captured INTO the round graph, forked onto the process group's
+            # own stream: it runs beside the next step's kernel (a few bytes over NVLink; pure latency) and joins
+            # before the replay ends.  If this torch / NCCL pair cannot capture collectives, the steps fall back to
+            # single-step graphs followed by an eager all-reduce.
+            try:
+                with torch.cuda.graph(self.round):
+                    works = []
+                    for i in range(self.n_sets):
+                        self.launch(i)
+                        works.append(self._reduce(i))
+                    for w in works:
+                        w.wait()
+                self.allreduce = 'captured in the step graph, on the NCCL stream beside the next step'
+            except Exception as e:   # noqa: BLE001 - any capture failure takes the eager route
+                sys.stderr.write('bench: collective capture failed (%s); eager all-reduce per step\n' % (e,))
+                self.round = None
         torch.cuda.synchronize()
 
     def run_steps(self, first, count):
         """Steps first .. first+count-1, as whole-round graph replays where aligned, single-step graphs otherwise."""
         i, end = first, first + count
         while i < end:
-            if i % self.n_sets == 0 and end - i >= self.n_sets:
+            if self.round is not None and i % self.n_sets == 0 and end - i >= self.n_sets:
                 self.round.replay()
                 i += self.n_sets
             else:
                 self.graphs[i % self.n_sets].replay()
+                if self.world > 1:
+                    self._reduce(i).wait()
                 i += 1
 
 
@@ -222,12 +251,7 @@ def timed_region(shard, steps, warmup, world, sampler_note=None):
     dev = shard.dev
 
     def step_range(first, count):
-        if world == 1:
-            shard.run_steps(first, count)
-        else:
-            for i in range(first, first + count):
-                shard.graphs[i % shard.n_sets].replay()
-                dist.all_reduce(shard.sets[i % shard.n_sets]['losses'][3:7])
+        shard.run_steps(first, count)
     step_range(0, warmup)
     torch.cuda.synchronize()
     if world > 1:
@@ -404,20 +428,20 @@ def main():
             dist.barrier()
     dev = torch.device('cuda', local)
     torch.cuda.set_device(dev)
-    shard = Shard(dev, args.clips, args.clip_len, SEED + rank)
+    shard = Shard(dev, args.clips, args.clip_len, SEED + rank, world=world)
 
     sampler = ClockSampler(local)
     sampler.start()
     ms = timed_region(shard, args.steps, args.warmup, world)
     note = 'timed region'
-    if len(sampler.samples) < 8:   # microsecond steps: keep the same load running until NVML has been polled enough
-        t_end = time.perf_counter() + 0.4
-        i = 0
-        while time.perf_counter() < t_end:
-            shard.run_steps(i, shard.n_sets)
-            i += shard.n_sets
+    if ms < 400.0:   # microsecond steps: keep the same load running until NVML has been polled enough.  The decision
+        # and the number of extra rounds come from the max-reduced time, so every rank replays the same number of
+        # graphs (they hold collectives when N > 1)
+        rounds = int(400.0 / max(ms / args.steps * shard.n_sets, 1e-3)) + 1
+        for r in range(rounds):
+            shard.run_steps(r * shard.n_sets, shard.n_sets)
         torch.cuda.synchronize()
-        note = 'timed region + the same step loop continued for 0.4 s (region shorter than the NVML poll)'
+        note = 'timed region + the same step loop continued for ~0.4 s (region shorter than the NVML poll)'
     sampler.stop()
     ms_per_step = ms / args.steps
     poses_total = world * shard.poses
@@ -430,7 +454,7 @@ def main():
     line = {'metric': METRIC, 'value': round(value, 1), 'unit': 'poses/s', 'n_gpus': world, 'steps': args.steps,
             'warmup': args.warmup, 'ms_per_step': round(ms_per_step, 6), 'higher_is_better': True, 'scaling': 'weak',
             'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
-            'config': config_of(args, world),
+            'config': dict(config_of(args, world), allreduce=shard.allreduce),
             'clocks': sampler.summary(note),
             'e2e': {'value': round(e2e_value, 1), 'unit': 'poses/s', 'h2d_bytes_per_step': h2d,
                     'd2h_bytes_per_step': d2h, 'steps': e2e_steps,
@@ -449,9 +473,18 @@ def main():
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world > 1:
+        # graphs that hold captured NCCL kernels go first; then leave without running the process group's
+        # destructors (a communicator torn down at interpreter exit, with graph-captured collectives behind it, can
+        # wait forever on this torch / NCCL pair)
         import torch.distributed as dist
+        shard.round = None
+        shard.graphs = None
+        torch.cuda.synchronize()
         dist.barrier()
-        dist.destroy_process_group()
+        torch.cuda.synchronize()
+        sys.stdout.flush()
+        sys.stderr.flush()
+        os._exit(0)
 
 
 def sweep(dev):
