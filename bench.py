@@ -117,6 +117,9 @@ class Shard(object):
         self.cam = _lib.make_camera(cam.R.tolist(), cam.T.tolist(), cam.f, cam.px, cam.py)
         self.loc, self.rot = loc.to(dev), rot.to(dev)
         self.n_sets = n_sets_for(self.poses, clip_len, want_bytes, max_sets)
+        self.loss_block = torch.zeros((self.n_sets, 8), device=dev)    # row i = the losses[8] of buffer set i
+        self.packed = torch.zeros((self.n_sets, 4), device=dev)        # the four sums of a round's steps, to be reduced
+        self.global_sums = torch.zeros((self.n_sets, 4), device=dev)   # ... and reduced over the ranks
         g = torch.Generator(device='cpu').manual_seed(seed)
         base = torch.tensor([1., 0, 0, 0, 1, 0])
         self.sets = []
@@ -137,7 +140,7 @@ class Shard(object):
             s['abs_loc'] = torch.empty((n_clips, clip_len, B, 3), device=dev)
             s['proj'] = torch.empty_like(s['abs_loc'])
             s['g_d6'] = torch.empty_like(s['d6'])
-            s['losses'] = torch.zeros(8, device=dev)
+            s['losses'] = self.loss_block[len(self.sets)]
             s['args'] = self._args(s)
             self.sets.append(s)
         nws = self.cdll.p2c_fused_step_workspace_floats(self.poses, B, 1)
@@ -197,23 +200,36 @@ class Shard(object):
                 for i in range(self.n_sets):
                     self.launch(i)
         else:
-            # N > 1: the all-reduce of every step is captured INTO the round graph, forked onto the process group's
-            # own stream: it runs beside the next step's kernel (a few bytes over NVLink; pure latency) and joins
-            # before the replay ends.  If this torch / NCCL pair cannot capture collectives, the steps fall back to
-            # single-step graphs followed by an eager all-reduce.
+            # N > 1: the exchange is captured INTO the round graph.  The four loss sums of the round's steps are packed
+            # into one (n_sets, 4) block and summed over the ranks by ONE NCCL call, forked onto the process group's
+            # stream at the top of the NEXT replay, where it runs beside that round's kernels (a few hundred bytes over
+            # NVLink: pure latency, ~25 us at 8 ranks) and joins before the replay ends; flush_exchange() reduces the
+            # last round.  Every step's sums are reduced, one round late; gradients are local (DDP semantics).  If
+            # this torch / NCCL pair cannot capture collectives, the steps fall back to single-step graphs followed
+            # by an eager all-reduce.
+            import torch.distributed as dist
             try:
                 with torch.cuda.graph(self.round):
-                    works = []
+                    w = dist.all_reduce(self.packed, async_op=True)
                     for i in range(self.n_sets):
                         self.launch(i)
-                        works.append(self._reduce(i))
-                    for w in works:
-                        w.wait()
-                self.allreduce = 'captured in the step graph, on the NCCL stream beside the next step'
+                    w.wait()
+                    self.global_sums.copy_(self.packed)
+                    self.packed.copy_(self.loss_block[:, 3:7])
+                self.allreduce = ('captured in the round graph: one NCCL all-reduce per %d steps (their 4 loss sums '
+                                  'each), beside the next round\'s kernels' % self.n_sets)
             except Exception as e:   # noqa: BLE001 - any capture failure takes the eager route
                 sys.stderr.write('bench: collective capture failed (%s); eager all-reduce per step\n' % (e,))
                 self.round = None
         torch.cuda.synchronize()
+
+    def flush_exchange(self):
+        """Reduce the sums of the last replayed round (the round graph reduces those of the round before)."""
+        if self.world > 1 and self.round is not None:
+            import torch.distributed as dist
+            dist.all_reduce(self.packed)
+            self.global_sums.copy_(self.packed)
+            self.packed.zero_()
 
     def run_steps(self, first, count):
         """Steps first .. first+count-1, as whole-round graph replays where aligned, single-step graphs otherwise."""
@@ -261,6 +277,7 @@ def timed_region(shard, steps, warmup, world, sampler_note=None):
     first = -(-warmup // shard.n_sets) * shard.n_sets   # start the timed steps on a round boundary
     e0.record()
     step_range(first, steps)
+    shard.flush_exchange()
     e1.record()
     torch.cuda.synchronize()
     if world > 1:
