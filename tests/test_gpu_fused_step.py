@@ -214,3 +214,53 @@ def test_full_size_properties(ops, lib, n, l):
     again.loc_2d_3d.backward()
     assert float(again.loc_2d_3d.detach()) == 0.0
     assert float(x.grad.abs().max()) == 0.0
+
+
+@pytest.mark.parametrize('n,l', [(2048, 16), (640, 64)])
+def test_many_tiles_deterministic_and_chunk_consistent(ops, lib, n, l):
+    """More tiles than CTAs (tiles handed out by the grid-wide counter, mask count in the pre-pass, one loss partial per
+    tile): (1) two runs are bitwise equal although the tile -> CTA assignment differs from run to run; (2) with the
+    mask off, the same clips run in chunks small enough for one tile per CTA (the other kernel instance) give the same
+    outputs bit for bit, gradients equal up to the 1/N of the mean, and loss sums that add up."""
+    g = torch.Generator().manual_seed(7 * n + l)
+    loc, rot, _, par = O.reference_tensors(torch.float32)
+    cam = O.training_camera()
+    tree, cams = lib.make_tree(par), lib.make_camera(cam.R.tolist(), cam.T.tolist(), cam.f, cam.px, cam.py)
+    sid = torch.randint(0, 4, (n,), generator=g).int().to(DEV)
+    loc, rot = loc.to(DEV), rot.to(DEV)
+    base = torch.tensor([1., 0, 0, 0, 1, 0])
+    d6 = (torch.randn((n, l, 26, 6), generator=g) * 0.3 + base).to(DEV)
+    d6_gt = (torch.randn((n, l, 26, 6), generator=g) * 0.3 + base).to(DEV)
+    zeros = torch.zeros((n, l, 26, 3), device=DEV)
+    t = ops.fused_step(d6_gt, tree, cams, loc, rot, zeros, zeros, ref_index=sid)
+    gt2, gt3 = t.projection_2d_transformed.clone(), t.absolute_pose_loc.clone()
+    drop = (torch.rand((n, l, 26), generator=g) < 0.1).to(DEV)
+    gt2[drop] = 0
+
+    def run(lo, hi, mask):
+        x = d6[lo:hi].clone().requires_grad_(True)
+        r = ops.fused_step(x, tree, cams, loc, rot, gt2[lo:hi].contiguous(), gt3[lo:hi].contiguous(),
+                           ref_index=sid[lo:hi].contiguous(), mask_missing_joints=mask)
+        r.loc_2d_3d.backward()
+        return r, x.grad
+
+    r1, g1 = run(0, n, True)
+    r2, g2 = run(0, n, True)
+    assert torch.equal(r1.losses, r2.losses)
+    assert torch.equal(g1, g2)
+    kept = (gt2[..., 0] != 0) & (gt2[..., 1] != 0)
+    kept[..., 1] = True   # hips: always kept (utils/tensors.py:29-40)
+    assert float(r1.losses[4]) == float(2 * kept.sum())   # kept (joint, channel) pairs
+
+    full, gf = run(0, n, False)
+    chunk = 256 if l == 16 else 128   # clips per chunk: 128 tiles <= SMs (one tile per CTA)
+    sums = torch.zeros(4, dtype=torch.float64)
+    for lo in range(0, n, chunk):
+        hi = min(n, lo + chunk)
+        part, gp = run(lo, hi, False)
+        assert torch.equal(part.absolute_pose_loc, full.absolute_pose_loc[lo:hi])
+        assert torch.equal(part.projection_2d, full.projection_2d[lo:hi])
+        assert torch.equal(part.absolute_pose_rot, full.absolute_pose_rot[lo:hi])
+        assert_close('chunk grad', gp * ((hi - lo) / n), gf[lo:hi], tol=2e-6)
+        sums += part.losses[3:7].double().cpu()
+    assert_close('loss sums', full.losses[3:7].double().cpu(), sums, tol=1e-6)
