@@ -31,6 +31,8 @@ def build(force=False, verbose=False):
         return LIB_PATH
     nvcc = shutil.which('nvcc') or '/usr/local/cuda/bin/nvcc'
     flags = [f for f in NVCC_FLAGS if f != '--use_fast_math=false']
+    if os.environ.get('P2C_BUILD_CLOCKS') == '1':   # debug build: phase clocks of the tile kernel (tools/tile_clocks.py)
+        flags.append('-DP2C_CLOCKS_BUILD')
     objs = []
     build_dir = os.path.join(PKG_DIR, 'build')
     os.makedirs(build_dir, exist_ok=True)

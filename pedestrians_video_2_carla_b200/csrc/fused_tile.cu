@@ -345,10 +345,19 @@ __device__ __forceinline__ unsigned long long globaltimer() {
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
     return t;
 }
+// phase clocks are a debug build (P2C_BUILD_CLOCKS=1 python -c 'import __graft_entry__ as g; g.build()'): the checks
+// cost 2 % of the step when compiled in
+#ifndef P2C_CLOCKS_BUILD
+#define CTA_CLOCK(k)
+#define TILE_CLOCK(k)
+#define DEBUG_CLOCK(stmt)
+#else
+#define DEBUG_CLOCK(stmt) stmt
 #define CTA_CLOCK(k) \
     if (a.clocks && (int)blockIdx.x == a.clock_cta && threadIdx.x == 0) g_tile_clocks[k] = clock64();
 #define TILE_CLOCK(k)                                                              \
     if (a.clocks && (int)blockIdx.x == a.clock_cta && (int)it == a.clocks - 1 && tid == 0) g_tile_clocks[k] = clock64();
+#endif
 
 __device__ __forceinline__ void named_arrive(int id, int threads) {
     asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(threads) : "memory");
@@ -407,6 +416,14 @@ __device__ __forceinline__ void sts3(float* pose, int b, const V3& v) {
 }
 
 // ---- loss totals (rarely executed, kept out of line: the double-precision divisions are long instruction sequences)
+// draw a ticket with RELEASE semantics (this thread's partial store is ordered before it).  __threadfence() would
+// also do, but it is a sequentially consistent fence followed by an L1 invalidate (MEMBAR.SC.GPU + CCTL.IVALL), which
+// stalls the whole SM's memory pipe for ~2k cycles in the middle of the backward phases
+__device__ __forceinline__ unsigned ticket_release(unsigned int* p) {
+    unsigned t;
+    asm volatile("atom.add.release.gpu.global.u32 %0, [%1], 1;" : "=r"(t) : "l"(p) : "memory");
+    return t;
+}
 struct FoldArgs {   // (by value: a reference to the kernel parameters would force a local copy of all of them)
     float* losses;
     const float* partials;
@@ -431,10 +448,7 @@ __device__ __noinline__ void finish_losses(const FoldArgs a, double d2, double d
 __device__ __noinline__ void warp_ticket_and_fold(const FoldArgs a, int ntiles) {
     const int lane = threadIdx.x & 31;
     bool lastw = false;
-    if (lane == 0) {
-        __threadfence();
-        lastw = atomicAdd(a.header, 1u) == gridDim.x - 1;
-    }
+    if (lane == 0) lastw = ticket_release(a.header) == gridDim.x - 1;
     if (!__shfl_sync(FULL_MASK, lastw, 0)) return;
     __threadfence();
     double d2 = 0.0, d3 = 0.0;
@@ -463,7 +477,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     const int B3 = B * 3, B6 = B * 6, B9 = B * 9, PS = 32 * slices, L = a.L;
     const TilePlan sm = tile_plan(PS, B);
     CTA_CLOCK(16)
-    if (a.clocks && threadIdx.x == 0 && blockIdx.x < 1024) g_cta_times[blockIdx.x * 2] = globaltimer();
+    DEBUG_CLOCK(if (a.clocks && threadIdx.x == 0 && blockIdx.x < 1024) g_cta_times[blockIdx.x * 2] = globaltimer();)
     float* D = smem + sm.d;
     float* G3 = smem + sm.g3;     // G3 and G2 are adjacent: together they hold the re-fetched 6-D records
     float* G2 = smem + sm.g2;
@@ -541,10 +555,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     auto finish = [&](double d2, double d3) { finish_losses(fold_args(), d2, d3); };
     auto ticket_and_fold = [&]() { warp_ticket_and_fold(fold_args(), ntiles); };
     unsigned my_ticket = 0xffffffffu;   // (drawn by one lane after this CTA's last partial store, looked at on exit)
-    auto take_ticket = [&]() {
-        __threadfence();
-        my_ticket = atomicAdd(a.ticket, 1u);
-    };
+    auto take_ticket = [&]() { my_ticket = ticket_release(a.ticket); };
     const float k3 = a.w3 * 2.0f / (float)a.count3;
     unsigned it = 0;
     CTA_CLOCK(17)
@@ -771,7 +782,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             }
 #undef P2C_RUN
             fence_async_smem();
-            if (a.clocks && (int)blockIdx.x == a.clock_cta && tid == 0) g_tile_clocks[21] = clock64();
+            DEBUG_CLOCK(if (a.clocks && (int)blockIdx.x == a.clock_cta && tid == 0) g_tile_clocks[21] = clock64();)
         } else if (!limbs && warp < fk_warps) {
             const int jc = warp % 3, col = (warp / 3) * 32 + lane, pl = min(col, np - 1);
             const bool valid = col < np;
@@ -838,7 +849,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 v = *reinterpret_cast<volatile unsigned long long*>(a.count2);
             } while ((unsigned)(v >> 32) < gridDim.x);
             k2_shared = a.w2 * 2.0f / (float)(unsigned)(v & 0xffffffffull);
-            if (a.clocks && (int)blockIdx.x == a.clock_cta) g_tile_clocks[22] = clock64();
+            DEBUG_CLOCK(if (a.clocks && (int)blockIdx.x == a.clock_cta) g_tile_clocks[22] = clock64();)
         }
         __syncthreads();   // #4
         nxt = next_s[it & 1];
@@ -1143,7 +1154,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         }
     }
     CTA_CLOCK(20)
-    if (a.clocks && threadIdx.x == 0 && blockIdx.x < 1024) g_cta_times[blockIdx.x * 2 + 1] = globaltimer();
+    DEBUG_CLOCK(if (a.clocks && threadIdx.x == 0 && blockIdx.x < 1024) g_cta_times[blockIdx.x * 2 + 1] = globaltimer();)
 }
 
 int g_sms = 0;

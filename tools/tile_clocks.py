@@ -1,4 +1,6 @@
-"""Phase timeline of the tile kernel (CTA 0, second tile): P2C_TILE_CLOCKS=1 python tools/tile_clocks.py N L"""
+"""Phase timeline of the tile kernel (CTA P2C_TILE_CTA, n-th tile): needs the debug build of the library,
+  P2C_BUILD_CLOCKS=1 python -c "import __graft_entry__ as g; g.build()"   (touch csrc/fused_tile.cu first)
+  P2C_TILE_CLOCKS=1 python tools/tile_clocks.py N L"""
 import ctypes, os, sys
 os.environ.setdefault('P2C_TILE_CLOCKS', '2')
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
