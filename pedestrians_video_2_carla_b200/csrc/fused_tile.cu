@@ -340,11 +340,13 @@ __host__ __device__ __forceinline__ constexpr int carla_parent(int b) {
 
 __device__ long long g_tile_clocks[64];
 __device__ unsigned long long g_cta_times[2 * 1024];   // debug (P2C_TILE_CLOCKS): globaltimer at entry / exit of every CTA
+#ifdef P2C_CLOCKS_BUILD
 __device__ __forceinline__ unsigned long long globaltimer() {
     unsigned long long t;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
     return t;
 }
+#endif
 // phase clocks are a debug build (P2C_BUILD_CLOCKS=1 python -c 'import __graft_entry__ as g; g.build()'): the checks
 // cost 2 % of the step when compiled in
 #ifndef P2C_CLOCKS_BUILD
@@ -654,13 +656,15 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 }
             }
         }
-        // bone offsets of every pose's skeleton as SoA rows (row 3b+k, column = pose) in the upper half of the scratch
-        // region: the forward walk reads them conflict free instead of going to the table in global memory
+        // bone offsets of the skeleton of every clip the tile touches, one 3B-word record per clip, in the upper half of
+        // the scratch region: the forward walk reads them from there (lanes of one clip read one address: a broadcast)
+        // instead of going to the table in global memory
+        const int clip0 = m0 / L, nclip = (m0 + np - 1) / L - clip0 + 1;
         {
             const int busy = (a.scan && tile_clips * B3 <= 160 && NT >= 256) ? 160 : 0;   // threads that ran the scan
-            for (int i = tid - busy; i >= 0 && i < B3 * PS; i += NT - busy) {
-                const int k = i / PS, col = i - k * PS;
-                GV[i] = __ldg(a.ref_loc + (size_t)row[col] * B3 + k);
+            for (int i = tid - busy; i >= 0 && i < nclip * B3; i += NT - busy) {
+                const int cl = i / B3, k = i - cl * B3;
+                GV[i] = __ldg(a.ref_loc + (size_t)row[max((clip0 + cl) * L - m0, 0)] * B3 + k);
             }
             if (a.mask && a.count_inline) {
                 // utils/tensors.py:29-40 (one tile per CTA): the threads without a scan item count the kept (joint,
@@ -709,6 +713,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             const bool valid = col < np;
             const float* rb = R + pl * B9;
             float* ab = A + pl * B9;
+            const float* lc = GV + ((m0 + pl) / L - clip0) * B3;   // this pose's skeleton offsets
             float P[9], tp[3];   // A and t of the previous bone of the run
             auto rec_ld = [&](const float* base, int b, float* x) {   // 9-word record b of an even-word pose record
                 const float* q = base + 9 * b;
@@ -746,7 +751,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 }
                 float x[9], n[9];
                 rec_ld(rb, b, x);
-                const float l0 = GV[(3 * b) * PS + col], l1 = GV[(3 * b + 1) * PS + col], l2 = GV[(3 * b + 2) * PS + col];
+                const float l0 = lc[3 * b], l1 = lc[3 * b + 1], l2 = lc[3 * b + 2];
 #pragma unroll
                 for (int i = 0; i < 3; ++i)
 #pragma unroll
@@ -788,7 +793,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             const bool valid = col < np;
             const float* rb = R + pl * B9;
             float* ab = A + pl * B9 + jc;
-            const float* lc = GV + col;
+            const float* lc = GV + ((m0 + pl) / L - clip0) * B3;   // this pose's skeleton offsets
             float* tr = TS + jc * PS + col;
             float c0 = 0.f, c1 = 0.f, c2 = 0.f, ct = 0.f;   // column jc of A_{b-1}, component jc of t_{b-1}
             // two bones per trip (B is even); the inputs of the next bone (its rel_rot record, its offset, its parent)
@@ -798,7 +803,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             auto fetch = [&](float* x, int b) {
 #pragma unroll
                 for (int i = 0; i < 9; ++i) x[i] = rb[9 * b + i];
-                x[9] = lc[(3 * b) * PS]; x[10] = lc[(3 * b + 1) * PS]; x[11] = lc[(3 * b + 2) * PS];
+                x[9] = lc[3 * b]; x[10] = lc[3 * b + 1]; x[11] = lc[3 * b + 2];
             };
             auto bone = [&](const float* x, int b, int par) {
                 float p0 = c0, p1 = c1, p2 = c2, tp = ct;
