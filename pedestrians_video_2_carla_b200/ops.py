@@ -347,25 +347,24 @@ class _FusedStep(torch.autograd.Function):
         a.g_pose_in, a.workspace, a.losses = ptr(g_in), ptr(ws), ptr(losses)
         check(lib.p2c_fused_step(a, stream()), 'fused_step')
         ctx.save_for_backward(g_in)
-        ctx.weights = (a.weight_2d, a.weight_3d)
+        ctx.set_materialize_grads(False)
         res = cfg.setdefault('_result', FusedStepResult())
         res.losses = losses
         res.relative_pose_rot, res.absolute_pose_rot, res.absolute_pose_loc = rel_rot, abs_rot, abs_loc
         res.projection_2d, res.projection_2d_transformed = proj, proj_norm
-        return losses[0].clone(), losses[1].clone(), losses[2].clone()
+        # loc_2d / loc_3d are reported values (views of the losses buffer, no autograd edge); the fused sum is the one
+        # differentiable output
+        l2, l3 = losses[0], losses[1]
+        ctx.mark_non_differentiable(l2, l3)
+        return l2, l3, losses[2].clone()
 
     @staticmethod
     def backward(ctx, g2d, g3d, g23):
-        # g_pose_in holds d(w2*loc_2d + w3*loc_3d)/d pose_in.  The common case (loss = loc_2d_3d or the weighted
-        # sum) is a pure scale; separate upstream weights on loc_2d / loc_3d alone are not representable from the
-        # single stored gradient and raise instead of silently returning something wrong.
-        (g_in,) = ctx.saved_tensors
-        for g in (g2d, g3d):
-            if g is not None and bool((g != 0).any()):
-                raise RuntimeError('fused_step: backpropagate through loc_2d_3d (the fused sum); for loc_2d or '
-                                   'loc_3d alone call fused_step with weight_3d=0 or weight_2d=0')
+        # g_pose_in holds d(w2*loc_2d + w3*loc_3d)/d pose_in: the backward is a pure scale by the upstream scalar.
+        # (For loc_2d or loc_3d alone call fused_step with weight_3d=0 or weight_2d=0.)
         if g23 is None:
             return None, None
+        (g_in,) = ctx.saved_tensors
         return g_in * g23, None
 
 
@@ -381,5 +380,5 @@ def fused_step(pose_in, tree, camera, ref_loc, ref_rot, gt_2d, gt_3d, ref_index=
                weight_3d=weight_3d, want_transformed=want_transformed, out=out)
     l2, l3, l23 = _FusedStep.apply(pose_in, cfg)
     res = cfg['_result']
-    res.loc_2d, res.loc_3d, res.loc_2d_3d = l2.detach(), l3.detach(), l23
+    res.loc_2d, res.loc_3d, res.loc_2d_3d = l2, l3, l23
     return res
