@@ -1334,15 +1334,26 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     cfg.blockDim = dim3(t.threads);
     cfg.dynamicSmemBytes = t.smem;
     cfg.stream = st;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
+    attr[1].id = cudaLaunchAttributeCooperative;
+    attr[1].val.cooperative = 1;
     cfg.attrs = attr;
     // programmatic dependent launch: with the count pre-pass in front, this kernel overlaps it up to the loss pass; with
     // one tile per CTA (no pre-pass) the CTAs may be placed while the previous kernel of the stream drains, and wait
-    // (griddepcontrol.wait, before their first global access) until it is complete and flushed
-    cfg.numAttrs = ((a.mask && !a.count_inline) || a.count_inline) ? 1 : 0;
+    // (griddepcontrol.wait, before their first global access) until it is complete and flushed.
+    // One tile per CTA with the mask on: the CTAs wait for each other's joint counts inside the kernel, so the launch
+    // is COOPERATIVE (the whole grid is resident at once or the launch fails: two such kernels on two streams cannot
+    // starve each other).
+    cfg.numAttrs = (a.mask && a.count_inline && !env_on("P2C_TILE_NO_COOP")) ? 2 : 1;
     cudaError_t le = cudaLaunchKernelEx(&cfg, k, a);
+    if (le != cudaSuccess && cfg.numAttrs == 2) {   // (the two attributes together are refused: cooperative only)
+        (void)cudaGetLastError();
+        cfg.attrs = attr + 1;
+        cfg.numAttrs = 1;
+        le = cudaLaunchKernelEx(&cfg, k, a);
+    }
     if (le != cudaSuccess) return (int)le;
     P2C_LAUNCH_CHECK();
     return 0;
