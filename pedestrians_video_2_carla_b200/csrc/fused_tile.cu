@@ -168,16 +168,31 @@ __device__ __forceinline__ void sts9(float* pose, int b, const M3& a) {
     }
 }
 
-// utils/tensors.py:29-40 count of kept (joint, channel) pairs of the 2-D targets (integer => order independent)
+// utils/tensors.py:29-40 count of kept (joint, channel) pairs of the 2-D targets (integer => order independent).
+// The 3-channel records are read as the flat float4 stream they are: four joints per 48-byte group (the tile path
+// only takes 16-byte aligned tensors with an even bone and pose count, so the joint count is a multiple of four).
 __global__ void __launch_bounds__(256) tile_count_kernel(const float* __restrict__ gt2, unsigned joints, unsigned B,
                                                         unsigned gt_c, unsigned hips, int* __restrict__ count) {
     // programmatic dependent launch: the step kernel may start its prologue, input loads and forward phases now; it
     // executes griddepcontrol.wait (= this grid complete and flushed) before it reads the count
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     int c = 0;
-    for (unsigned i = blockIdx.x * 256u + threadIdx.x; i < joints; i += gridDim.x * 256u) {
-        const float* g = gt2 + (size_t)i * gt_c;
-        if (i % B == hips || (__ldg(g) != 0.f && __ldg(g + 1) != 0.f)) c += 2;
+    const float4* q4 = reinterpret_cast<const float4*>(gt2);
+    const unsigned groups = joints >> 2;
+#pragma unroll 2
+    for (unsigned q = blockIdx.x * 256u + threadIdx.x; q < groups; q += gridDim.x * 256u) {
+        const float4 v0 = __ldg(q4 + 3 * (size_t)q), v1 = __ldg(q4 + 3 * (size_t)q + 1), v2 = __ldg(q4 + 3 * (size_t)q + 2);
+        const unsigned j = (q << 2) % B;   // bone of the group's first joint
+        auto wrap = [B](unsigned h) {      // (h < B + 3 and B >= 2: two conditional subtractions reduce it)
+            h -= h >= B ? B : 0u;
+            h -= h >= B ? B : 0u;
+            return h;
+        };
+        const unsigned h0 = j, h1 = wrap(j + 1), h2 = wrap(j + 2), h3 = wrap(j + 3);
+        if (h0 == hips || (v0.x != 0.f && v0.y != 0.f)) c += 2;
+        if (h1 == hips || (v0.w != 0.f && v1.x != 0.f)) c += 2;
+        if (h2 == hips || (v1.z != 0.f && v1.w != 0.f)) c += 2;
+        if (h3 == hips || (v2.y != 0.f && v2.z != 0.f)) c += 2;
     }
     c = __reduce_add_sync(FULL_MASK, c);
     __shared__ int sh[8];
@@ -1304,8 +1319,8 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     a.count3 = (double)total * B * 3;
     cudaStream_t st = (cudaStream_t)stream;
     if (a.mask && !a.count_inline) {
-        long blocks = (total * B + 255) / 256;
-        if (blocks > 4 * 148 * 8) blocks = 4 * 148 * 8;
+        long blocks = (total * B / 4 + 511) / 512;   // two 48-byte groups per thread and trip
+        if (blocks > 148 * 8) blocks = 148 * 8;
         tile_count_kernel<<<(int)blocks, 256, 0, st>>>(p->gt_2d, (unsigned)(total * B), (unsigned)B,
                                                        (unsigned)p->gt_2d_channels, (unsigned)p->hips, a.count2);
         P2C_LAUNCH_CHECK();
