@@ -722,7 +722,8 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         //      streams beat one long one): three warps per slice, one per column of A (a column needs only the same
         //      column of the parent), each walking the whole tree in bone order.
         constexpr bool limbs = BT == 26 && !LONE;
-        const int fk_warps = limbs ? 5 * slices : 3 * slices;
+        constexpr bool lone_limbs = BT == 26 && LONE && SL == 1;   // limb groups of three column warps each
+        const int fk_warps = limbs ? 5 * slices : lone_limbs ? 15 : 3 * slices;
         if (limbs && warp < fk_warps) {
             const int grp = warp / slices, col = (warp - grp * slices) * 32 + lane, pl = min(col, np - 1);
             const bool valid = col < np;
@@ -804,7 +805,8 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             fence_async_smem();
             DEBUG_CLOCK(if (a.clocks && (int)blockIdx.x == a.clock_cta && tid == 0) g_tile_clocks[21] = clock64();)
         } else if (!limbs && warp < fk_warps) {
-            const int jc = warp % 3, col = (warp / 3) * 32 + lane, pl = min(col, np - 1);
+            const int cgrp = lone_limbs ? warp / 3 : 0, cw = lone_limbs ? warp - 3 * cgrp : warp;
+            const int jc = cw % 3, col = (cw / 3) * 32 + lane, pl = min(col, np - 1);
             const bool valid = col < np;
             const float* rb = R + pl * B9;
             float* ab = A + pl * B9 + jc;
@@ -816,8 +818,14 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             float u[12], w[12];
             int pu, pw;
             auto fetch = [&](float* x, int b) {
+                if (BT == 26) {   // (b is a compile-time constant in the unrolled walks: no parity branch)
+                    const M3 r = lds9(rb, b);
 #pragma unroll
-                for (int i = 0; i < 9; ++i) x[i] = rb[9 * b + i];
+                    for (int i = 0; i < 9; ++i) x[i] = r.m[i];
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 9; ++i) x[i] = rb[9 * b + i];
+                }
                 x[9] = lc[3 * b]; x[10] = lc[3 * b + 1]; x[11] = lc[3 * b + 2];
             };
             auto bone = [&](const float* x, int b, int par) {
@@ -840,11 +848,33 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 tr[(3 * b) * PS] = ct;
             };
             if (BT == 26) {   // (one tile per CTA: latency matters, three short instruction streams beat one long one)
-#pragma unroll
-                for (int b = 0; b < 26; ++b) {
-                    fetch(u, b);
-                    bone(u, b, carla_parent(b));
+#define P2C_RUNC(B0, B1)                                  \
+    _Pragma("unroll") for (int b = B0; b < B1; ++b) {     \
+        fetch(u, b);                                      \
+        bone(u, b, carla_parent(b));                      \
+    }
+                if (!lone_limbs) {
+                    P2C_RUNC(0, 26)
+                } else if (cgrp == 0) {   // the same limb groups as above, three column warps each
+                    P2C_RUNC(0, 2)
+                    named_arrive(3, 9 * 32);   // hips
+                    P2C_RUNC(2, 4)
+                    named_arrive(4, 9 * 32);   // spine01
+                    P2C_RUNC(4, 8)
+                } else if (cgrp == 1) {
+                    named_barrier(4, 9 * 32);
+                    P2C_RUNC(8, 12)
+                } else if (cgrp == 2) {
+                    named_barrier(4, 9 * 32);
+                    P2C_RUNC(12, 16)
+                } else if (cgrp == 3) {
+                    named_barrier(3, 9 * 32);
+                    P2C_RUNC(16, 21)
+                } else {
+                    named_barrier(3, 9 * 32);
+                    P2C_RUNC(21, 26)
                 }
+#undef P2C_RUNC
             } else {
                 fetch(u, 0);
                 pu = a.parent[0];
