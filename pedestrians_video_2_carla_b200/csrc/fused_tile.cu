@@ -462,11 +462,9 @@ __device__ __noinline__ void finish_losses(const FoldArgs a, double d2, double d
 }
 // few tiles (a.warp_fold): the warp that stored this CTA's last partial waits for its ticket and, if it is the grid's
 // last, folds right there, behind the backward phases of the other warps
-__device__ __noinline__ void warp_ticket_and_fold(const FoldArgs a, int ntiles) {
+__device__ __noinline__ void warp_fold_if_last(const FoldArgs a, int ntiles, unsigned ticket) {
     const int lane = threadIdx.x & 31;
-    bool lastw = false;
-    if (lane == 0) lastw = ticket_release(a.header) == gridDim.x - 1;
-    if (!__shfl_sync(FULL_MASK, lastw, 0)) return;
+    if (__shfl_sync(FULL_MASK, ticket, 0) != gridDim.x - 1) return;
     __threadfence();
     double d2 = 0.0, d3 = 0.0;
     for (int i = lane; i < ntiles; i += 32) {
@@ -563,6 +561,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     __shared__ int next_s[2];
     __shared__ int last_s;
     if (tid == 0) last_s = 0;
+    unsigned my_ticket = 0xffffffffu;   // (drawn by one lane after this CTA's last partial store, looked at later)
     auto fold_args = [&]() {
         FoldArgs f;
         f.losses = a.losses; f.partials = a.partials; f.header = a.ticket;
@@ -570,8 +569,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         return f;
     };
     auto finish = [&](double d2, double d3) { finish_losses(fold_args(), d2, d3); };
-    auto ticket_and_fold = [&]() { warp_ticket_and_fold(fold_args(), ntiles); };
-    unsigned my_ticket = 0xffffffffu;   // (drawn by one lane after this CTA's last partial store, looked at on exit)
+    auto fold_if_last = [&]() { warp_fold_if_last(fold_args(), ntiles, my_ticket); };
     auto take_ticket = [&]() { my_ticket = ticket_release(a.ticket); };
     const float k3 = a.w3 * 2.0f / (float)a.count3;
     unsigned it = 0;
@@ -978,6 +976,18 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         if (tma) bulk_wait_read_all();   // rel_rot / abs_rot stores have read R and A
         __syncthreads();   // #5
         TILE_CLOCK(7)
+        if (warp == W - 2) {
+            // the tile's loss partial (a fixed shuffle tree over the per-warp sums: W <= 32); on this CTA's last tile
+            // also its ticket, drawn now and looked at after the next phases (an L2 round trip later)
+            float x = lane < W ? red[lane * 2] : 0.f, y = lane < W ? red[lane * 2 + 1] : 0.f;
+            x = warp_sum(x);
+            y = warp_sum(y);
+            if (lane == 0) {
+                a.partials[tile * 2] = x;
+                a.partials[tile * 2 + 1] = y;
+                if (nxt >= ntiles) take_ticket();
+            }
+        }
         if (tma) {
             if (a.abs_loc) bulk_s2g(a.abs_loc + (size_t)m0 * B3, G3, (uint32_t)(np * B3) * 4u);
             if (a.proj) bulk_s2g(a.proj + (size_t)m0 * B3, G2, (uint32_t)(np * B3) * 4u);
@@ -1036,7 +1046,48 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         //      meets every child before its parent):  Sx_b = sum_{d in subtree(b)} g_d x t_d (rows XR), Sg_b = sum g_d
         //      (in place over g_b).  The six components are independent: one warp each per slice, no barrier inside
         //      the walk, the running value stays in a register along chains.
-        if (warp < 6 * slices) {
+        constexpr bool lone_sums = BT == 26 && LONE && SL == 1;
+        if (lone_sums) {
+            // (one tile per CTA) the limbs in parallel, three warps each (component k of both sums); the limb groups
+            // leave the sum of their head bone in its own row and signal, the trunk group adds those rows when it
+            // reaches spine01 (head, right arm) and hips (legs)
+            if (warp < 15) {
+                const int grp = warp / 3, k = warp - 3 * grp;
+                float* rx = XR + k * PS + lane;
+                float* rg = GV + k * PS + lane;
+                float cx = 0.f, cg = 0.f;
+#define P2C_SUMS(HI, LO)                                                                      \
+    _Pragma("unroll") for (int c = HI; c >= LO; --c) {                                        \
+        float vx = rx[c * 3 * PS], vg = rg[c * 3 * PS];                                       \
+        bool changed = false;                                                                 \
+        if (c + 1 <= HI && carla_parent(c + 1) == c) { vx += cx; vg += cg; changed = true; }  \
+        if (LO == 0 && c == 3) {                                                              \
+            named_barrier(5, 15 * 32);                                                        \
+            vx += rx[8 * 3 * PS] + rx[12 * 3 * PS];                                           \
+            vg += rg[8 * 3 * PS] + rg[12 * 3 * PS];                                           \
+        }                                                                                     \
+        if (LO == 0 && c == 1) {                                                              \
+            vx += rx[16 * 3 * PS] + rx[21 * 3 * PS];                                          \
+            vg += rg[16 * 3 * PS] + rg[21 * 3 * PS];                                          \
+        }                                                                                     \
+        if (changed || (LO == 0 && (c == 3 || c == 1))) { rx[c * 3 * PS] = vx; rg[c * 3 * PS] = vg; } \
+        if (c > LO) {                                                                         \
+            if (carla_parent(c) == c - 1) { cx = vx; cg = vg; }                               \
+            else { rx[carla_parent(c) * 3 * PS] += vx; rg[carla_parent(c) * 3 * PS] += vg; }  \
+        }                                                                                     \
+    }
+                if (grp == 0) {
+                    P2C_SUMS(7, 0)
+                } else {
+                    if (grp == 1) { P2C_SUMS(11, 8) }
+                    else if (grp == 2) { P2C_SUMS(15, 12) }
+                    else if (grp == 3) { P2C_SUMS(20, 16) }
+                    else { P2C_SUMS(25, 21) }
+                    named_arrive(5, 15 * 32);
+                }
+#undef P2C_SUMS
+            }
+        } else if (warp < 6 * slices) {
             const int k = warp % 6, col = (warp / 6) * 32 + lane;
             float* rowp = (k < 3 ? XR + k * PS : GV + (k - 3) * PS) + col;
             if (BT == 26) {
@@ -1082,21 +1133,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         }
         // (two warps without a column when W >= 6 slices + 2: both jobs wait on global memory, off the critical path)
         if (nxt < ntiles && warp == W - 1) fill_rows(nxt, (it + 1) & 1);
-        if (warp == W - 2) {
-            {   // (a fixed shuffle tree over the per-warp sums: W <= 32)
-                float x = lane < W ? red[lane * 2] : 0.f, y = lane < W ? red[lane * 2 + 1] : 0.f;
-                x = warp_sum(x);
-                y = warp_sum(y);
-                if (lane == 0) {
-                    a.partials[tile * 2] = x;
-                    a.partials[tile * 2 + 1] = y;
-                }
-            }
-            if (nxt >= ntiles) {   // this CTA's last tile
-                if (a.warp_fold) ticket_and_fold();
-                else if (lane == 0) take_ticket();
-            }
-        }
+        if (nxt >= ntiles && a.warp_fold && warp == W - 2) fold_if_last();   // (the ticket was drawn after the loss pass)
         while (!mbar_try_wait(bars + 2, it & 1u)) {}
         __syncthreads();   // #6
         TILE_CLOCK(8)
@@ -1175,10 +1212,10 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     CTA_CLOCK(19)
 
     if (it == 0 && warp == 0) {   // (a CTA without a tile still takes its ticket)
-        if (a.warp_fold) ticket_and_fold();
-        else if (lane == 0) take_ticket();
+        if (lane == 0) take_ticket();
+        if (a.warp_fold) fold_if_last();
     }
-    if (my_ticket == gridDim.x - 1) last_s = 1;
+    if (!a.warp_fold && my_ticket == gridDim.x - 1) last_s = 1;
     __syncthreads();
     if (last_s) {
         // every CTA has stored its partials and taken its ticket: fold them in tile order, in double, all threads
