@@ -392,7 +392,7 @@ def measured_peak():
 
 # dram__bytes_read.sum + dram__bytes_write.sum of the step kernel, one launch, from the committed `ncu --set full`
 # captures (profiles/r01_tile_<clips>x<len>.txt); writes still in L2 when the kernel ends are not in it
-NCU_DRAM_BYTES = {(256, 16): 5.227e6, (8192, 16): 164.17e6 + 353.15e6, (4096, 64): 327.93e6 + 760.38e6}
+NCU_DRAM_BYTES = {(256, 16): 5.184e6, (8192, 16): 164.11e6 + 353.60e6, (4096, 64): 327.81e6 + 759.60e6}
 
 
 def roofline_of(poses, clip_len, ms_per_step, note):
