@@ -185,6 +185,30 @@ int p2c_fused_step(const p2c_fused_step_t* p, void* stream);
 /* number of kernels p2c_fused_step(p) enqueues (for launch accounting; < 0 = bad argument) */
 int p2c_fused_step_launches(const p2c_fused_step_t* p);
 
+/* ---- loss/cum_pose_changes.py:9-56: per-bone cumulative product of the pose changes over the frames of a clip,
+ *      cumulative[n,t,b] = cumulative[n,t-1,b] . changes[n,t,b] (identity before frame 0); (N,L,B,3,3) both.
+ *      The loss itself is p2c_masked_mse_fwd over 9 channels of the two scans (prediction and target).          */
+int p2c_cum_changes_fwd(const float* changes, float* cumulative, int32_t n_clips, int32_t clip_len,
+                        int32_t n_bones, void* stream);
+int p2c_cum_changes_bwd(const float* changes, const float* cumulative, const float* g_cumulative,
+                        float* g_changes, int32_t n_clips, int32_t clip_len, int32_t n_bones, void* stream);
+
+/* ---- Normalizer.__call__(sample, dim) (transforms/pose/normalization/normalizer.py:20-41) for dim 2 or 3, optionally
+ *      followed by DeNormalizer.from_reference (denormalizer.py:13-37) with a per-clip reference shift / scale, i.e.
+ *      ReferenceSkeletonsDeNormalizer.from_abs / from_projection (reference_skeletons_denormalizer.py:41-91), the
+ *      entry of the absolute_loc(_rot) movements output (modules/layers/projection.py:125-142).
+ *      sample, out (M,J,c), c == dim or (dim 2, c 3: channel 2 carried).  autonormalize 0: denormalise only.
+ *      ref_shift (rows,dim) / ref_scale (rows): both NULL = normalise only.  Pose m belongs to clip m / clip_len;
+ *      its row is ref_index[clip] (int32) or, with ref_index NULL, the clip itself.                              */
+int p2c_renormalize_fwd(const float* sample, float* out, int64_t m, int32_t j, int32_t c, int32_t dim,
+                        int32_t hips, int32_t neck, int32_t autonormalize, float near_zero,
+                        const float* ref_shift, const float* ref_scale, const int32_t* ref_index,
+                        int32_t clip_len, void* stream);
+int p2c_renormalize_bwd(const float* sample, const float* g_out, float* g_sample, int64_t m, int32_t j,
+                        int32_t c, int32_t dim, int32_t hips, int32_t neck, int32_t autonormalize,
+                        float near_zero, const float* ref_scale, const int32_t* ref_index, int32_t clip_len,
+                        void* stream);
+
 const char* p2c_version(void);
 
 #ifdef __cplusplus

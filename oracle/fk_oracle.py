@@ -23,6 +23,8 @@ __all__ = [
     'training_camera', 'reference_camera', 'project', 'abs_from_pose_changes', 'abs_from_relative_rot',
     'projection_module_forward', 'hips_neck_normalize', 'missing_joints_mask', 'loss_loc_2d',
     'loss_loc_3d', 'loss_loc_2d_3d', 'full_step', 'HIPS', 'NECK',
+    'normalize', 'get_shift_scale', 'denormalize', 'reference_denormalize', 'cumulative_changes', 'loss_rot_3d',
+    'loss_cum_pose_changes', 'loss_pose_changes', 'loss_weighted_loc_2d_loc_rot_3d', 'abs_from_abs_loc',
 ]
 
 FILES_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), '..',
@@ -377,3 +379,86 @@ def full_step(pose_changes, ref_loc, ref_rot, parents, cam, gt_proj_transformed,
     out.update(projection_2d=proj, projection_2d_transformed=proj_t, loc_2d=l2d, loc_3d=l3d,
                loc_2d_3d=loss_loc_2d_3d(l2d, l3d))
     return out
+
+
+# ----------------------------------------------------------------------------- SURVEY 8f rows 1-2
+def get_shift_scale(sample, hips=HIPS, neck=NECK):
+    """transforms/pose/normalization/extractor.py:23-36 with hips_neck_extractor.py:6-13."""
+    shift = sample[..., (hips,), :].mean(dim=-2)
+    scale_pt = sample[..., (neck,), :].mean(dim=-2)
+    scale = torch.linalg.norm(scale_pt - shift, dim=shift.ndim - 1, ord=2)
+    scale = scale[((slice(None),) * scale.ndim + (None,) * 2)[:(sample.ndim - 2)]]
+    return shift, scale
+
+
+def normalize(sample, dim=2, hips=HIPS, neck=NECK, near_zero=1e-5):
+    """transforms/pose/normalization/normalizer.py:20-41 for dim = 2 or 3."""
+    shift, scale = get_shift_scale(sample[..., 0:dim], hips, neck)
+    out = torch.empty_like(sample)
+    out[..., 0:dim] = (sample[..., 0:dim] - torch.unsqueeze(shift, -2)) / scale[(...,) + (None,) * 2]
+    if dim == 2 and sample.shape[-1] > 2:
+        out[..., 2] = sample[..., 2]
+    out = torch.nan_to_num(out, nan=0, posinf=0, neginf=0)
+    if dim == 2 and out.shape[-1] > 2:
+        out[..., 0:2] = out[..., 0:2].where(out[..., 2:] >= near_zero, torch.tensor(0.0, dtype=out.dtype))
+    return out
+
+
+def denormalize(sample, scale, shift, dim=2):
+    """transforms/pose/normalization/denormalizer.py:13-29."""
+    out = torch.empty_like(sample)
+    d = scale[(slice(None),) * scale.ndim + (None,) * (sample.ndim - scale.ndim)]
+    h = shift[(slice(None),) * scale.ndim + (None,) * (sample.ndim - shift.ndim) + (slice(None),)]
+    out[..., 0:dim] = (sample[..., 0:dim] * d) + h
+    if dim == 2 and sample.shape[-1] > 2:
+        out[..., 2] = sample[..., 2]
+    return out
+
+
+def reference_denormalize(frames, reference, skeleton_id, dim, autonormalize=False, hips=HIPS, neck=NECK):
+    """reference_skeletons_denormalizer.py:41-91 (from_projection: dim 2, reference = reference projections[..., :2];
+    from_abs: dim 3, reference = reference absolute locations); `reference` holds one entry per skeleton type and
+    `skeleton_id` picks the clip's (the reference stacks them per clip, :60-63 / :84-88)."""
+    if autonormalize:
+        frames = normalize(frames, dim, hips, neck)
+    per_clip = torch.stack([reference[int(i)] for i in skeleton_id], dim=0)
+    shift, scale = get_shift_scale(per_clip, hips, neck)       # denormalizer.py:31-35
+    return denormalize(frames, scale, shift, dim)
+
+
+def abs_from_abs_loc(pose_inputs, reference_abs_loc, skeleton_id):
+    """modules/layers/projection.py:125-136."""
+    return reference_denormalize(pose_inputs, reference_abs_loc, skeleton_id, 3, autonormalize=True)
+
+
+def cumulative_changes(changes):
+    """loss/cum_pose_changes.py:24-52: prev = prev . changes[t] per (clip, bone), frame by frame."""
+    n, l, b = changes.shape[:3]
+    prev = torch.eye(3, dtype=changes.dtype).reshape(1, 3, 3).repeat(n * b, 1, 1)
+    mats = changes.transpose(0, 1).reshape(l, -1, 3, 3)
+    out = []
+    for i in range(l):
+        prev = torch.bmm(prev, mats[i])
+        out.append(prev)
+    return torch.stack(out, dim=0).reshape(l, n, b, 3, 3).transpose(0, 1)
+
+
+def loss_cum_pose_changes(pose_inputs, gt_pose_changes):
+    """loss/cum_pose_changes.py:9-56 with nn.MSELoss('mean')."""
+    return F.mse_loss(cumulative_changes(pose_inputs), cumulative_changes(gt_pose_changes), reduction='mean')
+
+
+def loss_pose_changes(pose_inputs, gt_pose_changes):
+    """loss/pose_changes.py:7-29 with nn.MSELoss('sum') (loss/__init__.py:33)."""
+    return F.mse_loss(pose_inputs, gt_pose_changes, reduction='sum')
+
+
+def loss_rot_3d(abs_rot, gt_abs_rot):
+    """loss/rot_3d.py:9-37."""
+    return F.mse_loss(abs_rot, gt_abs_rot, reduction='mean')
+
+
+def loss_weighted_loc_2d_loc_rot_3d(l2d, l3d, r3d, weights=None):
+    """loss/weighted_loc_2d_loc_rot_3d.py:6-25 (unit weights: loc_2d_loc_rot_3d.py:6-21)."""
+    w = weights or {}
+    return w.get('loc_2d', 1.0) * l2d + w.get('loc_3d', 1.0) * l3d + w.get('rot_3d', 1.0) * r3d

@@ -71,6 +71,12 @@ _SIGS = {
     'p2c_fused_step_workspace_floats': (C.c_int64, [C.c_int64, C.c_int32, C.c_int32]),
     'p2c_fused_step': (C.c_int, [C.POINTER(FusedStep), _P]),
     'p2c_fused_step_launches': (C.c_int, [C.POINTER(FusedStep)]),
+    'p2c_cum_changes_fwd': (C.c_int, [_P, _P, C.c_int32, C.c_int32, C.c_int32, _P]),
+    'p2c_cum_changes_bwd': (C.c_int, [_P, _P, _P, _P, C.c_int32, C.c_int32, C.c_int32, _P]),
+    'p2c_renormalize_fwd': (C.c_int, [_P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
+                                      C.c_int32, C.c_float, _P, _P, _P, C.c_int32, _P]),
+    'p2c_renormalize_bwd': (C.c_int, [_P, _P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
+                                      C.c_int32, C.c_float, _P, _P, C.c_int32, _P]),
     'p2c_version': (C.c_char_p, []),
 }
 

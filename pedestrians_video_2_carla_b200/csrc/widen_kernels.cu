@@ -1,0 +1,272 @@
+// the callers either side of the fused step.
+//   cum_pose_changes scan : loss/cum_pose_changes.py:9-56 (per-bone cumulative product of the pose changes over frames)
+//   Normalizer(dim=2|3) + ReferenceSkeletonsDeNormalizer.from_abs / from_projection:
+//                           transforms/pose/normalization/normalizer.py:20-41, extractor.py:23-36,
+//                           denormalizer.py:13-37, reference_skeletons_denormalizer.py:41-91
+//                           (modules/layers/projection.py:125-142: absolute_loc(_rot) movements output)
+// Both are streaming passes: every input float is read once and every output float written once.
+#include "common.cuh"
+
+namespace {
+
+constexpr int WARPS = 4;
+constexpr float FMAX = 3.402823466e38f;
+
+// ---- cum_pose_changes: P[n,t,b] = P[n,t-1,b] . C[n,t,b], P[n,-1,b] = I --------------------------
+// thread = (clip, bone); for a fixed frame the 26 bones of a clip are 936 contiguous bytes, so a warp's loads of one
+// frame touch one or two contiguous runs and every sector fetched is fully used.
+__global__ void __launch_bounds__(128) cum_changes_fwd_kernel(const float* __restrict__ c, float* __restrict__ out,
+                                                              long units, int L, int B) {
+    const long u = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (u >= units) return;
+    const long n = u / B;
+    const int b = (int)(u - n * B);
+    M3 p = m3_identity();
+    for (int t = 0; t < L; ++t) {
+        const long e = ((n * L + t) * B + b) * 9;
+        p = m3_mul(p, m3_from(c + e));
+        m3_to(out + e, p);
+    }
+}
+
+// G[t] = g_out[t] + G[t+1] . C[t+1]^T ;  g_C[t] = P[t-1]^T . G[t]
+__global__ void __launch_bounds__(128) cum_changes_bwd_kernel(const float* __restrict__ c,
+                                                              const float* __restrict__ cum,
+                                                              const float* __restrict__ g_out,
+                                                              float* __restrict__ g_c, long units, int L, int B) {
+    const long u = (long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (u >= units) return;
+    const long n = u / B;
+    const int b = (int)(u - n * B);
+    M3 g = m3_zero();
+    for (int t = L - 1; t >= 0; --t) {
+        const long e = ((n * L + t) * B + b) * 9;
+        m3_acc(g, m3_from(g_out + e));
+        const M3 prev = (t > 0) ? m3_from(cum + e - (long)B * 9) : m3_identity();
+        m3_to(g_c + e, m3_mul_at(prev, g));
+        g = m3_mul_bt(g, m3_from(c + e));
+    }
+}
+
+// ---- Normalizer (optional) followed by DeNormalizer.from_reference (optional) ------------------
+// one warp per pose, lanes stride over joints.  DIM = channels that are shifted and scaled (2: projections, 3:
+// absolute locations); C = channels per joint (DIM, or 3 with DIM 2: channel 2 is carried through).
+struct Renorm {
+    long M;
+    int J, C, L, hips, neck, autonormalize;
+    float near_zero;
+    const float* ref_shift;   // (rows, DIM) or NULL
+    const float* ref_scale;   // (rows) or NULL
+    const int* ref_index;     // (clips) or NULL: row = clip
+};
+
+template <int DIM>
+__global__ void __launch_bounds__(WARPS * 32) renorm_fwd_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                               Renorm a) {
+    const int lane = threadIdx.x & 31;
+    const int C = a.C;
+    const long wstride = (long)gridDim.x * WARPS;
+    for (long m = (long)blockIdx.x * WARPS + (threadIdx.x >> 5); m < a.M; m += wstride) {
+        const float* p = in + m * a.J * C;
+        float* o = out + m * a.J * C;
+        float s[DIM], scale = 1.f, rs = 1.f, rh[DIM];
+#pragma unroll
+        for (int k = 0; k < DIM; ++k) { s[k] = 0.f; rh[k] = 0.f; }
+        if (a.autonormalize) {
+            float q = 0.f;
+#pragma unroll
+            for (int k = 0; k < DIM; ++k) {
+                s[k] = __ldg(p + a.hips * C + k);
+                const float d = __ldg(p + a.neck * C + k) - s[k];
+                q = fmaf(d, d, q);
+            }
+            scale = sqrtf(q);
+        }
+        if (a.ref_scale) {
+            const long clip = m / a.L;
+            const long row = a.ref_index ? (long)__ldg(a.ref_index + clip) : clip;
+            rs = __ldg(a.ref_scale + row);
+#pragma unroll
+            for (int k = 0; k < DIM; ++k) rh[k] = __ldg(a.ref_shift + row * DIM + k);
+        }
+        for (int j = lane; j < a.J; j += 32) {
+            float y[DIM];
+#pragma unroll
+            for (int k = 0; k < DIM; ++k)
+                y[k] = a.autonormalize ? nan_to_zero((p[j * C + k] - s[k]) / scale) : p[j * C + k];
+            if (DIM == 2 && C > 2) {
+                float q = p[j * C + 2];
+                if (a.autonormalize) {
+                    q = nan_to_zero(q);
+                    if (!(q >= a.near_zero)) {
+#pragma unroll
+                        for (int k = 0; k < DIM; ++k) y[k] = 0.f;
+                    }
+                }
+                o[j * C + 2] = q;
+            }
+#pragma unroll
+            for (int k = 0; k < DIM; ++k) o[j * C + k] = a.ref_scale ? fmaf(y[k], rs, rh[k]) : y[k];
+        }
+    }
+}
+
+template <int DIM>
+__global__ void __launch_bounds__(WARPS * 32) renorm_bwd_kernel(const float* __restrict__ in,
+                                                               const float* __restrict__ g_out,
+                                                               float* __restrict__ g_in, Renorm a) {
+    const int lane = threadIdx.x & 31;
+    const int C = a.C;
+    const long wstride = (long)gridDim.x * WARPS;
+    for (long m = (long)blockIdx.x * WARPS + (threadIdx.x >> 5); m < a.M; m += wstride) {
+        const float* p = in + m * a.J * C;
+        const float* g = g_out + m * a.J * C;
+        float* o = g_in + m * a.J * C;
+        float rs = 1.f;
+        if (a.ref_scale) {
+            const long clip = m / a.L;
+            rs = __ldg(a.ref_scale + (a.ref_index ? (long)__ldg(a.ref_index + clip) : clip));
+        }
+        if (!a.autonormalize) {
+            for (int j = lane; j < a.J; j += 32) {
+#pragma unroll
+                for (int k = 0; k < DIM; ++k) o[j * C + k] = g[j * C + k] * rs;
+                if (DIM == 2 && C > 2) o[j * C + 2] = g[j * C + 2];
+            }
+            continue;
+        }
+        float s[DIM], d[DIM], q2 = 0.f;
+#pragma unroll
+        for (int k = 0; k < DIM; ++k) {
+            s[k] = __ldg(p + a.hips * C + k);
+            d[k] = __ldg(p + a.neck * C + k) - s[k];
+            q2 = fmaf(d[k], d[k], q2);
+        }
+        const float scale = sqrtf(q2);
+        const bool ok = scale > 0.f && scale <= FMAX;
+        float sg[DIM], sgn = 0.f;
+#pragma unroll
+        for (int k = 0; k < DIM; ++k) sg[k] = 0.f;
+        for (int j = lane; j < a.J; j += 32) {
+            float gy[DIM], r[DIM];
+            bool zeroed = false;
+            if (DIM == 2 && C > 2) {
+                const float qraw = p[j * C + 2];
+                const bool fin = fabsf(qraw) <= FMAX;
+                zeroed = !((fin ? qraw : 0.f) >= a.near_zero);
+                o[j * C + 2] = fin ? g[j * C + 2] : 0.f;
+            }
+#pragma unroll
+            for (int k = 0; k < DIM; ++k) {
+                r[k] = (p[j * C + k] - s[k]) / scale;
+                gy[k] = g[j * C + k] * rs;
+                // nan_to_num passes no gradient to non-finite entries
+                if (!(fabsf(r[k]) <= FMAX) || zeroed || !ok) gy[k] = 0.f;
+                o[j * C + k] = ok ? gy[k] / scale : 0.f;
+                sg[k] += gy[k];
+                sgn = fmaf(gy[k], nan_to_zero(r[k]), sgn);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < DIM; ++k) sg[k] = warp_sum(sg[k]);
+        sgn = warp_sum(sgn);
+        __syncwarp();
+        if (lane == 0 && ok) {
+            const float gscale = -sgn / scale;  // d / d scale
+#pragma unroll
+            for (int k = 0; k < DIM; ++k) {
+                const float un = gscale * d[k] / scale;  // through scale = |neck - hips|
+                if (a.hips == a.neck) {
+                    o[a.hips * C + k] += -sg[k] / scale;
+                } else {
+                    o[a.hips * C + k] += -sg[k] / scale - un;
+                    o[a.neck * C + k] += un;
+                }
+            }
+        }
+    }
+}
+
+int warp_grid(long units) {
+    long blocks = (units + WARPS - 1) / WARPS;
+    if (blocks > 148L * 64) blocks = 148L * 64;
+    if (blocks < 1) blocks = 1;
+    return (int)blocks;
+}
+
+int renorm_args(Renorm& a, int64_t m, int32_t j, int32_t c, int32_t dim, int32_t hips, int32_t neck,
+                int32_t autonormalize, float near_zero, const float* ref_shift, const float* ref_scale,
+                const int32_t* ref_index, int32_t clip_len) {
+    if (m < 0 || j < 1 || (dim != 2 && dim != 3) || !(c == dim || (dim == 2 && c == 3))) return P2C_E_BADARG;
+    if (hips < 0 || hips >= j || neck < 0 || neck >= j) return P2C_E_BADARG;
+    if ((ref_shift == nullptr) != (ref_scale == nullptr)) return P2C_E_NULL;
+    if (ref_scale && clip_len < 1) return P2C_E_BADARG;
+    a.M = (long)m; a.J = j; a.C = c; a.L = clip_len > 0 ? clip_len : 1; a.hips = hips; a.neck = neck;
+    a.autonormalize = autonormalize ? 1 : 0; a.near_zero = near_zero;
+    a.ref_shift = ref_shift; a.ref_scale = ref_scale; a.ref_index = ref_index;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int p2c_cum_changes_fwd(const float* changes, float* cumulative, int32_t n_clips, int32_t clip_len,
+                                   int32_t n_bones, void* stream) {
+    if (!changes || !cumulative) return P2C_E_NULL;
+    if (n_clips < 0 || clip_len < 1 || n_bones < 1) return P2C_E_BADARG;
+    const long units = (long)n_clips * n_bones;
+    if (units == 0) return 0;
+    cum_changes_fwd_kernel<<<(unsigned)((units + 127) / 128), 128, 0, (cudaStream_t)stream>>>(changes, cumulative,
+                                                                                             units, clip_len, n_bones);
+    P2C_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int p2c_cum_changes_bwd(const float* changes, const float* cumulative, const float* g_cumulative,
+                                   float* g_changes, int32_t n_clips, int32_t clip_len, int32_t n_bones,
+                                   void* stream) {
+    if (!changes || !cumulative || !g_cumulative || !g_changes) return P2C_E_NULL;
+    if (n_clips < 0 || clip_len < 1 || n_bones < 1) return P2C_E_BADARG;
+    const long units = (long)n_clips * n_bones;
+    if (units == 0) return 0;
+    cum_changes_bwd_kernel<<<(unsigned)((units + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
+        changes, cumulative, g_cumulative, g_changes, units, clip_len, n_bones);
+    P2C_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int p2c_renormalize_fwd(const float* sample, float* out, int64_t m, int32_t j, int32_t c, int32_t dim,
+                                   int32_t hips, int32_t neck, int32_t autonormalize, float near_zero,
+                                   const float* ref_shift, const float* ref_scale, const int32_t* ref_index,
+                                   int32_t clip_len, void* stream) {
+    if (!sample || !out) return P2C_E_NULL;
+    Renorm a;
+    const int rc = renorm_args(a, m, j, c, dim, hips, neck, autonormalize, near_zero, ref_shift, ref_scale, ref_index,
+                               clip_len);
+    if (rc) return rc;
+    if (m == 0) return 0;
+    if (dim == 2)
+        renorm_fwd_kernel<2><<<warp_grid(m), WARPS * 32, 0, (cudaStream_t)stream>>>(sample, out, a);
+    else
+        renorm_fwd_kernel<3><<<warp_grid(m), WARPS * 32, 0, (cudaStream_t)stream>>>(sample, out, a);
+    P2C_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int p2c_renormalize_bwd(const float* sample, const float* g_out, float* g_sample, int64_t m, int32_t j,
+                                   int32_t c, int32_t dim, int32_t hips, int32_t neck, int32_t autonormalize,
+                                   float near_zero, const float* ref_scale, const int32_t* ref_index,
+                                   int32_t clip_len, void* stream) {
+    if (!sample || !g_out || !g_sample) return P2C_E_NULL;
+    Renorm a;
+    // the reference shift does not enter the gradient; pass the scale pointer for both so the pair check holds
+    const int rc = renorm_args(a, m, j, c, dim, hips, neck, autonormalize, near_zero, ref_scale, ref_scale, ref_index,
+                               clip_len);
+    if (rc) return rc;
+    if (m == 0) return 0;
+    if (dim == 2)
+        renorm_bwd_kernel<2><<<warp_grid(m), WARPS * 32, 0, (cudaStream_t)stream>>>(sample, g_out, g_sample, a);
+    else
+        renorm_bwd_kernel<3><<<warp_grid(m), WARPS * 32, 0, (cudaStream_t)stream>>>(sample, g_out, g_sample, a);
+    P2C_LAUNCH_CHECK();
+    return 0;
+}

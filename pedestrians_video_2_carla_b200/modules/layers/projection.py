@@ -13,6 +13,7 @@ from .. import flow_output_types as T
 from ... import _lib, ops
 from ...data.carla import reference as R
 from ...data.carla.skeleton import get_neck_point, get_root_point
+from ...transforms.pose.normalization.reference_skeletons_denormalizer import ReferenceSkeletonsDeNormalizer
 from ...utils.world import calculate_world_from_changes
 from ...walker_control.p3d_pose import P3dPose
 from ...walker_control.p3d_pose_projection import P3dPoseProjection
@@ -24,10 +25,10 @@ class ProjectionModule(nn.Module):
         super().__init__()
         self.movements_output_type = movements_output_type
         self.trajectory_output_type = trajectory_output_type
-        if movements_output_type in (T.MovementsModelOutputType.absolute_loc,
-                                     T.MovementsModelOutputType.absolute_loc_rot):
-            raise NotImplementedError('absolute_loc(_rot) inputs go through ReferenceSkeletonsDeNormalizer, which is '
-                                      'outside the accelerated path (SURVEY 8f, DESIGN.md section 7)')
+        self._absolute = movements_output_type in (T.MovementsModelOutputType.absolute_loc,
+                                                   T.MovementsModelOutputType.absolute_loc_rot)
+        if self._absolute:   # projection.py:30-35: self-normalise, then rescale to the clip's reference skeleton
+            self._denormalize = ReferenceSkeletonsDeNormalizer()
         self._mode = (_lib.MODE_POSE_CHANGES if movements_output_type == T.MovementsModelOutputType.pose_changes
                       else _lib.MODE_RELATIVE_ROT)
         self._pose = None
@@ -79,7 +80,38 @@ class ProjectionModule(nn.Module):
             rot_in = torch.eye(3, device=device).reshape(1, 1, 3, 3).repeat(n, l, 1, 1)
         return loc_in, rot_in
 
+    def _forward_absolute(self, pose_inputs_batch, world_loc_change_batch, world_rot_change_batch):
+        """absolute_loc / absolute_loc_rot movements output (projection.py:125-142): the model emits absolute joint
+        locations in its own scale; one kernel self-normalises them (hips -> 0, |neck - hips| -> 1) and rescales to
+        the clip's reference skeleton, one kernel projects.  No FK: relative tensors are None as in the reference."""
+        abs_rot = None
+        if self.movements_output_type == T.MovementsModelOutputType.absolute_loc_rot:
+            if not isinstance(pose_inputs_batch, tuple):
+                raise RuntimeError('Absolute location with rotation should be a Tuple of tensors.')
+            pose_inputs_batch, abs_rot = pose_inputs_batch
+        if pose_inputs_batch.ndim < 4:
+            raise RuntimeError('Absolute location should have shape of (N - batch_size, L - clip_length, B - bones, '
+                               '3 - absolute location coordinates)')
+        n, l, b = pose_inputs_batch.shape[:3]
+        device = pose_inputs_batch.device
+        if self._ref_index is None:
+            raise RuntimeError('absolute_loc movements need (age, gender) reference skeletons, not custom poses')
+        abs_loc = self._denormalize.from_abs(pose_inputs_batch, None, autonormalize=True, rows=self._ref_index)
+        world_loc, world_rot = self._world((n, l), device, world_loc_change_batch, world_rot_change_batch)
+        proj = ops.project(abs_loc.reshape(n * l, b, 3), world_loc.reshape(n * l, 3), world_rot.reshape(n * l, 3, 3),
+                           self._projection.camera.struct).reshape(n, l, b, 3)
+        return proj, {
+            'relative_pose_loc': None,
+            'relative_pose_rot': None,
+            'absolute_pose_loc': abs_loc,
+            'absolute_pose_rot': abs_rot,
+            'world_loc': world_loc,
+            'world_rot': world_rot,
+        }
+
     def forward(self, pose_inputs_batch, world_loc_change_batch=None, world_rot_change_batch=None):
+        if self._absolute:
+            return self._forward_absolute(pose_inputs_batch, world_loc_change_batch, world_rot_change_batch)
         if pose_inputs_batch.ndim < 5:
             raise RuntimeError('Pose changes should have shape of (N - batch_size, L - clip_length, B - bones, 3, 3 '
                                '- rotations as rotation matrices)')

@@ -282,6 +282,87 @@ def masked_mse(pred, gt, c_used, mask_hips=-1):
     return _MaskedMSE.apply(pred, gt, c_used, mask_hips)
 
 
+class _CumChanges(torch.autograd.Function):
+    """Per-bone cumulative product of pose changes over frames (loss/cum_pose_changes.py:26-48)."""
+
+    @staticmethod
+    def forward(ctx, changes):
+        c = _f32c(changes, 'pose_changes')
+        if c.dim() != 5 or c.shape[-2:] != (3, 3):
+            raise RuntimeError('cumulative_changes expects (N, L, B, 3, 3), got %s' % (tuple(c.shape),))
+        out = torch.empty_like(c)
+        n, l, b = c.shape[:3]
+        check(_lib.load().p2c_cum_changes_fwd(ptr(c), ptr(out), n, l, b, stream()), 'cum_changes_fwd')
+        ctx.save_for_backward(c, out)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        c, out = ctx.saved_tensors
+        g = _f32c(g, 'grad')
+        gc = torch.empty_like(c)
+        n, l, b = c.shape[:3]
+        check(_lib.load().p2c_cum_changes_bwd(ptr(c), ptr(out), ptr(g), ptr(gc), n, l, b, stream()),
+              'cum_changes_bwd')
+        return gc
+
+
+def cumulative_changes(changes):
+    return _CumChanges.apply(changes)
+
+
+class _Renormalize(torch.autograd.Function):
+    """Normalizer(dim) and/or DeNormalizer.from_reference per clip (normalizer.py:20-41, denormalizer.py:13-37,
+    reference_skeletons_denormalizer.py:41-91) in one pass."""
+
+    @staticmethod
+    def forward(ctx, sample, dim, hips, neck, autonormalize, near_zero, ref_shift, ref_scale, ref_index):
+        s = _f32c(sample, 'sample')
+        if s.dim() < 3:
+            raise RuntimeError('renormalize expects (..., L, J, C), got %s' % (tuple(s.shape),))
+        out = torch.empty_like(s)
+        l, j, c = s.shape[-3:]
+        m = s.numel() // (j * c)
+        ref_shift, ref_scale = _f32c(ref_shift, 'ref_shift'), _f32c(ref_scale, 'ref_scale')
+        if ref_scale is not None:
+            rows = ref_scale.numel()
+            if ref_shift.numel() != rows * dim:
+                raise RuntimeError('ref_shift %s does not match ref_scale %s for dim %d'
+                                   % (tuple(ref_shift.shape), tuple(ref_scale.shape), dim))
+            if ref_index is None and rows != m // l:
+                raise RuntimeError('per-clip reference rows (%d) do not match the clips (%d)' % (rows, m // l))
+            if ref_index is not None and ref_index.numel() != m // l:
+                raise RuntimeError('ref_index has %d entries for %d clips' % (ref_index.numel(), m // l))
+        check(_lib.load().p2c_renormalize_fwd(ptr(s), ptr(out), m, j, c, dim, hips, neck, 1 if autonormalize else 0,
+                                              near_zero, ptr(ref_shift), ptr(ref_scale), ptr(ref_index), l, stream()),
+              'renormalize_fwd')
+        ctx.save_for_backward(s, ref_scale, ref_index)
+        ctx.cfg = (dim, hips, neck, autonormalize, near_zero)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        s, ref_scale, ref_index = ctx.saved_tensors
+        dim, hips, neck, autonormalize, near_zero = ctx.cfg
+        g = _f32c(g, 'grad')
+        gs = torch.empty_like(s)
+        l, j, c = s.shape[-3:]
+        check(_lib.load().p2c_renormalize_bwd(ptr(s), ptr(g), ptr(gs), s.numel() // (j * c), j, c, dim, hips, neck,
+                                              1 if autonormalize else 0, near_zero, ptr(ref_scale), ptr(ref_index), l,
+                                              stream()), 'renormalize_bwd')
+        return gs, None, None, None, None, None, None, None, None
+
+
+def renormalize(sample, dim, hips, neck, autonormalize=True, near_zero=1e-5, ref_shift=None, ref_scale=None,
+                ref_index=None):
+    """sample (N, L, J, C).  autonormalize: hips -> 0, |neck - hips| -> 1 over the first `dim` channels; ref_shift
+    (rows, dim) / ref_scale (rows): then `y * scale + shift` with the row of each clip (ref_index (N,) int32, or one
+    row per clip).  The reference tables carry no gradient (they are constants of the reference skeletons)."""
+    return _Renormalize.apply(sample, dim, hips, neck, autonormalize, near_zero,
+                              None if ref_shift is None else ref_shift.detach(),
+                              None if ref_scale is None else ref_scale.detach(), ref_index)
+
+
 _WS = {}
 
 

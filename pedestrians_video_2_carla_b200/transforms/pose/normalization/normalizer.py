@@ -13,6 +13,8 @@ class Normalizer(object):
         return '%s(extractor=%s)' % (self.__class__.__name__, self.extractor.__class__.__name__)
 
     def __call__(self, sample, dim=2, *args, **kwargs):
-        if dim != 2:
-            raise NotImplementedError('only the 2-D normalisation of the projection is on the accelerated path')
-        return ops.hips_neck_normalize(sample, self.extractor.hips, self.extractor.neck, self._near_zero)
+        if dim == 2 and sample.shape[-1] in (2, 3):
+            return ops.hips_neck_normalize(sample, self.extractor.hips, self.extractor.neck, self._near_zero)
+        if dim == 3 and sample.shape[-1] == 3 and sample.dim() >= 3:   # absolute locations (denormaliser entry)
+            return ops.renormalize(sample, 3, self.extractor.hips, self.extractor.neck, True, self._near_zero)
+        raise NotImplementedError('Normalizer takes (..., J, 2|3) with dim=2 or (..., L, J, 3) with dim=3')

@@ -1,0 +1,233 @@
+"""SURVEY 8f rows 1-2 on the GPU: the remaining LossModes of the pose_lifting flow, Normalizer(dim=3),
+ReferenceSkeletonsDeNormalizer and the absolute_loc(_rot) movements output of ProjectionModule, through the drop-in
+classes (-> ctypes -> C ABI -> kernels), against (a) the golden vectors produced by the reference's own code
+(tests/golden/reference_widen.npz) and (b) the float64 oracle on larger seeded cases.  Tolerance 1e-4 scale-relative."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import oracle as O
+from _util import assert_close, assert_close_fp32_aware
+
+pytestmark = pytest.mark.gpu
+DEV = torch.device('cuda', 0)
+HERE = os.path.dirname(os.path.abspath(__file__))
+TYPES = (('adult', 'female'), ('adult', 'male'), ('child', 'female'), ('child', 'male'))
+
+
+@pytest.fixture(scope='module')
+def gold():
+    z = np.load(os.path.join(HERE, 'golden', 'reference_widen.npz'))
+    return {k: torch.from_numpy(z[k]) for k in z.files}
+
+
+@pytest.fixture(scope='module')
+def api():
+    from pedestrians_video_2_carla_b200 import ops
+    from pedestrians_video_2_carla_b200.loss import LossModes
+    from pedestrians_video_2_carla_b200.modules.flow_output_types import MovementsModelOutputType
+    from pedestrians_video_2_carla_b200.modules.layers.projection import ProjectionModule
+    from pedestrians_video_2_carla_b200.transforms.pose.normalization.denormalizer import DeNormalizer
+    from pedestrians_video_2_carla_b200.transforms.pose.normalization.normalizer import Normalizer
+    from pedestrians_video_2_carla_b200.transforms.pose.normalization.reference_skeletons_denormalizer import \
+        ReferenceSkeletonsDeNormalizer
+    return dict(locals())
+
+
+def _meta(sid):
+    return {'age': [TYPES[int(i)][0] for i in sid], 'gender': [TYPES[int(i)][1] for i in sid]}
+
+
+def _losses(api, mats, proj_t, d, targets, weights=None):
+    """modules/flow/base.py:440-469: requirements first, then the dependent modes."""
+    L = api['LossModes']
+    kw = dict(input_nodes=None, output_nodes=None, mask_missing_joints=True)
+    sliced = dict(pose_inputs=mats, targets=targets, projection_2d_transformed=proj_t, **d)
+    res = {}
+    for mode in (L.loc_2d, L.loc_3d, L.rot_3d, L.cum_pose_changes, L.pose_changes):
+        fn, crit = mode.value[0], mode.value[1]
+        if isinstance(fn, type):
+            from pedestrians_video_2_carla_b200.data.carla.skeleton import CARLA_SKELETON
+            res[mode.name] = fn(criterion=crit, input_nodes=CARLA_SKELETON, output_nodes=CARLA_SKELETON,
+                                mask_missing_joints=True)(**sliced)
+        else:
+            res[mode.name] = fn(criterion=crit, **kw, **sliced)
+    for mode in (L.loc_2d_3d, L.loc_rot_3d, L.loc_2d_loc_rot_3d, L.weighted_loc_2d_loc_rot_3d):
+        res[mode.name] = mode.value[0](requirements=res, loss_weights=weights, **kw)
+    return res
+
+
+def test_extra_losses_against_reference_golden(api, gold):
+    sid = gold['skeleton_id']
+    n, l = gold['loss/d6'].shape[:2]
+    pm = api['ProjectionModule'](api['MovementsModelOutputType'].pose_changes)
+    pm.on_batch_start((torch.zeros((n, l, 26, 2), device=DEV), None, _meta(sid)), 0)
+    d6 = gold['loss/d6'].to(DEV).requires_grad_(True)
+    mats = api['ops'].rotation_6d_to_matrix(d6)
+    mats.retain_grad()
+    proj, d = pm(mats, None, None)
+    proj_t = api['Normalizer']()(proj)
+    targets = {'projection_2d_transformed': gold['loss/gt_projection_2d_transformed'].to(DEV),
+               'absolute_pose_loc': gold['loss/gt_absolute_pose_loc'].to(DEV),
+               'absolute_pose_rot': gold['loss/gt_absolute_pose_rot'].to(DEV),
+               'pose_changes': gold['loss/gt_pose_changes'].to(DEV)}
+    w = dict(zip(('loc_2d', 'loc_3d', 'rot_3d'), gold['loss/weights'].tolist()))
+    res = _losses(api, mats, proj_t, d, targets, w)
+    for ours, theirs in (('loc_2d', 'loc_2d'), ('loc_3d', 'loc_3d'), ('rot_3d', 'rot_3d'), ('loc_rot_3d', 'loc_rot_3d'),
+                         ('loc_2d_loc_rot_3d', 'loc_2d_loc_rot_3d'), ('weighted_loc_2d_loc_rot_3d', 'weighted'),
+                         ('cum_pose_changes', 'cum_pose_changes'), ('pose_changes', 'pose_changes')):
+        assert_close(ours, res[ours], gold['loss/' + theirs])
+    for ours, theirs in (('weighted_loc_2d_loc_rot_3d', 'weighted'), ('cum_pose_changes', 'cum_pose_changes'),
+                         ('pose_changes', 'pose_changes'), ('rot_3d', 'rot_3d')):
+        d6.grad = None
+        mats.grad = None
+        res[ours].backward(retain_graph=True)
+        assert_close('grad_mats_' + ours, mats.grad, gold['loss/grad_mats_' + theirs], 2e-4)
+        assert_close('grad_d6_' + ours, d6.grad, gold['loss/grad_d6_' + theirs], 2e-4)
+
+
+def test_missing_targets_give_none(api):
+    L = api['LossModes']
+    x = torch.zeros((1, 2, 26, 3, 3), device=DEV)
+    assert L.rot_3d.value[0](criterion=None, input_nodes=None, output_nodes=None, absolute_pose_rot=x,
+                             targets={}) is None
+    assert L.rot_3d.value[0](criterion=None, input_nodes=None, output_nodes=None, absolute_pose_rot=None,
+                             targets={'absolute_pose_rot': x}) is None
+    assert L.loc_rot_3d.value[0](requirements={'loc_3d': x.sum()}) is None
+    assert L.loc_2d_loc_rot_3d.value[0](requirements={'loc_3d': x.sum(), 'rot_3d': x.sum()}) is None
+    assert L.weighted_loc_2d_loc_rot_3d.value[0](requirements={'loc_2d': x.sum()}, loss_weights={}) is None
+
+
+@pytest.mark.parametrize('n,l,b', [(64, 16, 26), (3, 1, 26), (5, 37, 24), (1, 64, 1)])
+def test_cumulative_changes_against_oracle(api, n, l, b):
+    g = torch.Generator().manual_seed(22742 + n + l)
+    # non-orthonormal changes are accepted, as everywhere on the path (tests/walker_control/test_p3d_pose.py:93-95)
+    c = torch.eye(3, dtype=torch.float64) + torch.randn((n, l, b, 3, 3), generator=g, dtype=torch.float64) * 0.08
+    t = torch.eye(3, dtype=torch.float64) + torch.randn((n, l, b, 3, 3), generator=g, dtype=torch.float64) * 0.08
+    c64 = c.clone().requires_grad_(True)
+    want = O.loss_cum_pose_changes(c64, t)
+    want.backward()
+    c32 = c.float().requires_grad_(True)
+    want32 = O.loss_cum_pose_changes(c32, t.float())
+    want32.backward()
+    cg = c.float().to(DEV).requires_grad_(True)
+    cum = api['ops'].cumulative_changes(cg)
+    assert_close('cumulative', cum, O.cumulative_changes(c))
+    got = api['LossModes'].cum_pose_changes.value[0](criterion=None, pose_inputs=cg,
+                                                     targets={'pose_changes': t.float().to(DEV)})
+    assert_close('cum_pose_changes', got, want)
+    got.backward()
+    assert_close_fp32_aware('grad', cg.grad, c64.grad, c32.grad)
+
+
+def test_cumulative_changes_empty_and_bad_shapes(api):
+    out = api['ops'].cumulative_changes(torch.zeros((0, 4, 26, 3, 3), device=DEV))
+    assert out.shape == (0, 4, 26, 3, 3)
+    with pytest.raises(RuntimeError):
+        api['ops'].cumulative_changes(torch.zeros((2, 4, 26, 9), device=DEV))
+    with pytest.raises(RuntimeError):
+        api['ops'].cumulative_changes(torch.zeros((2, 4, 26, 3, 3)))      # CPU tensor: no fallback
+
+
+def test_denormalizer_against_reference_golden(api, gold):
+    sid = gold['skeleton_id']
+    meta = _meta(sid)
+    den = api['ReferenceSkeletonsDeNormalizer']()
+    x3 = gold['den/x3'].to(DEV).requires_grad_(True)
+    assert_close('norm3', api['Normalizer']()(x3, dim=3), gold['den/norm3'])
+    a3 = den.from_abs(x3, meta, autonormalize=True)
+    assert_close('from_abs', a3, gold['den/from_abs'])
+    (a3 * gold['den/w3'].to(DEV)).sum().backward()
+    assert_close('grad_x3', x3.grad, gold['den/grad_x3'], 2e-4)
+    x3b = gold['den/x3'].to(DEV).requires_grad_(True)
+    (api['Normalizer']()(x3b, dim=3) * gold['den/w3'].to(DEV)).sum().backward()
+    assert_close('grad_x3_norm3', x3b.grad, gold['den/grad_x3_norm3'], 2e-4)
+    assert_close('from_abs_plain', den.from_abs(gold['den/norm3'].to(DEV), meta), gold['den/from_abs_plain'])
+    x2 = gold['den/x2'].to(DEV).requires_grad_(True)
+    p2 = den.from_projection(x2, meta, autonormalize=True)
+    assert_close('from_projection', p2, gold['den/from_projection'])
+    (p2 * gold['den/w2'].to(DEV)).sum().backward()
+    assert_close('grad_x2', x2.grad, gold['den/grad_x2'], 2e-4)
+    p2c = den.from_projection(gold['den/x2'][..., :2].contiguous().to(DEV), meta, autonormalize=True)
+    assert_close('from_projection_2ch', p2c, gold['den/from_projection_2ch'])
+    # age / gender substitutions (reference_skeletons_denormalizer.py:11-32)
+    sub = den.from_abs(gold['den/x3'][:2].to(DEV), {'age': ['senior', float('nan')], 'gender': ['neutral', 'male']},
+                       autonormalize=True)
+    plain = den.from_abs(gold['den/x3'][:2].to(DEV), {'age': ['adult', 'adult'], 'gender': ['female', 'male']},
+                         autonormalize=True)
+    assert torch.equal(sub, plain)
+
+
+def test_denormalizer_from_reference_matches_oracle(api):
+    g = torch.Generator().manual_seed(5)
+    ref = torch.randn((3, 26, 3), generator=g, dtype=torch.float64)
+    x = torch.randn((3, 4, 26, 3), generator=g, dtype=torch.float64)
+    shift, scale = O.get_shift_scale(ref)
+    want = O.denormalize(x, scale, shift, 3)
+    from pedestrians_video_2_carla_b200.transforms.pose.normalization.hips_neck_extractor import HipsNeckExtractor
+    got = api['DeNormalizer'].from_reference(HipsNeckExtractor(), ref.float().to(DEV))(x.float().to(DEV), dim=3)
+    assert_close('denormalize', got, want)
+
+
+def test_degenerate_scale_is_zeroed_like_the_reference(api):
+    """hips == neck position: the reference divides by 0 and nan_to_zero()s the result (normalizer.py:27-29)."""
+    x = torch.randn((2, 3, 26, 3), generator=torch.Generator().manual_seed(1))
+    x[0, 1, O.NECK] = x[0, 1, O.HIPS]
+    want = O.normalize(x.double(), 3)
+    xg = x.to(DEV).requires_grad_(True)
+    got = api['Normalizer']()(xg, dim=3)
+    assert_close('normalize dim 3', got, want)
+    assert float(got[0, 1].abs().max()) == 0.0
+    got.sum().backward()
+    assert torch.isfinite(xg.grad).all() and float(xg.grad[0, 1].abs().max()) == 0.0
+
+
+def test_absolute_loc_movements_against_reference_golden(api, gold):
+    sid = gold['skeleton_id']
+    n, l = gold['absloc/x'].shape[:2]
+    T = api['MovementsModelOutputType']
+    pm = api['ProjectionModule'](T.absolute_loc)
+    pm.on_batch_start((torch.zeros((n, l, 26, 2), device=DEV), None, _meta(sid)), 0)
+    x = gold['absloc/x'].to(DEV).requires_grad_(True)
+    proj, d = pm(x, None, None)
+    assert d['relative_pose_loc'] is None and d['relative_pose_rot'] is None and d['absolute_pose_rot'] is None
+    assert_close('absolute_pose_loc', d['absolute_pose_loc'], gold['absloc/absolute_pose_loc'])
+    assert_close('projection_2d', proj, gold['absloc/projection_2d'])
+    (proj * gold['absloc/w'].to(DEV)).sum().backward()
+    assert_close('grad_x', x.grad, gold['absloc/grad_x'], 2e-4)
+    # absolute_loc_rot: same locations, the rotations are handed through (projection.py:138-142)
+    pr = api['ProjectionModule'](T.absolute_loc_rot)
+    pr.on_batch_start((torch.zeros((n, l, 26, 2), device=DEV), None, _meta(sid)), 0)
+    rot = torch.eye(3, device=DEV).expand(n, l, 26, 3, 3).contiguous()
+    proj2, d2 = pr((gold['absloc/x'].to(DEV), rot), None, None)
+    assert torch.equal(proj2, proj.detach()) and d2['absolute_pose_rot'] is rot
+    with pytest.raises(RuntimeError):
+        pr(gold['absloc/x'].to(DEV), None, None)
+
+
+def test_absolute_loc_large_batch_against_oracle(api):
+    """BASELINE config 2 size (256 x 16) through the absolute_loc entry vs the float64 oracle."""
+    n, l = 256, 16
+    g = torch.Generator().manual_seed(22742 + 7)
+    loc, rot, _, par = O.reference_tensors(torch.float64)
+    ident = torch.eye(3, dtype=torch.float64).reshape(1, 1, 3, 3).repeat(4, 26, 1, 1)
+    ref_abs, _, _ = O.p3d_pose_forward(ident, loc, rot, par)
+    sid = torch.randint(0, 4, (n,), generator=g)
+    x = (ref_abs[sid].unsqueeze(1) * 0.6 + torch.randn((n, l, 26, 3), generator=g, dtype=torch.float64) * 0.05)
+    x64 = x.clone().requires_grad_(True)
+    abs_loc = O.abs_from_abs_loc(x64, ref_abs, sid)
+    cam = O.training_camera()
+    zl, zr = torch.zeros((n * l, 3), dtype=torch.float64), torch.eye(3, dtype=torch.float64).repeat(n * l, 1, 1)
+    proj = O.project(abs_loc.reshape(n * l, 26, 3), zl, zr, cam).reshape(n, l, 26, 3)
+    w = torch.randn((n, l, 26, 3), generator=g, dtype=torch.float64) * torch.tensor([1e-2, 1e-2, 1.0])
+    (proj * w).sum().backward()
+    pm = api['ProjectionModule'](api['MovementsModelOutputType'].absolute_loc)
+    pm.on_batch_start((torch.zeros((n, l, 26, 2), device=DEV), None, _meta(sid)), 0)
+    xg = x.float().to(DEV).requires_grad_(True)
+    got, d = pm(xg, None, None)
+    assert_close('absolute_pose_loc', d['absolute_pose_loc'], abs_loc)
+    assert_close('projection_2d', got, proj)
+    (got * w.float().to(DEV)).sum().backward()
+    assert_close('grad', xg.grad, x64.grad, 2e-4)

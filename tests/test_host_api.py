@@ -58,19 +58,31 @@ def test_camera_constants_match_oracle():
         P3dPoseProjection(device='cuda:0')
 
 
-def test_projection_module_rejects_out_of_scope_modes():
+def test_projection_module_rejects_bad_input_ranks():
     from pedestrians_video_2_carla_b200.modules.flow_output_types import MovementsModelOutputType
     from pedestrians_video_2_carla_b200.modules.layers.projection import ProjectionModule
-    with pytest.raises(NotImplementedError):
-        ProjectionModule(movements_output_type=MovementsModelOutputType.absolute_loc)
     m = ProjectionModule()
     with pytest.raises(RuntimeError):          # reference projection.py:90-92
         m.forward(torch.zeros(2, 3, 26, 6))
+    m = ProjectionModule(movements_output_type=MovementsModelOutputType.absolute_loc)
+    with pytest.raises(RuntimeError):          # reference projection.py:93-95
+        m.forward(torch.zeros(2, 26, 3))
+    m = ProjectionModule(movements_output_type=MovementsModelOutputType.absolute_loc_rot)
+    with pytest.raises(RuntimeError):          # reference projection.py:96-98
+        m.forward(torch.zeros(2, 3, 26, 3))
 
 
 def test_loss_modes_contract():
     from pedestrians_video_2_carla_b200.loss import LossModes
-    assert [m.name for m in LossModes] == ['loc_2d', 'loc_3d', 'loc_2d_3d']
+    assert [m.name for m in LossModes] == ['loc_2d', 'loc_3d', 'rot_3d', 'cum_pose_changes', 'pose_changes',
+                                           'loc_2d_3d', 'loc_2d_loc_rot_3d', 'weighted_loc_2d_loc_rot_3d',
+                                           'loc_rot_3d']
+    assert LossModes.loc_rot_3d.value[2] == ('loc_3d', 'rot_3d')
+    assert LossModes.weighted_loc_2d_loc_rot_3d.value[2] == ('loc_2d', 'loc_3d', 'rot_3d')
+    w = LossModes.weighted_loc_2d_loc_rot_3d.value[0]
+    req = {'loc_2d': torch.tensor(1.0), 'loc_3d': torch.tensor(2.0), 'rot_3d': torch.tensor(4.0)}
+    assert float(w(requirements=req, loss_weights={'loc_3d': 0.5})) == 6.0
+    assert w(requirements={'loc_2d': torch.tensor(1.0)}, loss_weights={}) is None
     assert LossModes.loc_2d_3d.value[2] == ('loc_2d', 'loc_3d')
     fn = LossModes.loc_2d_3d.value[0]
     assert float(fn(requirements={'loc_2d': torch.tensor(1.5), 'loc_3d': torch.tensor(2.0)})) == 3.5
