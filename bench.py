@@ -294,34 +294,72 @@ def e2e_region(shard, steps, warmup, world):
     step's d6 / targets / skeleton ids from pinned host memory, runs forward + backward, and reads the loss back."""
     import torch.distributed as dist
     ops, dev = shard.ops, shard.dev
+    # Host side of a static-shape training loop: every step's inputs (6-D output stand-in, 2-D / 3-D targets, skeleton
+    # ids) sit in ONE pinned staging image and cross PCIe as one copy into one of two device images; the copy of step
+    # i+1 runs on a copy stream while step i computes and its loss is read back (a prefetching loader).  Outputs are
+    # preallocated (ops.fused_step_buffers), so the call reuses its argument block.
+    keys = ('d6', 'gt2', 'gt3', 'sid')
+    ref = shard.sets[0]
+    offs, total = {}, 0
+    for k in keys:
+        offs[k] = total
+        total += (ref[k].numel() * ref[k].element_size() + 255) // 256 * 256
+
+    def views(buf):
+        return {k: buf[offs[k]:offs[k] + ref[k].numel() * ref[k].element_size()].view(ref[k].dtype).view(ref[k].shape)
+                for k in keys}
     host = []
     for s in shard.sets[:4]:
-        host.append({k: s[k].cpu().pin_memory() for k in ('d6', 'gt2', 'gt3', 'sid')})
-    dbuf = {k: torch.empty_like(shard.sets[0][k]) for k in ('d6', 'gt2', 'gt3', 'sid')}
-    h2d = sum(v.numel() * v.element_size() for v in host[0].values())
+        hb = torch.empty(total, dtype=torch.uint8).pin_memory()
+        hv = views(hb)
+        for k in keys:
+            hv[k].copy_(s[k])
+        host.append(hb)
+    dimg = [torch.empty(total, dtype=torch.uint8, device=dev) for _ in range(2)]
+    dbufs = [views(d) for d in dimg]
+    h2d = sum(ref[k].numel() * ref[k].element_size() for k in keys)
+    n, l, b = ref['d6'].shape[:3]
+    pre = ops.fused_step_buffers(n, l, b, dev)
     loss_host = torch.zeros(1).pin_memory()
+    copy_stream = torch.cuda.Stream(dev)
+    ready = [torch.cuda.Event() for _ in range(2)]
+    consumed = [torch.cuda.Event() for _ in range(2)]
+    for e in consumed:
+        e.record()
 
-    def one(i):
-        h = host[i % len(host)]
-        for k in dbuf:
-            dbuf[k].copy_(h[k], non_blocking=True)
+    def prefetch(i):
+        k = i % 2
+        copy_stream.wait_event(consumed[k])
+        with torch.cuda.stream(copy_stream):
+            dimg[k].copy_(host[i % len(host)], non_blocking=True)
+        ready[k].record(copy_stream)
+
+    def one(i, last):
+        k = i % 2
+        if not last:
+            prefetch(i + 1)
+        torch.cuda.current_stream().wait_event(ready[k])
+        dbuf = dbufs[k]
         x = dbuf['d6'].requires_grad_(True)
         r = ops.fused_step(x, shard.tree, shard.cam, shard.loc, shard.rot, dbuf['gt2'], dbuf['gt3'], ref_index=dbuf['sid'],
-                           want_transformed=False)
+                           want_transformed=False, out=pre)
         r.loc_2d_3d.backward()
+        consumed[k].record()
         if world > 1:
             dist.all_reduce(r.losses[3:7])
         loss_host.copy_(r.loc_2d_3d.detach().reshape(1), non_blocking=False)   # device -> host read of the result
         dbuf['d6'] = x.detach()
         return float(loss_host[0])
+    prefetch(0)
     for i in range(warmup):
-        one(i)
+        one(i, i == warmup - 1)
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     t0 = time.perf_counter()
+    prefetch(0)
     for i in range(steps):
-        one(i)
+        one(i, i == steps - 1)
     torch.cuda.synchronize()
     dt = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
     if world > 1:
@@ -475,7 +513,8 @@ def main():
             'clocks': sampler.summary(note),
             'e2e': {'value': round(e2e_value, 1), 'unit': 'poses/s', 'h2d_bytes_per_step': h2d,
                     'd2h_bytes_per_step': d2h, 'steps': e2e_steps,
-                    'api': 'ops.fused_step(...).loc_2d_3d.backward() with pinned-host inputs'},
+                    'api': 'ops.fused_step(..., out=fused_step_buffers).loc_2d_3d.backward(); inputs from one pinned staging image '
+                           'per step, copied on a prefetch stream'},
             'gpu_launches': shard.launches_per_step * args.steps}
     line['roofline'] = roofline_of(shard.poses, args.clip_len, ms_per_step,
                                    'p2c_fused_step (%d launch(es)/step; duration = whole step, CUDA events)'

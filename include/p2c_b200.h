@@ -185,6 +185,13 @@ int p2c_fused_step(const p2c_fused_step_t* p, void* stream);
 /* number of kernels p2c_fused_step(p) enqueues (for launch accounting; < 0 = bad argument) */
 int p2c_fused_step_launches(const p2c_fused_step_t* p);
 
+/* ---- pytorch3d 0.6.0 quaternion_to_matrix (real part first, not normalised first): the quaternion entry the
+ *      north star names next to euler_angles_to_matrix (walker_control/p3d_pose.py:54) and rotation_6d_to_matrix
+ *      (modules/movements/movements.py:113-116); the reference itself has no quaternion call site.
+ *      quat (n,4) -> out (n,3,3); both quaternion pointers must be 16-byte aligned.                             */
+int p2c_quaternion_to_matrix_fwd(const float* quat, float* out, int64_t n, void* stream);
+int p2c_quaternion_to_matrix_bwd(const float* quat, const float* g_out, float* g_quat, int64_t n, void* stream);
+
 /* ---- loss/cum_pose_changes.py:9-56: per-bone cumulative product of the pose changes over the frames of a clip,
  *      cumulative[n,t,b] = cumulative[n,t-1,b] . changes[n,t,b] (identity before frame 0); (N,L,B,3,3) both.
  *      The loss itself is p2c_masked_mse_fwd over 9 channels of the two scans (prediction and target).          */

@@ -24,7 +24,7 @@ __all__ = [
     'projection_module_forward', 'hips_neck_normalize', 'missing_joints_mask', 'loss_loc_2d',
     'loss_loc_3d', 'loss_loc_2d_3d', 'full_step', 'HIPS', 'NECK',
     'normalize', 'get_shift_scale', 'denormalize', 'reference_denormalize', 'cumulative_changes', 'loss_rot_3d',
-    'loss_cum_pose_changes', 'loss_pose_changes', 'loss_weighted_loc_2d_loc_rot_3d', 'abs_from_abs_loc',
+    'quaternion_to_matrix', 'loss_cum_pose_changes', 'loss_pose_changes', 'loss_weighted_loc_2d_loc_rot_3d', 'abs_from_abs_loc',
 ]
 
 FILES_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), '..',
@@ -462,3 +462,16 @@ def loss_weighted_loc_2d_loc_rot_3d(l2d, l3d, r3d, weights=None):
     """loss/weighted_loc_2d_loc_rot_3d.py:6-25 (unit weights: loc_2d_loc_rot_3d.py:6-21)."""
     w = weights or {}
     return w.get('loc_2d', 1.0) * l2d + w.get('loc_3d', 1.0) * l3d + w.get('rot_3d', 1.0) * r3d
+
+
+def quaternion_to_matrix(quaternions):
+    """pytorch3d 0.6.0 transforms/rotation_conversions.py quaternion_to_matrix (real part first; restated from the
+    published formula -- the reference has no quaternion call site, the north star names the entry).  Pinned in
+    tests/ against scipy.spatial.transform.Rotation for unit quaternions."""
+    r, i, j, k = torch.unbind(quaternions, -1)
+    two_s = 2.0 / (quaternions * quaternions).sum(-1)
+    o = torch.stack((
+        1 - two_s * (j * j + k * k), two_s * (i * j - k * r), two_s * (i * k + j * r),
+        two_s * (i * j + k * r), 1 - two_s * (i * i + k * k), two_s * (j * k - i * r),
+        two_s * (i * k - j * r), two_s * (j * k + i * r), 1 - two_s * (i * i + j * j)), -1)
+    return o.reshape(quaternions.shape[:-1] + (3, 3))

@@ -187,6 +187,72 @@ __global__ void __launch_bounds__(WARPS * 32) renorm_bwd_kernel(const float* __r
     }
 }
 
+
+// ---- quaternion_to_matrix (pytorch3d 0.6.0 rotation_conversions.quaternion_to_matrix, real part first) -------------
+// The north star's quaternion entry next to the Euler / 6-D ones.  M = I + (2 / |q|^2) A(q), A quadratic in q; not
+// normalised first (pytorch3d does not either), so the gradient has the -(2/|q|^2)^2 q <G, A> term of the scale.
+// 16 B in / 36 B out per record: quaternions are one float4 per thread, matrices go through shared memory (stride 9
+// is conflict free) and leave as coalesced float4.
+constexpr int QT = 256;
+
+__device__ __forceinline__ void quat_A(float r, float i, float j, float k, float* A) {
+    A[0] = -(j * j + k * k); A[1] = i * j - k * r;    A[2] = i * k + j * r;
+    A[3] = i * j + k * r;    A[4] = -(i * i + k * k); A[5] = j * k - i * r;
+    A[6] = i * k - j * r;    A[7] = j * k + i * r;    A[8] = -(i * i + j * j);
+}
+
+__global__ void __launch_bounds__(QT) quat_fwd_kernel(const float* __restrict__ q, float* __restrict__ out, long n) {
+    __shared__ __align__(16) float s[QT * 9];
+    const long first = (long)blockIdx.x * QT;
+    const int cnt = (int)min((long)QT, n - first);
+    if (threadIdx.x < cnt) {
+        const float4 v = __ldg(reinterpret_cast<const float4*>(q) + first + threadIdx.x);
+        float A[9];
+        quat_A(v.x, v.y, v.z, v.w, A);
+        const float two_s = 2.0f / (v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w);
+#pragma unroll
+        for (int e = 0; e < 9; ++e) s[threadIdx.x * 9 + e] = ((e & 3) == 0 ? 1.f : 0.f) + two_s * A[e];
+    }
+    __syncthreads();
+    float* g = out + first * 9;  // QT * 9 floats per CTA: 16-byte aligned whenever `out` is
+    const int count = cnt * 9;
+    const int n4 = ((reinterpret_cast<uintptr_t>(g) & 15) == 0) ? (count >> 2) : 0;
+    for (int t = threadIdx.x; t < n4; t += QT) reinterpret_cast<float4*>(g)[t] = reinterpret_cast<const float4*>(s)[t];
+    for (int t = (n4 << 2) + threadIdx.x; t < count; t += QT) g[t] = s[t];
+}
+
+__global__ void __launch_bounds__(QT) quat_bwd_kernel(const float* __restrict__ q, const float* __restrict__ g_out,
+                                                      float* __restrict__ g_q, long n) {
+    __shared__ __align__(16) float s[QT * 9];
+    const long first = (long)blockIdx.x * QT;
+    const int cnt = (int)min((long)QT, n - first);
+    const float* g = g_out + first * 9;
+    const int count = cnt * 9;
+    const int n4 = ((reinterpret_cast<uintptr_t>(g) & 15) == 0) ? (count >> 2) : 0;
+    for (int t = threadIdx.x; t < n4; t += QT) reinterpret_cast<float4*>(s)[t] = __ldg(reinterpret_cast<const float4*>(g) + t);
+    for (int t = (n4 << 2) + threadIdx.x; t < count; t += QT) s[t] = __ldg(g + t);
+    __syncthreads();
+    if (threadIdx.x >= cnt) return;
+    const float4 v = __ldg(reinterpret_cast<const float4*>(q) + first + threadIdx.x);
+    const float r = v.x, i = v.y, j = v.z, k = v.w;
+    float G[9], A[9];
+#pragma unroll
+    for (int e = 0; e < 9; ++e) G[e] = s[threadIdx.x * 9 + e];
+    quat_A(r, i, j, k, A);
+    const float two_s = 2.0f / (r * r + i * i + j * j + k * k);
+    float ga = 0.f;
+#pragma unroll
+    for (int e = 0; e < 9; ++e) ga = fmaf(G[e], A[e], ga);
+    const float dr = -k * G[1] + j * G[2] + k * G[3] - i * G[5] - j * G[6] + i * G[7];
+    const float di = j * (G[1] + G[3]) + k * (G[2] + G[6]) - 2.f * i * (G[4] + G[8]) + r * (G[7] - G[5]);
+    const float dj = -2.f * j * (G[0] + G[8]) + i * (G[1] + G[3]) + r * (G[2] - G[6]) + k * (G[5] + G[7]);
+    const float dk = -2.f * k * (G[0] + G[4]) + r * (G[3] - G[1]) + i * (G[2] + G[6]) + j * (G[5] + G[7]);
+    const float c = two_s * two_s * ga;  // d(2/|q|^2)/dq = -(2/|q|^2)^2 q
+    float4 o;
+    o.x = two_s * dr - c * r; o.y = two_s * di - c * i; o.z = two_s * dj - c * j; o.w = two_s * dk - c * k;
+    reinterpret_cast<float4*>(g_q)[first + threadIdx.x] = o;
+}
+
 int warp_grid(long units) {
     long blocks = (units + WARPS - 1) / WARPS;
     if (blocks > 148L * 64) blocks = 148L * 64;
@@ -211,10 +277,10 @@ int renorm_args(Renorm& a, int64_t m, int32_t j, int32_t c, int32_t dim, int32_t
 
 extern "C" int p2c_cum_changes_fwd(const float* changes, float* cumulative, int32_t n_clips, int32_t clip_len,
                                    int32_t n_bones, void* stream) {
-    if (!changes || !cumulative) return P2C_E_NULL;
     if (n_clips < 0 || clip_len < 1 || n_bones < 1) return P2C_E_BADARG;
     const long units = (long)n_clips * n_bones;
-    if (units == 0) return 0;
+    if (units == 0) return 0;  // empty batch: nothing to read or write (pointers of empty tensors are NULL)
+    if (!changes || !cumulative) return P2C_E_NULL;
     cum_changes_fwd_kernel<<<(unsigned)((units + 127) / 128), 128, 0, (cudaStream_t)stream>>>(changes, cumulative,
                                                                                              units, clip_len, n_bones);
     P2C_LAUNCH_CHECK();
@@ -224,10 +290,10 @@ extern "C" int p2c_cum_changes_fwd(const float* changes, float* cumulative, int3
 extern "C" int p2c_cum_changes_bwd(const float* changes, const float* cumulative, const float* g_cumulative,
                                    float* g_changes, int32_t n_clips, int32_t clip_len, int32_t n_bones,
                                    void* stream) {
-    if (!changes || !cumulative || !g_cumulative || !g_changes) return P2C_E_NULL;
     if (n_clips < 0 || clip_len < 1 || n_bones < 1) return P2C_E_BADARG;
     const long units = (long)n_clips * n_bones;
     if (units == 0) return 0;
+    if (!changes || !cumulative || !g_cumulative || !g_changes) return P2C_E_NULL;
     cum_changes_bwd_kernel<<<(unsigned)((units + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
         changes, cumulative, g_cumulative, g_changes, units, clip_len, n_bones);
     P2C_LAUNCH_CHECK();
@@ -238,12 +304,12 @@ extern "C" int p2c_renormalize_fwd(const float* sample, float* out, int64_t m, i
                                    int32_t hips, int32_t neck, int32_t autonormalize, float near_zero,
                                    const float* ref_shift, const float* ref_scale, const int32_t* ref_index,
                                    int32_t clip_len, void* stream) {
-    if (!sample || !out) return P2C_E_NULL;
     Renorm a;
     const int rc = renorm_args(a, m, j, c, dim, hips, neck, autonormalize, near_zero, ref_shift, ref_scale, ref_index,
                                clip_len);
     if (rc) return rc;
     if (m == 0) return 0;
+    if (!sample || !out) return P2C_E_NULL;
     if (dim == 2)
         renorm_fwd_kernel<2><<<warp_grid(m), WARPS * 32, 0, (cudaStream_t)stream>>>(sample, out, a);
     else
@@ -256,17 +322,38 @@ extern "C" int p2c_renormalize_bwd(const float* sample, const float* g_out, floa
                                    int32_t c, int32_t dim, int32_t hips, int32_t neck, int32_t autonormalize,
                                    float near_zero, const float* ref_scale, const int32_t* ref_index,
                                    int32_t clip_len, void* stream) {
-    if (!sample || !g_out || !g_sample) return P2C_E_NULL;
     Renorm a;
     // the reference shift does not enter the gradient; pass the scale pointer for both so the pair check holds
     const int rc = renorm_args(a, m, j, c, dim, hips, neck, autonormalize, near_zero, ref_scale, ref_scale, ref_index,
                                clip_len);
     if (rc) return rc;
     if (m == 0) return 0;
+    if (!sample || !g_out || !g_sample) return P2C_E_NULL;
     if (dim == 2)
         renorm_bwd_kernel<2><<<warp_grid(m), WARPS * 32, 0, (cudaStream_t)stream>>>(sample, g_out, g_sample, a);
     else
         renorm_bwd_kernel<3><<<warp_grid(m), WARPS * 32, 0, (cudaStream_t)stream>>>(sample, g_out, g_sample, a);
+    P2C_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int p2c_quaternion_to_matrix_fwd(const float* quat, float* out, int64_t n, void* stream) {
+    if (n < 0) return P2C_E_BADARG;
+    if (n == 0) return 0;
+    if (!quat || !out) return P2C_E_NULL;
+    if (reinterpret_cast<uintptr_t>(quat) & 15) return P2C_E_UNSUPPORTED;  // quaternions are read as float4
+    quat_fwd_kernel<<<(unsigned)((n + QT - 1) / QT), QT, 0, (cudaStream_t)stream>>>(quat, out, (long)n);
+    P2C_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int p2c_quaternion_to_matrix_bwd(const float* quat, const float* g_out, float* g_quat, int64_t n,
+                                            void* stream) {
+    if (n < 0) return P2C_E_BADARG;
+    if (n == 0) return 0;
+    if (!quat || !g_out || !g_quat) return P2C_E_NULL;
+    if ((reinterpret_cast<uintptr_t>(quat) | reinterpret_cast<uintptr_t>(g_quat)) & 15) return P2C_E_UNSUPPORTED;
+    quat_bwd_kernel<<<(unsigned)((n + QT - 1) / QT), QT, 0, (cudaStream_t)stream>>>(quat, g_out, g_quat, (long)n);
     P2C_LAUNCH_CHECK();
     return 0;
 }

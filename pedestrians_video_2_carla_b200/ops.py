@@ -47,6 +47,35 @@ def rotation_6d_to_matrix(d6):
     return _Rot6dToMatrix.apply(d6)
 
 
+class _QuaternionToMatrix(torch.autograd.Function):
+    """pytorch3d quaternion_to_matrix (real part first; the quaternion need not be unit: M = I + 2/|q|^2 A(q))."""
+
+    @staticmethod
+    def forward(ctx, q):
+        q = _f32c(q, 'quaternions')
+        out = torch.empty(q.shape[:-1] + (3, 3), device=q.device, dtype=torch.float32)
+        check(_lib.load().p2c_quaternion_to_matrix_fwd(ptr(q), ptr(out), q.numel() // 4, stream()),
+              'quaternion_to_matrix_fwd')
+        ctx.save_for_backward(q)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        (q,) = ctx.saved_tensors
+        g = _f32c(g, 'grad')
+        gq = torch.empty_like(q)
+        check(_lib.load().p2c_quaternion_to_matrix_bwd(ptr(q), ptr(g), ptr(gq), q.numel() // 4, stream()),
+              'quaternion_to_matrix_bwd')
+        return gq
+
+
+def quaternion_to_matrix(quaternions):
+    """(..., 4) quaternions, real part first -> (..., 3, 3) rotation matrices acting like the rest of the path."""
+    if quaternions.shape[-1] != 4:
+        raise RuntimeError('quaternion_to_matrix expects (..., 4)')
+    return _QuaternionToMatrix.apply(quaternions)
+
+
 def matrix_to_rotation_6d(matrix):
     """pytorch3d matrix_to_rotation_6d (modules/movements/seq2seq.py:330): first two rows; a view + copy."""
     return matrix[..., :2, :].clone().reshape(matrix.shape[:-2] + (6,))
@@ -395,37 +424,57 @@ class _FusedStep(torch.autograd.Function):
         pose_in = _f32c(pose_in, 'pose_in')
         N, L, B = pose_in.shape[:3]
         dev = pose_in.device
-        a = _lib.FusedStep()
-        a.tree, a.hips, a.neck = cfg['tree'], cfg['hips'], cfg['neck']
-        a.n_clips, a.clip_len, a.mode = N, L, cfg['mode']
-        a.input_6d = 1 if pose_in.shape[-1] == 6 and pose_in.dim() == 4 else 0
-        a.normalize = 1 if cfg['normalize'] else 0
-        a.mask_missing_joints = 1 if cfg['mask_missing_joints'] else 0
         gt2, gt3 = _f32c(cfg['gt_2d'], 'gt_2d'), _f32c(cfg['gt_3d'], 'gt_3d')
-        ref_loc, ref_rot = _f32c(cfg['ref_loc'], 'ref_loc'), _f32c(cfg['ref_rot'], 'ref_rot')
-        world_loc, world_rot = _f32c(cfg.get('world_loc'), 'world_loc'), _f32c(cfg.get('world_rot'), 'world_rot')
         ref_index = cfg.get('ref_index')
-        a.pose_in, a.ref_loc, a.ref_rot, a.ref_index = ptr(pose_in), ptr(ref_loc), ptr(ref_rot), ptr(ref_index)
-        a.world_loc, a.world_rot, a.camera = ptr(world_loc), ptr(world_rot), cfg['camera']
-        a.gt_2d, a.gt_2d_channels, a.gt_3d = ptr(gt2), gt2.shape[-1], ptr(gt3)
-        a.weight_2d, a.weight_3d = float(cfg.get('weight_2d', 1.0)), float(cfg.get('weight_3d', 1.0))
         out = cfg.get('out') or {}
-        rel_rot = out.get('rel_rot') if out.get('rel_rot') is not None else torch.empty((N, L, B, 3, 3), device=dev)
-        abs_rot = out.get('abs_rot') if out.get('abs_rot') is not None else torch.empty((N, L, B, 3, 3), device=dev)
-        abs_loc = out.get('abs_loc') if out.get('abs_loc') is not None else torch.empty((N, L, B, 3), device=dev)
-        proj = out.get('proj') if out.get('proj') is not None else torch.empty((N, L, B, 3), device=dev)
-        proj_norm = None
-        if cfg.get('want_transformed', True) and cfg['normalize']:
-            proj_norm = out.get('proj_norm') if out.get('proj_norm') is not None else torch.empty((N, L, B, 3), device=dev)
-        g_in = out.get('g_pose_in') if out.get('g_pose_in') is not None else torch.empty_like(pose_in)
-        nws = lib.p2c_fused_step_workspace_floats(N * L, B, a.input_6d)
-        ws = out.get('workspace')
-        if ws is None or ws.numel() < nws:
-            ws = _workspace(dev, int(nws))
-        losses = out.get('losses') if out.get('losses') is not None else torch.empty(8, device=dev)
-        a.rel_rot, a.abs_rot, a.abs_loc, a.proj, a.proj_norm = (ptr(rel_rot), ptr(abs_rot), ptr(abs_loc), ptr(proj),
-                                                                ptr(proj_norm))
-        a.g_pose_in, a.workspace, a.losses = ptr(g_in), ptr(ws), ptr(losses)
+        input_6d = 1 if pose_in.shape[-1] == 6 and pose_in.dim() == 4 else 0
+        # a caller that passes the same `out` dict every step (preallocated buffers, see fused_step_buffers) gets the
+        # argument block of the previous call back: only the per-step pointers are refreshed
+        key = (N, L, B, input_6d, gt2.shape[-1], cfg['mode'], cfg['hips'], cfg['neck'], bool(cfg['normalize']),
+               bool(cfg['mask_missing_joints']), float(cfg.get('weight_2d', 1.0)), float(cfg.get('weight_3d', 1.0)),
+               bool(cfg.get('want_transformed', True)), id(cfg['tree']), id(cfg['camera']),
+               cfg['ref_loc'].data_ptr(), cfg['ref_rot'].data_ptr(),
+               None if cfg.get('world_loc') is None else cfg['world_loc'].data_ptr(),
+               None if cfg.get('world_rot') is None else cfg['world_rot'].data_ptr(), _lib.raw_stream())
+        plan = out.get('_plan')
+        if plan is not None and plan[0] == key:
+            _, a, rel_rot, abs_rot, abs_loc, proj, proj_norm, g_in, losses, keep = plan
+            a.pose_in, a.gt_2d, a.gt_3d, a.ref_index = ptr(pose_in), ptr(gt2), ptr(gt3), ptr(ref_index)
+        else:
+            a = _lib.FusedStep()
+            a.tree, a.hips, a.neck = cfg['tree'], cfg['hips'], cfg['neck']
+            a.n_clips, a.clip_len, a.mode = N, L, cfg['mode']
+            a.input_6d = input_6d
+            a.normalize = 1 if cfg['normalize'] else 0
+            a.mask_missing_joints = 1 if cfg['mask_missing_joints'] else 0
+            ref_loc, ref_rot = _f32c(cfg['ref_loc'], 'ref_loc'), _f32c(cfg['ref_rot'], 'ref_rot')
+            world_loc, world_rot = _f32c(cfg.get('world_loc'), 'world_loc'), _f32c(cfg.get('world_rot'), 'world_rot')
+            a.pose_in, a.ref_loc, a.ref_rot, a.ref_index = ptr(pose_in), ptr(ref_loc), ptr(ref_rot), ptr(ref_index)
+            a.world_loc, a.world_rot, a.camera = ptr(world_loc), ptr(world_rot), cfg['camera']
+            a.gt_2d, a.gt_2d_channels, a.gt_3d = ptr(gt2), gt2.shape[-1], ptr(gt3)
+            a.weight_2d, a.weight_3d = float(cfg.get('weight_2d', 1.0)), float(cfg.get('weight_3d', 1.0))
+            rel_rot = out.get('rel_rot') if out.get('rel_rot') is not None else torch.empty((N, L, B, 3, 3), device=dev)
+            abs_rot = out.get('abs_rot') if out.get('abs_rot') is not None else torch.empty((N, L, B, 3, 3), device=dev)
+            abs_loc = out.get('abs_loc') if out.get('abs_loc') is not None else torch.empty((N, L, B, 3), device=dev)
+            proj = out.get('proj') if out.get('proj') is not None else torch.empty((N, L, B, 3), device=dev)
+            proj_norm = None
+            if cfg.get('want_transformed', True) and cfg['normalize']:
+                proj_norm = (out.get('proj_norm') if out.get('proj_norm') is not None
+                             else torch.empty((N, L, B, 3), device=dev))
+            g_in = out.get('g_pose_in') if out.get('g_pose_in') is not None else torch.empty_like(pose_in)
+            nws = lib.p2c_fused_step_workspace_floats(N * L, B, a.input_6d)
+            ws = out.get('workspace')
+            if ws is None or ws.numel() < nws:
+                ws = _workspace(dev, int(nws))
+            losses = out.get('losses') if out.get('losses') is not None else torch.empty(8, device=dev)
+            a.rel_rot, a.abs_rot, a.abs_loc, a.proj, a.proj_norm = (ptr(rel_rot), ptr(abs_rot), ptr(abs_loc),
+                                                                    ptr(proj), ptr(proj_norm))
+            a.g_pose_in, a.workspace, a.losses = ptr(g_in), ptr(ws), ptr(losses)
+            if all(out.get(k) is not None for k in ('rel_rot', 'abs_rot', 'abs_loc', 'proj', 'g_pose_in', 'losses')) \
+                    and (proj_norm is None or out.get('proj_norm') is not None):
+                # `keep` pins the tensors whose pointers live in the argument block
+                out['_plan'] = (key, a, rel_rot, abs_rot, abs_loc, proj, proj_norm, g_in, losses,
+                                (ws, ref_loc, ref_rot, world_loc, world_rot, cfg['tree'], cfg['camera']))
         check(lib.p2c_fused_step(a, stream()), 'fused_step')
         ctx.save_for_backward(g_in)
         ctx.set_materialize_grads(False)
@@ -447,6 +496,20 @@ class _FusedStep(torch.autograd.Function):
             return None, None
         (g_in,) = ctx.saved_tensors
         return g_in * g23, None
+
+
+def fused_step_buffers(n_clips, clip_len, n_bones, device, input_6d=True, transformed=False):
+    """Preallocated outputs for fused_step(out=...): a training loop with static shapes passes the same dict every
+    step, which also lets fused_step reuse its argument block (no per-step allocations; the outputs of step i are
+    overwritten by step i+1)."""
+    n, l, b = n_clips, clip_len, n_bones
+    out = dict(rel_rot=torch.empty((n, l, b, 3, 3), device=device), abs_rot=torch.empty((n, l, b, 3, 3), device=device),
+               abs_loc=torch.empty((n, l, b, 3), device=device), proj=torch.empty((n, l, b, 3), device=device),
+               g_pose_in=torch.empty((n, l, b, 6) if input_6d else (n, l, b, 3, 3), device=device),
+               losses=torch.empty(8, device=device))
+    if transformed:
+        out['proj_norm'] = torch.empty((n, l, b, 3), device=device)
+    return out
 
 
 def fused_step(pose_in, tree, camera, ref_loc, ref_rot, gt_2d, gt_3d, ref_index=None, world_loc=None, world_rot=None,

@@ -264,3 +264,35 @@ def test_many_tiles_deterministic_and_chunk_consistent(ops, lib, n, l):
         assert_close('chunk grad', gp * ((hi - lo) / n), gf[lo:hi], tol=2e-6)
         sums += part.losses[3:7].double().cpu()
     assert_close('loss sums', full.losses[3:7].double().cpu(), sums, tol=1e-6)
+
+
+def test_preallocated_buffers_reuse_the_argument_block(ops, lib):
+    """fused_step(out=fused_step_buffers(...)) over several steps with DIFFERENT inputs (the end-to-end loop of
+    bench.py): the cached argument block must pick up each step's input pointers, and the results must equal the
+    fresh-output call bit for bit."""
+    cam = None
+    pre = None
+    tree = None
+    for seed in (101, 102, 103):
+        c = make_case(8, 16, seed, world=False)
+        gt2, gt3 = make_targets(c)
+        if pre is None:
+            pre = ops.fused_step_buffers(c['n'], c['l'], c['b'], DEV, transformed=True)
+            tree = lib.make_tree(c['par'])
+            k = c['cam']
+            cam = lib.make_camera(k.R.tolist(), k.T.tolist(), k.f, k.px, k.py)
+            loc, rot = cu(c['loc']), cu(c['rot'])
+        args = dict(ref_index=c['sid'].int().to(DEV), hips=c['hips'], neck=c['neck'])
+        x = cu(c['d6']).requires_grad_(True)
+        r = ops.fused_step(x, tree, cam, loc, rot, cu(gt2), cu(gt3), out=pre, **args)
+        r.loc_2d_3d.backward()
+        assert '_plan' in pre
+        y = cu(c['d6']).requires_grad_(True)
+        f = ops.fused_step(y, tree, cam, loc, rot, cu(gt2), cu(gt3), **args)
+        f.loc_2d_3d.backward()
+        assert torch.equal(r.loc_2d_3d, f.loc_2d_3d) and torch.equal(x.grad, y.grad)
+        for name in ('relative_pose_rot', 'absolute_pose_rot', 'absolute_pose_loc', 'projection_2d',
+                     'projection_2d_transformed'):
+            assert torch.equal(getattr(r, name), getattr(f, name)), name
+        want = oracle_step(c, O.rotation_6d_to_matrix(c['d6']), gt=(gt2, gt3))
+        assert_close('loc_2d_3d', r.loc_2d_3d, want['loc_2d_3d'])

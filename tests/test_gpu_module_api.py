@@ -165,7 +165,8 @@ def test_projection_module_and_losses_against_oracle(api, mode):
     assert_close('projection_2d_transformed', sliced['projection_2d_transformed'], want['projection_2d_transformed'])
     from pedestrians_video_2_carla_b200.data.carla.skeleton import CARLA_SKELETON
     losses = {}
-    for m in api['LossModes']:
+    # loss_modes=[loc_2d_3d]: its requirements first, then the mode itself (modules/flow/base.py:71-93)
+    for m in (api['LossModes'][k] for k in ('loc_2d', 'loc_3d', 'loc_2d_3d')):
         fn, criterion, *deps = m.value
         if isinstance(fn, type):
             fn = fn(criterion=criterion, input_nodes=CARLA_SKELETON, output_nodes=CARLA_SKELETON, mask_missing_joints=True)

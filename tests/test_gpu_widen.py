@@ -231,3 +231,34 @@ def test_absolute_loc_large_batch_against_oracle(api):
     assert_close('projection_2d', got, proj)
     (got * w.float().to(DEV)).sum().backward()
     assert_close('grad', xg.grad, x64.grad, 2e-4)
+
+
+@pytest.mark.parametrize('shape', [(1000,), (7, 5, 26), (1,), (0,)])
+def test_quaternion_to_matrix_against_oracle(api, shape):
+    """The north star's quaternion entry (pytorch3d quaternion_to_matrix, real part first, not normalised first)."""
+    g = torch.Generator().manual_seed(22742 + len(shape))
+    q = torch.randn(tuple(shape) + (4,), generator=g, dtype=torch.float64)
+    w = torch.randn(tuple(shape) + (3, 3), generator=g, dtype=torch.float64)
+    q64 = q.clone().requires_grad_(True)
+    want = O.quaternion_to_matrix(q64)
+    (want * w).sum().backward()
+    qg = q.float().to(DEV).requires_grad_(True)
+    got = api['ops'].quaternion_to_matrix(qg)
+    assert got.shape == tuple(shape) + (3, 3)
+    if q.numel() == 0:
+        return
+    assert_close('matrix', got, want)
+    (got * w.float().to(DEV)).sum().backward()
+    assert_close('grad', qg.grad, q64.grad, 2e-4)
+
+
+def test_unit_quaternions_match_scipy_and_feed_the_fk(api):
+    from scipy.spatial.transform import Rotation
+    g = torch.Generator().manual_seed(3)
+    q = torch.randn((64, 4), generator=g, dtype=torch.float64)
+    q = q / q.norm(dim=-1, keepdim=True)
+    want = Rotation.from_quat(q[:, [1, 2, 3, 0]].numpy()).as_matrix()      # scipy is scalar-last
+    got = api['ops'].quaternion_to_matrix(q.float().to(DEV))
+    assert_close('vs scipy', got, torch.from_numpy(want))
+    with pytest.raises(RuntimeError):
+        api['ops'].quaternion_to_matrix(torch.zeros((3, 3), device=DEV))

@@ -91,3 +91,15 @@ def test_absolute_loc_movements_output(gold, ref32):
     assert_close('projection_2d', proj, gold['absloc/projection_2d'], 1e-6)
     (proj * gold['absloc/w']).sum().backward()
     assert_close('grad_x', x.grad, gold['absloc/grad_x'], 2e-5)
+
+
+def test_quaternion_oracle_against_scipy():
+    """pytorch3d is not installed anywhere reachable: the restated quaternion_to_matrix is pinned to scipy for unit
+    quaternions and to its own scale invariance (M(q) == M(c q)) for the rest."""
+    from scipy.spatial.transform import Rotation
+    g = torch.Generator().manual_seed(11)
+    q = torch.randn((200, 4), generator=g, dtype=torch.float64)
+    unit = q / q.norm(dim=-1, keepdim=True)
+    want = Rotation.from_quat(unit[:, [1, 2, 3, 0]].numpy()).as_matrix()
+    assert np.abs(O.quaternion_to_matrix(unit).numpy() - want).max() < 1e-12
+    assert np.abs(O.quaternion_to_matrix(q * 3.7).numpy() - want).max() < 1e-12
