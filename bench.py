@@ -343,7 +343,7 @@ def e2e_region(shard, steps, warmup, world):
         x = dbuf['d6'].requires_grad_(True)
         r = ops.fused_step(x, shard.tree, shard.cam, shard.loc, shard.rot, dbuf['gt2'], dbuf['gt3'], ref_index=dbuf['sid'],
                            want_transformed=False, out=pre)
-        r.loc_2d_3d.backward()
+        r.backward()            # = r.loc_2d_3d.backward(): the gradient is already in the step's output block
         consumed[k].record()
         if world > 1:
             dist.all_reduce(r.losses[3:7])
@@ -513,7 +513,7 @@ def main():
             'clocks': sampler.summary(note),
             'e2e': {'value': round(e2e_value, 1), 'unit': 'poses/s', 'h2d_bytes_per_step': h2d,
                     'd2h_bytes_per_step': d2h, 'steps': e2e_steps,
-                    'api': 'ops.fused_step(..., out=fused_step_buffers).loc_2d_3d.backward(); inputs from one pinned staging image '
+                    'api': 'r = ops.fused_step(..., out=fused_step_buffers); r.backward(); inputs from one pinned staging image '
                            'per step, copied on a prefetch stream'},
             'gpu_launches': shard.launches_per_step * args.steps}
     line['roofline'] = roofline_of(shard.poses, args.clip_len, ms_per_step,

@@ -410,7 +410,18 @@ def _workspace(dev, nfloats):
 class FusedStepResult(object):
     """Outputs of one fused pose_lifting step (see fused_step)."""
     __slots__ = ('loc_2d', 'loc_3d', 'loc_2d_3d', 'losses', 'relative_pose_rot', 'absolute_pose_rot',
-                 'absolute_pose_loc', 'projection_2d', 'projection_2d_transformed')
+                 'absolute_pose_loc', 'projection_2d', 'projection_2d_transformed', 'pose_in', 'grad_pose_in')
+
+    def backward(self):
+        """Same effect as `self.loc_2d_3d.backward()`, without a pass through the autograd engine for the loss node:
+        the kernel has already left d(loc_2d_3d)/d(pose_in) in `grad_pose_in`.  A leaf input receives it in `.grad`
+        (accumulated like autograd does); a model output continues into the model's graph from there.  With
+        preallocated `out=` buffers the gradient tensor is the preallocated one (overwritten by the next step)."""
+        x, g = self.pose_in, self.grad_pose_in
+        if x.grad_fn is not None:
+            torch.autograd.backward(x, g)
+        elif x.requires_grad:
+            x.grad = g if x.grad is None else x.grad + g
 
 
 class _FusedStep(torch.autograd.Function):
@@ -479,7 +490,7 @@ class _FusedStep(torch.autograd.Function):
         ctx.save_for_backward(g_in)
         ctx.set_materialize_grads(False)
         res = cfg.setdefault('_result', FusedStepResult())
-        res.losses = losses
+        res.losses, res.grad_pose_in = losses, g_in
         res.relative_pose_rot, res.absolute_pose_rot, res.absolute_pose_loc = rel_rot, abs_rot, abs_loc
         res.projection_2d, res.projection_2d_transformed = proj, proj_norm
         # loc_2d / loc_3d are reported values (views of the losses buffer, no autograd edge); the fused sum is the one
@@ -524,5 +535,5 @@ def fused_step(pose_in, tree, camera, ref_loc, ref_rot, gt_2d, gt_3d, ref_index=
                weight_3d=weight_3d, want_transformed=want_transformed, out=out)
     l2, l3, l23 = _FusedStep.apply(pose_in, cfg)
     res = cfg['_result']
-    res.loc_2d, res.loc_3d, res.loc_2d_3d = l2, l3, l23
+    res.loc_2d, res.loc_3d, res.loc_2d_3d, res.pose_in = l2, l3, l23, pose_in
     return res

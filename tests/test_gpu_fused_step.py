@@ -296,3 +296,30 @@ def test_preallocated_buffers_reuse_the_argument_block(ops, lib):
             assert torch.equal(getattr(r, name), getattr(f, name)), name
         want = oracle_step(c, O.rotation_6d_to_matrix(c['d6']), gt=(gt2, gt3))
         assert_close('loc_2d_3d', r.loc_2d_3d, want['loc_2d_3d'])
+
+
+def test_result_backward_equals_autograd_backward(ops, lib):
+    """FusedStepResult.backward() == loc_2d_3d.backward() for a leaf input and for a model output (non-leaf)."""
+    c = make_case(6, 16, 77, world=False)
+    gt2, gt3 = make_targets(c)
+    tree = lib.make_tree(c['par'])
+    k = c['cam']
+    cam = lib.make_camera(k.R.tolist(), k.T.tolist(), k.f, k.px, k.py)
+    args = dict(ref_index=c['sid'].int().to(DEV), hips=c['hips'], neck=c['neck'])
+
+    def run(direct, through_model):
+        w = torch.full((6,), 1.25, device=DEV, requires_grad=True)
+        leaf = cu(c['d6']).requires_grad_(True)
+        x = leaf * w if through_model else leaf
+        r = ops.fused_step(x, tree, cam, cu(c['loc']), cu(c['rot']), cu(gt2), cu(gt3), **args)
+        if direct:
+            r.backward()
+        else:
+            r.loc_2d_3d.backward()
+        return leaf.grad, w.grad
+    for through_model in (False, True):
+        a, aw = run(True, through_model)
+        b, bw = run(False, through_model)
+        assert torch.equal(a, b)
+        if through_model:
+            assert torch.equal(aw, bw)
