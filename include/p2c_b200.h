@@ -216,6 +216,23 @@ int p2c_renormalize_bwd(const float* sample, const float* g_out, float* g_sample
                         float near_zero, const float* ref_scale, const int32_t* ref_index, int32_t clip_len,
                         void* stream);
 
+/* ---- Evaluation metrics on the step's output buffers: MPJPE (metrics/mpjpe.py:29-45), MRPE (metrics/mrpe.py:38-76),
+ *      PCK (metrics/pck.py:54-97 with utils/tensors.py:12-40).  pred / gt (M,J,c).  `partials`: caller-owned workspace
+ *      of p2c_metric_workspace_floats() floats; `out`: two DOUBLES on the device, (sum of distances, number of
+ *      distances) or (correct, total); accumulate != 0 adds to them (the metric's running state), 0 overwrites.
+ *      MRPE: *_world (M,c) or NULL (zeros).  PCK: mask_src (M,J,c_mask) = targets['projection_2d'] or NULL (no mask),
+ *      mask_hips < 0: hips not exempt; norm_kind 0 = hips-neck distance of gt, 1 = bounding-box diagonal of gt.     */
+int64_t p2c_metric_workspace_floats(void);
+int p2c_mpjpe_sum(const float* pred, const float* gt, int64_t m, int32_t j, int32_t c, float* partials,
+                  double* out, int32_t accumulate, void* stream);
+int p2c_mrpe_sum(const float* pred, const float* gt, const float* pred_world, const float* gt_world,
+                 int64_t m, int32_t j, int32_t c, int32_t hips, float* partials, double* out,
+                 int32_t accumulate, void* stream);
+int p2c_pck_count(const float* pred, const float* gt, const float* mask_src, int64_t m, int32_t j,
+                  int32_t c, int32_t c_mask, int32_t mask_hips, int32_t hips, int32_t neck,
+                  int32_t norm_kind, float threshold, float near_zero, float* partials, double* out,
+                  int32_t accumulate, void* stream);
+
 const char* p2c_version(void);
 
 #ifdef __cplusplus

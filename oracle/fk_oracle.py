@@ -24,7 +24,7 @@ __all__ = [
     'projection_module_forward', 'hips_neck_normalize', 'missing_joints_mask', 'loss_loc_2d',
     'loss_loc_3d', 'loss_loc_2d_3d', 'full_step', 'HIPS', 'NECK',
     'normalize', 'get_shift_scale', 'denormalize', 'reference_denormalize', 'cumulative_changes', 'loss_rot_3d',
-    'quaternion_to_matrix', 'loss_cum_pose_changes', 'loss_pose_changes', 'loss_weighted_loc_2d_loc_rot_3d', 'abs_from_abs_loc',
+    'quaternion_to_matrix', 'metric_mpjpe', 'metric_mrpe', 'metric_pck', 'get_bboxes', 'loss_cum_pose_changes', 'loss_pose_changes', 'loss_weighted_loc_2d_loc_rot_3d', 'abs_from_abs_loc',
 ]
 
 FILES_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), '..',
@@ -475,3 +475,55 @@ def quaternion_to_matrix(quaternions):
         two_s * (i * j + k * r), 1 - two_s * (i * i + k * k), two_s * (j * k - i * r),
         two_s * (i * k - j * r), two_s * (j * k + i * r), 1 - two_s * (i * i + j * j)), -1)
     return o.reshape(quaternions.shape[:-1] + (3, 3))
+
+
+# ----------------------------------------------------------------------------- metrics
+def metric_mpjpe(pred_abs_loc, gt_abs_loc):
+    """metrics/mpjpe.py:29-49 for one update: millimetres."""
+    per_clip = torch.mean(torch.linalg.norm(pred_abs_loc - gt_abs_loc, dim=-1, ord=2), dim=(-2, -1))
+    return 1000.0 * torch.sum(per_clip) / per_clip.numel()
+
+
+def metric_mrpe(pred_abs_loc, gt_abs_loc, pred_world_loc_changes, gt_world_loc_changes, pred_world_loc=None,
+                hips=HIPS, neck=NECK):
+    """metrics/mrpe.py:38-80 for one update: millimetres."""
+    if pred_world_loc_changes is not None:
+        pw, _ = calculate_world_from_changes(pred_world_loc_changes.shape, pred_world_loc_changes,
+                                             dtype=pred_abs_loc.dtype)
+    else:
+        pw = pred_world_loc
+    gw, _ = calculate_world_from_changes(pw.shape, gt_world_loc_changes, dtype=pred_abs_loc.dtype)
+    ph, _ = get_shift_scale(pred_abs_loc, hips, neck)
+    th, _ = get_shift_scale(gt_abs_loc, hips, neck)
+    per_clip = torch.mean(torch.linalg.norm((pw + ph) - (gw + th), dim=-1, ord=2), dim=-1)
+    return 1000.0 * torch.sum(per_clip) / per_clip.numel()
+
+
+def get_bboxes(sample, near_zero=1e-5):
+    """utils/tensors.py:12-26."""
+    missing = torch.all(sample[..., 0:2] < near_zero, dim=-1)
+    lo = sample.clone()
+    lo[missing] = float('inf')
+    hi = sample.clone()
+    hi[missing] = float('-inf')
+    return torch.stack((lo.min(dim=-2)[0], hi.max(dim=-2)[0]), dim=-2)
+
+
+def metric_pck(pred, gt, gt_projection_2d=None, norm='bbox', threshold=0.05, mask_missing_joints=True, hips=HIPS,
+               neck=NECK, near_zero=1e-5):
+    """metrics/pck.py:54-97 for one update -> (correct, total)."""
+    if mask_missing_joints and gt_projection_2d is not None:
+        mask = missing_joints_mask(gt_projection_2d, hips)
+    else:
+        mask = torch.ones(gt.shape[:-1], dtype=torch.bool)
+    if norm == 'hn':
+        normalize = get_shift_scale(gt, hips, neck)[1]
+    else:
+        boxes = get_bboxes(gt, near_zero)
+        normalize = torch.linalg.norm(boxes[..., 1, :] - boxes[..., 0, :], dim=-1, ord=2)
+    normalize = normalize.clone()
+    mask[normalize < near_zero] = 0
+    normalize[normalize < near_zero] = 1
+    normalize = normalize[(slice(None),) * normalize.ndim + (None,) * (pred.ndim - normalize.ndim)]
+    dist = torch.linalg.norm((pred - gt) / normalize, dim=-1, ord=2)
+    return int(torch.sum(dist[mask] < threshold)), int(dist[mask].numel())

@@ -79,6 +79,11 @@ _SIGS = {
                                       C.c_int32, C.c_float, _P, _P, _P, C.c_int32, _P]),
     'p2c_renormalize_bwd': (C.c_int, [_P, _P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                                       C.c_int32, C.c_float, _P, _P, C.c_int32, _P]),
+    'p2c_metric_workspace_floats': (C.c_int64, []),
+    'p2c_mpjpe_sum': (C.c_int, [_P, _P, C.c_int64, C.c_int32, C.c_int32, _P, _P, C.c_int32, _P]),
+    'p2c_mrpe_sum': (C.c_int, [_P, _P, _P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, _P, _P, C.c_int32, _P]),
+    'p2c_pck_count': (C.c_int, [_P, _P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
+                                C.c_int32, C.c_int32, C.c_float, C.c_float, _P, _P, C.c_int32, _P]),
     'p2c_version': (C.c_char_p, []),
 }
 
@@ -122,8 +127,8 @@ def ptr(t, name='tensor'):
         return None
     if not t.is_cuda:
         raise RuntimeError('p2c_b200: %s must be a CUDA tensor (no CPU fallback); got device %s' % (name, t.device))
-    if t.dtype not in (torch.float32, torch.int32):
-        raise RuntimeError('p2c_b200: %s must be float32/int32, got %s' % (name, t.dtype))
+    if t.dtype not in (torch.float32, torch.int32, torch.float64):
+        raise RuntimeError('p2c_b200: %s must be float32/int32 (float64: metric accumulators), got %s' % (name, t.dtype))
     if not t.is_contiguous():
         raise RuntimeError('p2c_b200: %s must be contiguous' % name)
     return C.c_void_p(t.data_ptr())

@@ -120,6 +120,51 @@ def main():
     out['absloc/w'], out['absloc/grad_x'] = wp, xa.grad
     assert ad['absolute_pose_rot'] is None and ad['relative_pose_rot'] is None and ad['relative_pose_loc'] is None
 
+    # -- 4. metrics (metrics/mpjpe.py, mrpe.py, pck.py) with a stand-in for torchmetrics.Metric (state = attributes)
+    class Metric(object):
+        def __init__(self, dist_sync_on_step=False, **kw):
+            pass
+
+        def add_state(self, name, default, dist_reduce_fx=None):
+            setattr(self, name, default.clone())
+    G._mod('torchmetrics', Metric=Metric)
+    from pedestrians_video_2_carla.metrics.mpjpe import MPJPE
+    from pedestrians_video_2_carla.metrics.mrpe import MRPE
+    from pedestrians_video_2_carla.metrics.pck import PCK
+    wlc_p = torch.randn((N, L, 3), generator=g) * 0.05
+    wlc_t = torch.randn((N, L, 3), generator=g) * 0.05
+    noisy = tproj.detach().clone()
+    noisy[..., :2] += torch.randn((N, L, 26, 2), generator=g) * 12.0
+    tp = tproj.detach().clone()
+    tp[drop] = 0.0                                   # missing joints are perfect zeros in the targets
+    tp[1, 2] = 0.0                                   # a frame with no detection at all
+    noisy_t = proj_t.detach() + torch.randn((N, L, 26, 3), generator=g) * torch.tensor([0.05, 0.05, 0.0])
+    preds = {'absolute_pose_loc': d['absolute_pose_loc'].detach(), 'world_loc_changes': wlc_p,
+             'world_loc': None, 'projection_2d': noisy, 'projection_2d_transformed': noisy_t}
+    tgts = {'absolute_pose_loc': td['absolute_pose_loc'], 'world_loc_changes': wlc_t, 'projection_2d': tp,
+            'projection_2d_transformed': tproj_t}
+    out['metric/pred_abs_loc'], out['metric/gt_abs_loc'] = preds['absolute_pose_loc'], tgts['absolute_pose_loc']
+    out['metric/pred_wlc'], out['metric/gt_wlc'] = wlc_p, wlc_t
+    out['metric/pred_projection_2d'], out['metric/gt_projection_2d'] = noisy, tp
+    out['metric/pred_projection_2d_transformed'], out['metric/gt_projection_2d_transformed'] = noisy_t, tproj_t
+    m = MPJPE()
+    m.update(preds, tgts)
+    m.update(preds, tgts)                            # running state over two updates
+    out['metric/mpjpe'] = m.compute()
+    m = MRPE()
+    m.update(preds, tgts)
+    out['metric/mrpe'] = m.compute()
+    m = MRPE()
+    m.update(dict(preds, world_loc_changes=None, world_loc=torch.cumsum(wlc_p, dim=1) * 1.5), tgts)
+    out['metric/mrpe_world_loc'] = m.compute()
+    for name, kw in (('bbox', {}), ('hn', {'get_normalization_tensor': 'hn'}),
+                     ('bbox_nomask', {'mask_missing_joints': False}),
+                     ('hn_transformed', {'get_normalization_tensor': 'hn', 'key': 'projection_2d_transformed',
+                                         'threshold': 0.1})):
+        m = PCK(**kw)
+        m.update(preds, tgts)
+        out['metric/pck_' + name] = torch.stack((m.correct.double(), m.total.double(), m.compute().double()))
+
     skel_id = [ref.CARLA_REFERENCE_SKELETON_TYPES.index((a, s)) for a, s in zip(ages, genders)]
     arrays = {k: v.detach().numpy() for k, v in out.items()}
     arrays['skeleton_id'] = np.asarray(skel_id, dtype=np.int32)

@@ -262,3 +262,65 @@ def test_unit_quaternions_match_scipy_and_feed_the_fk(api):
     assert_close('vs scipy', got, torch.from_numpy(want))
     with pytest.raises(RuntimeError):
         api['ops'].quaternion_to_matrix(torch.zeros((3, 3), device=DEV))
+
+
+def test_metrics_against_reference_golden(gold):
+    """MPJPE / MRPE / PCK classes (kernel accumulators) vs the reference's torchmetrics classes run on the same
+    inputs; counts are exact, distances within 1e-4."""
+    from pedestrians_video_2_carla_b200.metrics import MPJPE, MRPE, PCK
+    d = {k: v.to(DEV) for k, v in gold.items() if k.startswith('metric/')}
+    preds = {'absolute_pose_loc': d['metric/pred_abs_loc'], 'world_loc_changes': d['metric/pred_wlc'],
+             'world_loc': None, 'projection_2d': d['metric/pred_projection_2d'],
+             'projection_2d_transformed': d['metric/pred_projection_2d_transformed']}
+    tgts = {'absolute_pose_loc': d['metric/gt_abs_loc'], 'world_loc_changes': d['metric/gt_wlc'],
+            'projection_2d': d['metric/gt_projection_2d'],
+            'projection_2d_transformed': d['metric/gt_projection_2d_transformed']}
+    m = MPJPE()
+    m.update(preds, tgts)
+    m.update(preds, tgts)
+    assert_close('mpjpe', m.compute(), gold['metric/mpjpe'])
+    m.reset()
+    m.update({}, tgts)                                # missing key: silently skipped like the reference (KeyError)
+    assert float(m.state[1]) == 0.0
+    r = MRPE()
+    r.update(preds, tgts)
+    assert_close('mrpe', r.compute(), gold['metric/mrpe'])
+    r = MRPE()
+    r.update(dict(preds, world_loc_changes=None, world_loc=torch.cumsum(d['metric/pred_wlc'], dim=1) * 1.5), tgts)
+    assert_close('mrpe world_loc', r.compute(), gold['metric/mrpe_world_loc'])
+    for name, kw in (('bbox', {}), ('hn', {'get_normalization_tensor': 'hn'}),
+                     ('bbox_nomask', {'mask_missing_joints': False}),
+                     ('hn_transformed', {'get_normalization_tensor': 'hn', 'key': 'projection_2d_transformed',
+                                         'threshold': 0.1})):
+        p = PCK(**kw)
+        p.update(preds, tgts)
+        want = gold['metric/pck_' + name]
+        assert (float(p.state[0]), float(p.state[1])) == (float(want[0]), float(want[1])), name
+        assert_close('pck ' + name, p.compute(), want[2].float())
+
+
+def test_metrics_large_batch_against_oracle():
+    """256 x 16 (BASELINE config 2 size): kernel accumulators vs the float64 oracle, run twice (determinism)."""
+    from pedestrians_video_2_carla_b200.metrics import MPJPE, PCK
+    g = torch.Generator().manual_seed(22742 + 9)
+    n, l = 256, 16
+    gt = torch.randn((n, l, 26, 3), generator=g, dtype=torch.float64)
+    pred = gt + torch.randn((n, l, 26, 3), generator=g, dtype=torch.float64) * 0.05
+    want = O.metric_mpjpe(pred, gt)
+    vals = []
+    for _ in range(2):
+        m = MPJPE()
+        m.update({'absolute_pose_loc': pred.float().to(DEV)}, {'absolute_pose_loc': gt.float().to(DEV)})
+        vals.append(m.compute())
+    assert torch.equal(vals[0], vals[1])
+    assert_close('mpjpe', vals[0], want)
+    g2 = gt.clone()
+    g2[..., :2] = g2[..., :2] * 40 + 300
+    g2[torch.rand((n, l, 26), generator=g) < 0.1] = 0
+    p2 = g2 + torch.randn((n, l, 26, 3), generator=g, dtype=torch.float64) * torch.tensor([2.0, 2.0, 0.0])
+    # decisions within 1e-3 of the threshold can flip in fp32: allow that many
+    correct, total = O.metric_pck(p2.float().double(), g2.float().double(), g2.float().double(), 'bbox', 0.05)
+    p = PCK()
+    p.update({'projection_2d': p2.float().to(DEV)}, {'projection_2d': g2.float().to(DEV)})
+    assert float(p.state[1]) == total
+    assert abs(float(p.state[0]) - correct) <= 3

@@ -103,3 +103,21 @@ def test_quaternion_oracle_against_scipy():
     want = Rotation.from_quat(unit[:, [1, 2, 3, 0]].numpy()).as_matrix()
     assert np.abs(O.quaternion_to_matrix(unit).numpy() - want).max() < 1e-12
     assert np.abs(O.quaternion_to_matrix(q * 3.7).numpy() - want).max() < 1e-12
+
+
+def test_metrics_against_reference_golden(gold):
+    pa, ga = gold['metric/pred_abs_loc'], gold['metric/gt_abs_loc']
+    assert_close('mpjpe', O.metric_mpjpe(pa, ga), gold['metric/mpjpe'], 1e-6)
+    assert_close('mrpe', O.metric_mrpe(pa, ga, gold['metric/pred_wlc'], gold['metric/gt_wlc']), gold['metric/mrpe'],
+                 1e-6)
+    wl = torch.cumsum(gold['metric/pred_wlc'], dim=1) * 1.5
+    assert_close('mrpe world_loc', O.metric_mrpe(pa, ga, None, gold['metric/gt_wlc'], wl),
+                 gold['metric/mrpe_world_loc'], 1e-6)
+    p2, g2 = gold['metric/pred_projection_2d'], gold['metric/gt_projection_2d']
+    pt, gt = gold['metric/pred_projection_2d_transformed'], gold['metric/gt_projection_2d_transformed']
+    for name, args in (('bbox', (p2, g2, g2, 'bbox', 0.05, True)), ('hn', (p2, g2, g2, 'hn', 0.05, True)),
+                       ('bbox_nomask', (p2, g2, g2, 'bbox', 0.05, False)),
+                       ('hn_transformed', (pt, gt, g2, 'hn', 0.1, True))):
+        correct, total = O.metric_pck(*args)
+        want = gold['metric/pck_' + name]
+        assert (correct, total) == (int(want[0]), int(want[1])), name
