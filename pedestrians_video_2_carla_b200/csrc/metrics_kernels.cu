@@ -34,17 +34,19 @@ __global__ void __launch_bounds__(WARPS * 32) metric_partial_kernel(MetricArgs a
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int C = a.C;
     float s0 = 0.f, s1 = 0.f;  // (sum, count) or (correct, total)
-    for (long m = (long)blockIdx.x * WARPS + warp; m < a.M; m += (long)gridDim.x * WARPS) {
+    if (a.kind == 0) {  // MPJPE has no per-pose structure: a flat grid-stride loop over joints
+        const long total = a.M * a.J;
+        for (long i = (long)blockIdx.x * (WARPS * 32) + threadIdx.x; i < total; i += (long)gridDim.x * (WARPS * 32)) {
+            float q = 0.f;
+            for (int c = 0; c < C; ++c) { const float d = __ldg(a.pred + i * C + c) - __ldg(a.gt + i * C + c); q = fmaf(d, d, q); }
+            s0 += sqrtf(q);
+            s1 += 1.f;
+        }
+    }
+    for (long m = (long)blockIdx.x * WARPS + warp; a.kind != 0 && m < a.M; m += (long)gridDim.x * WARPS) {
         const float* p = a.pred + m * a.J * C;
         const float* g = a.gt + m * a.J * C;
-        if (a.kind == 0) {  // MPJPE
-            for (int j = lane; j < a.J; j += 32) {
-                float q = 0.f;
-                for (int c = 0; c < C; ++c) { const float d = p[j * C + c] - g[j * C + c]; q = fmaf(d, d, q); }
-                s0 += sqrtf(q);
-                s1 += 1.f;
-            }
-        } else if (a.kind == 1) {  // MRPE
+        if (a.kind == 1) {  // MRPE
             if (lane == 0) {
                 float q = 0.f;
                 for (int c = 0; c < C; ++c) {
@@ -56,7 +58,45 @@ __global__ void __launch_bounds__(WARPS * 32) metric_partial_kernel(MetricArgs a
                 s0 += sqrtf(q);
                 s1 += 1.f;
             }
-        } else {  // PCK
+        } else if (a.J <= 32 && C <= 3) {  // PCK, lane = joint: every operand is read once into registers
+            const bool act = lane < a.J;
+            float gv[3] = {0.f, 0.f, 0.f}, pv[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+            for (int c = 0; c < 3; ++c)
+                if (c < C && act) { gv[c] = __ldg(g + lane * C + c); pv[c] = __ldg(p + lane * C + c); }
+            bool kept = act;
+            if (a.mask_src && act && lane != a.mask_hips) {
+                const float* ms = a.mask_src + (m * a.J + lane) * a.Cm;
+                for (int c = 0; c < a.Cm; ++c) kept = kept && (__ldg(ms + c) != 0.f);
+            }
+            float q = 0.f;
+            if (a.norm == 0) {  // 'hn'
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const float d = __shfl_sync(FULL_MASK, gv[c], a.neck) - __shfl_sync(FULL_MASK, gv[c], a.hips);
+                    if (c < C) q = fmaf(d, d, q);
+                }
+            } else {  // 'bbox' around the detected points of the target (all of x, y < near_zero = missing)
+                const bool detected = act && !(gv[0] < a.near_zero && gv[1] < a.near_zero);
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const float d = warp_max(detected ? gv[c] : -FINF) - warp_min(detected ? gv[c] : FINF);
+                    if (c < C) q = fmaf(d, d, q);
+                }
+            }
+            float norm = sqrtf(q);
+            if (norm < a.near_zero) { kept = false; norm = 1.f; }   // mask[normalize < near_zero] = 0
+            if (kept) {
+                float e2 = 0.f;
+#pragma unroll
+                for (int c = 0; c < 3; ++c) {
+                    const float d = (pv[c] - gv[c]) / norm;
+                    if (c < C) e2 = fmaf(d, d, e2);
+                }
+                if (sqrtf(e2) < a.threshold) s0 += 1.f;
+                s1 += 1.f;
+            }
+        } else {  // PCK, any joint count
             float norm;
             if (a.norm == 0) {  // 'hn': |neck - hips| of the target
                 float q = 0.f;

@@ -15,6 +15,7 @@ constexpr float FMAX = 3.402823466e38f;
 // ---- cum_pose_changes: P[n,t,b] = P[n,t-1,b] . C[n,t,b], P[n,-1,b] = I --------------------------
 // thread = (clip, bone); for a fixed frame the 26 bones of a clip are 936 contiguous bytes, so a warp's loads of one
 // frame touch one or two contiguous runs and every sector fetched is fully used.
+// Direct form (any alignment): a warp's nine 36-byte-strided loads touch 32 sectors each.
 __global__ void __launch_bounds__(128) cum_changes_fwd_kernel(const float* __restrict__ c, float* __restrict__ out,
                                                               long units, int L, int B) {
     const long u = (long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -22,10 +23,69 @@ __global__ void __launch_bounds__(128) cum_changes_fwd_kernel(const float* __res
     const long n = u / B;
     const int b = (int)(u - n * B);
     M3 p = m3_identity();
+#pragma unroll 4
     for (int t = 0; t < L; ++t) {
         const long e = ((n * L + t) * B + b) * 9;
         p = m3_mul(p, m3_from(c + e));
         m3_to(out + e, p);
+    }
+}
+
+// Staged form (B * 9 even, 8-byte aligned tensors): a CTA owns CK clips; per frame their CK rows of B * 9 floats come in
+// as coalesced float2 (prefetched into registers one frame ahead), the (clip, bone) threads update their 3x3 in shared
+// memory in place (stride 9 words: conflict free), and the rows leave as coalesced float2.  ncu on the direct form:
+// 32 sectors per request, stalled on lg_throttle.
+constexpr int CK = 8;
+constexpr int CT = 256;
+constexpr int CPF = 4;   // float2 per thread and frame: CK * 16 * 9 / 2 = 576 float2 <= CT * CPF (B <= 32)
+
+__global__ void __launch_bounds__(CT) cum_changes_fwd_staged_kernel(const float* __restrict__ c,
+                                                                   float* __restrict__ out, int N, int L, int B,
+                                                                   int ck) {
+    extern __shared__ float2 tile2[];                 // ck * row2 float2 (ck <= CK clips per CTA)
+    float* tile = reinterpret_cast<float*>(tile2);
+    const int row2 = B * 9 / 2;                        // float2 per (clip, frame) row
+    const int n0 = blockIdx.x * ck;
+    const int nk = min(ck, N - n0);
+    const int total2 = nk * row2;
+    const int k = threadIdx.x / B, b = threadIdx.x - k * B;
+    const bool worker = threadIdx.x < nk * B;
+    float2 pre[CPF];
+    auto fetch = [&](int t) {
+#pragma unroll
+        for (int r = 0; r < CPF; ++r) {
+            const int i = threadIdx.x + r * CT;
+            if (i < total2) {
+                const int kk = i / row2, w = i - kk * row2;
+                pre[r] = __ldg(reinterpret_cast<const float2*>(c + ((long)(n0 + kk) * L + t) * B * 9) + w);
+            }
+        }
+    };
+    M3 p = m3_identity();
+    fetch(0);
+    for (int t = 0; t < L; ++t) {
+#pragma unroll
+        for (int r = 0; r < CPF; ++r) {
+            const int i = threadIdx.x + r * CT;
+            if (i < total2) tile2[i] = pre[r];
+        }
+        __syncthreads();
+        if (t + 1 < L) fetch(t + 1);
+        if (worker) {
+            float* m = tile + (k * B + b) * 9;
+            p = m3_mul(p, m3_from(m));
+            m3_to(m, p);
+        }
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < CPF; ++r) {
+            const int i = threadIdx.x + r * CT;
+            if (i < total2) {
+                const int kk = i / row2, w = i - kk * row2;
+                reinterpret_cast<float2*>(out + ((long)(n0 + kk) * L + t) * B * 9)[w] = tile2[i];
+            }
+        }
+        __syncthreads();
     }
 }
 
@@ -253,6 +313,208 @@ __global__ void __launch_bounds__(QT) quat_bwd_kernel(const float* __restrict__ 
     reinterpret_cast<float4*>(g_q)[first + threadIdx.x] = o;
 }
 
+// ---- C == DIM (absolute locations, 2-channel projections): chunked flat variant --------------------------------
+// A CTA takes 32 consecutive poses (32 * J * DIM floats: a 16-byte multiple for even J * DIM), one thread per pose
+// derives the pose's constants into shared memory, then the whole chunk streams through as float4 with the pose and
+// channel of every float recovered from its flat index.  The per-element work is one FMA: with A = rs / scale and
+// B_k = rh_k - s_k * A, (x - s_k) / scale * rs + rh_k = x * A + B_k (the per-element IEEE division of the first
+// version kept the kernel instruction bound at 35 % of the HBM rate: ncu, issue slots 72 % busy).  nan_to_zero keeps
+// its meaning: a degenerate scale (0, inf, NaN) or a non-finite input gives y = 0, i.e. the bare reference shift.
+constexpr int RP = 32;
+constexpr int RTH = 128;
+
+template <int DIM>
+struct PoseConst {
+    float s[DIM], rh[DIM], d[DIM], hx[DIM], kx[DIM], bk[DIM];
+    float scale, rs, inv, A;
+    int ok;
+};
+
+template <int DIM>
+__device__ __forceinline__ void pose_consts(PoseConst<DIM>& c, const float* p, long m, const Renorm& a) {
+    float q = 0.f;
+#pragma unroll
+    for (int k = 0; k < DIM; ++k) {
+        c.s[k] = 0.f; c.rh[k] = 0.f; c.d[k] = 0.f; c.hx[k] = 0.f; c.kx[k] = 0.f;
+        if (a.autonormalize) {
+            c.s[k] = __ldg(p + a.hips * DIM + k);
+            c.d[k] = __ldg(p + a.neck * DIM + k) - c.s[k];
+            q = fmaf(c.d[k], c.d[k], q);
+        }
+    }
+    c.scale = a.autonormalize ? sqrtf(q) : 1.f;
+    c.ok = c.scale > 0.f && c.scale <= FMAX;
+    c.inv = c.ok ? 1.0f / c.scale : 0.f;
+    c.rs = 1.f;
+    if (a.ref_scale) {
+        const long clip = m / a.L;
+        const long row = a.ref_index ? (long)__ldg(a.ref_index + clip) : clip;
+        c.rs = __ldg(a.ref_scale + row);
+        if (a.ref_shift) {
+#pragma unroll
+            for (int k = 0; k < DIM; ++k) c.rh[k] = __ldg(a.ref_shift + row * DIM + k);
+        }
+    }
+    c.A = c.ok ? c.rs / c.scale : 0.f;
+#pragma unroll
+    for (int k = 0; k < DIM; ++k) c.bk[k] = c.ok ? fmaf(-c.s[k], c.A, c.rh[k]) : c.rh[k];
+    // (a non-finite hips or neck coordinate makes the scale non-finite: ok = 0, A = 0, y = 0 for the whole pose, which
+    //  is what nan_to_zero leaves of (x - s) / scale in the reference)
+}
+
+template <int DIM>
+__device__ __forceinline__ float pick(const float* v, int k) {
+    return k == 0 ? v[0] : (k == 1 ? v[1] : v[DIM - 1]);
+}
+
+template <int DIM>
+__global__ void __launch_bounds__(RTH) renorm_flat_fwd_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                             Renorm a) {
+    __shared__ PoseConst<DIM> cs[RP];
+    const int JC = a.J * DIM;
+    const float inv_jc = 1.0f / (float)JC;
+    for (long chunk = blockIdx.x; chunk * RP < a.M; chunk += gridDim.x) {
+        const long m0 = chunk * RP;
+        const int np = (int)min((long)RP, a.M - m0);
+        if (threadIdx.x < np) pose_consts<DIM>(cs[threadIdx.x], in + (m0 + threadIdx.x) * JC, m0 + threadIdx.x, a);
+        __syncthreads();
+        const float* src = in + m0 * JC;
+        float* dst = out + m0 * JC;
+        const int nf = np * JC;
+        const bool vec = ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0;
+        const int n4 = vec ? (nf >> 2) : 0;
+        auto value = [&](float x, float A, float B, float shift) {
+            // y = 0 (-> the bare shift) for what nan_to_zero cuts: a non-finite x
+            return (a.autonormalize && !(fabsf(x) <= FMAX)) ? shift : fmaf(x, A, B);
+        };
+        for (int i = threadIdx.x; i < n4; i += RTH) {
+            const float4 v = __ldg(reinterpret_cast<const float4*>(src) + i);
+            float r[4] = {v.x, v.y, v.z, v.w};
+            // floor(e / JC) through the reciprocal: exact, the quotient is >= 0.5 / JC away from an integer boundary
+            const int pose = (int)(((float)(4 * i) + 0.5f) * inv_jc);
+            int rem = 4 * i - pose * JC;
+            const PoseConst<DIM>& c0 = cs[pose];
+            const PoseConst<DIM>& c1 = cs[min(pose + 1, np - 1)];   // a float4 straddles at most one pose boundary
+            int k = rem % DIM;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const bool nxt = rem >= JC;
+                const PoseConst<DIM>& c = nxt ? c1 : c0;
+                const int kk = nxt ? (rem - JC) % DIM : k;
+                r[q] = value(r[q], c.A, pick<DIM>(c.bk, kk), pick<DIM>(c.rh, kk));
+                ++rem;
+                k = (k + 1 == DIM) ? 0 : k + 1;
+            }
+            reinterpret_cast<float4*>(dst)[i] = make_float4(r[0], r[1], r[2], r[3]);
+        }
+        for (int e = (n4 << 2) + threadIdx.x; e < nf; e += RTH) {
+            const int pose = e / JC, k = (e - pose * JC) % DIM;
+            const PoseConst<DIM>& c = cs[pose];
+            dst[e] = value(__ldg(src + e), c.A, pick<DIM>(c.bk, k), pick<DIM>(c.rh, k));
+        }
+        __syncthreads();
+    }
+}
+
+template <int DIM>
+__global__ void __launch_bounds__(RTH) renorm_flat_bwd_kernel(const float* __restrict__ in,
+                                                             const float* __restrict__ g_out,
+                                                             float* __restrict__ g_in, Renorm a) {
+    __shared__ PoseConst<DIM> cs[RP];
+    const int JC = a.J * DIM;
+    const float inv_jc = 1.0f / (float)JC;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (long chunk = blockIdx.x; chunk * RP < a.M; chunk += gridDim.x) {
+        const long m0 = chunk * RP;
+        const int np = (int)min((long)RP, a.M - m0);
+        if (threadIdx.x < np) pose_consts<DIM>(cs[threadIdx.x], in + (m0 + threadIdx.x) * JC, m0 + threadIdx.x, a);
+        __syncthreads();
+        const float* src = in + m0 * JC;
+        const float* gsrc = g_out + m0 * JC;
+        float* dst = g_in + m0 * JC;
+        // the upstream gradient of one normalised element (zero where nan_to_zero or a degenerate scale cut it);
+        // r = (x - s_k) / scale through the pose's reciprocal
+        auto upstream = [&](float x, float g, float sk, float inv, float rs, float& r) {
+            r = (x - sk) * inv;
+            return (fabsf(r) <= FMAX) ? g * rs : 0.f;
+        };
+        if (a.autonormalize) {
+            for (int pose = warp; pose < np; pose += RTH / 32) {   // sums over the joints of a pose: one warp each
+                PoseConst<DIM>& c = cs[pose];
+                const float inv = c.inv, rs = c.ok ? c.rs : 0.f;
+                float sg[DIM], sgn = 0.f;
+#pragma unroll
+                for (int k = 0; k < DIM; ++k) sg[k] = 0.f;
+                for (int e = lane; e < JC; e += 32) {
+                    const int k = e % DIM;
+                    float r;
+                    const float gy = upstream(__ldg(src + pose * JC + e), __ldg(gsrc + pose * JC + e),
+                                              pick<DIM>(c.s, k), inv, rs, r);
+#pragma unroll
+                    for (int kk = 0; kk < DIM; ++kk) sg[kk] += (kk == k) ? gy : 0.f;
+                    sgn = fmaf(gy, nan_to_zero(r), sgn);
+                }
+#pragma unroll
+                for (int k = 0; k < DIM; ++k) sg[k] = warp_sum(sg[k]);
+                sgn = warp_sum(sgn);
+                if (lane == 0 && c.ok) {
+                    const float gscale = -sgn * inv;
+#pragma unroll
+                    for (int k = 0; k < DIM; ++k) {
+                        const float un = gscale * c.d[k] * inv;
+                        c.hx[k] = (a.hips == a.neck) ? -sg[k] * inv : -sg[k] * inv - un;
+                        c.kx[k] = (a.hips == a.neck) ? 0.f : un;
+                    }
+                }
+            }
+            __syncthreads();
+        }
+        const int nf = np * JC;
+        const bool vec = ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(gsrc) |
+                           reinterpret_cast<uintptr_t>(dst)) & 15) == 0;
+        const int n4 = vec ? (nf >> 2) : 0;
+        auto value = [&](float x, float g, const PoseConst<DIM>& c, int rem) {
+            if (!a.autonormalize) return g * c.rs;
+            const int joint = rem / DIM, k = rem - joint * DIM;
+            float r;
+            const float gy = upstream(x, g, pick<DIM>(c.s, k), c.inv, c.ok ? c.rs : 0.f, r);
+            float o = gy * c.inv;
+            if (joint == a.hips) o += pick<DIM>(c.hx, k);
+            if (joint == a.neck) o += pick<DIM>(c.kx, k);
+            return o;
+        };
+        for (int i = threadIdx.x; i < n4; i += RTH) {
+            const float4 v = __ldg(reinterpret_cast<const float4*>(src) + i);
+            const float4 w = __ldg(reinterpret_cast<const float4*>(gsrc) + i);
+            const float x[4] = {v.x, v.y, v.z, v.w}, g[4] = {w.x, w.y, w.z, w.w};
+            float r[4];
+            const int pose = (int)(((float)(4 * i) + 0.5f) * inv_jc);
+            int rem = 4 * i - pose * JC;
+            const PoseConst<DIM>& c0 = cs[pose];
+            const PoseConst<DIM>& c1 = cs[min(pose + 1, np - 1)];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const bool nxt = rem >= JC;
+                r[q] = value(x[q], g[q], nxt ? c1 : c0, nxt ? rem - JC : rem);
+                ++rem;
+            }
+            reinterpret_cast<float4*>(dst)[i] = make_float4(r[0], r[1], r[2], r[3]);
+        }
+        for (int e = (n4 << 2) + threadIdx.x; e < nf; e += RTH) {
+            const int pose = e / JC;
+            dst[e] = value(__ldg(src + e), __ldg(gsrc + e), cs[pose], e - pose * JC);
+        }
+        __syncthreads();
+    }
+}
+
+int chunk_grid(long m) {
+    long blocks = (m + RP - 1) / RP;
+    if (blocks > 148L * 32) blocks = 148L * 32;
+    if (blocks < 1) blocks = 1;
+    return (int)blocks;
+}
+
 int warp_grid(long units) {
     long blocks = (units + WARPS - 1) / WARPS;
     if (blocks > 148L * 64) blocks = 148L * 64;
@@ -281,6 +543,16 @@ extern "C" int p2c_cum_changes_fwd(const float* changes, float* cumulative, int3
     const long units = (long)n_clips * n_bones;
     if (units == 0) return 0;  // empty batch: nothing to read or write (pointers of empty tensors are NULL)
     if (!changes || !cumulative) return P2C_E_NULL;
+    const bool aligned = ((reinterpret_cast<uintptr_t>(changes) | reinterpret_cast<uintptr_t>(cumulative)) & 7) == 0;
+    if (aligned && (n_bones * 9) % 2 == 0 && CK * n_bones <= CT && CK * n_bones * 9 / 2 <= CT * CPF) {
+        int ck = CK;   // fewer clips per CTA while the grid would leave SMs idle
+        while (ck > 1 && (n_clips + ck - 1) / ck < 2 * 148) ck >>= 1;
+        const size_t smem = (size_t)ck * n_bones * 9 * sizeof(float);
+        cum_changes_fwd_staged_kernel<<<(unsigned)((n_clips + ck - 1) / ck), CT, smem, (cudaStream_t)stream>>>(
+            changes, cumulative, n_clips, clip_len, n_bones, ck);
+        P2C_LAUNCH_CHECK();
+        return 0;
+    }
     cum_changes_fwd_kernel<<<(unsigned)((units + 127) / 128), 128, 0, (cudaStream_t)stream>>>(changes, cumulative,
                                                                                              units, clip_len, n_bones);
     P2C_LAUNCH_CHECK();
@@ -310,6 +582,14 @@ extern "C" int p2c_renormalize_fwd(const float* sample, float* out, int64_t m, i
     if (rc) return rc;
     if (m == 0) return 0;
     if (!sample || !out) return P2C_E_NULL;
+    if (c == dim) {   // no carried channel: the chunked float4 variant
+        if (dim == 2)
+            renorm_flat_fwd_kernel<2><<<chunk_grid(m), RTH, 0, (cudaStream_t)stream>>>(sample, out, a);
+        else
+            renorm_flat_fwd_kernel<3><<<chunk_grid(m), RTH, 0, (cudaStream_t)stream>>>(sample, out, a);
+        P2C_LAUNCH_CHECK();
+        return 0;
+    }
     if (dim == 2)
         renorm_fwd_kernel<2><<<warp_grid(m), WARPS * 32, 0, (cudaStream_t)stream>>>(sample, out, a);
     else
@@ -329,6 +609,15 @@ extern "C" int p2c_renormalize_bwd(const float* sample, const float* g_out, floa
     if (rc) return rc;
     if (m == 0) return 0;
     if (!sample || !g_out || !g_sample) return P2C_E_NULL;
+    if (c == dim) {
+        a.ref_shift = nullptr;   // the shift does not enter the gradient
+        if (dim == 2)
+            renorm_flat_bwd_kernel<2><<<chunk_grid(m), RTH, 0, (cudaStream_t)stream>>>(sample, g_out, g_sample, a);
+        else
+            renorm_flat_bwd_kernel<3><<<chunk_grid(m), RTH, 0, (cudaStream_t)stream>>>(sample, g_out, g_sample, a);
+        P2C_LAUNCH_CHECK();
+        return 0;
+    }
     if (dim == 2)
         renorm_bwd_kernel<2><<<warp_grid(m), WARPS * 32, 0, (cudaStream_t)stream>>>(sample, g_out, g_sample, a);
     else
