@@ -216,6 +216,13 @@ int p2c_renormalize_bwd(const float* sample, const float* g_out, float* g_sample
                         float near_zero, const float* ref_scale, const int32_t* ref_index, int32_t clip_len,
                         void* stream);
 
+/* ---- Normalizer.__call__(sample, dim=2) with BBoxExtractor (extractor 1; bbox_extractor.py:6-18) or
+ *      HipsNeckBBoxFallbackExtractor (extractor 2; hips_neck_bbox_fallback_extractor.py:10-46, the reference's default
+ *      `hips_neck_bbox` transform, base_datamodule.py:61,276).  Forward only: these normalise dataset inputs.
+ *      sample, out (M,J,c), c 2 or 3 (channel 2 = confidence, carried; xy zeroed where it is < near_zero).      */
+int p2c_normalize_extractor_fwd(const float* sample, float* out, int64_t m, int32_t j, int32_t c,
+                                int32_t hips, int32_t neck, int32_t extractor, float near_zero, void* stream);
+
 /* ---- Evaluation metrics on the step's output buffers: MPJPE (metrics/mpjpe.py:29-45), MRPE (metrics/mrpe.py:38-76),
  *      PCK (metrics/pck.py:54-97 with utils/tensors.py:12-40).  pred / gt (M,J,c).  `partials`: caller-owned workspace
  *      of p2c_metric_workspace_floats() floats; `out`: two DOUBLES on the device, (sum of distances, number of

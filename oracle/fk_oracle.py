@@ -24,7 +24,7 @@ __all__ = [
     'projection_module_forward', 'hips_neck_normalize', 'missing_joints_mask', 'loss_loc_2d',
     'loss_loc_3d', 'loss_loc_2d_3d', 'full_step', 'HIPS', 'NECK',
     'normalize', 'get_shift_scale', 'denormalize', 'reference_denormalize', 'cumulative_changes', 'loss_rot_3d',
-    'quaternion_to_matrix', 'metric_mpjpe', 'metric_mrpe', 'metric_pck', 'get_bboxes', 'loss_cum_pose_changes', 'loss_pose_changes', 'loss_weighted_loc_2d_loc_rot_3d', 'abs_from_abs_loc',
+    'quaternion_to_matrix', 'normalize_with_extractor', 'metric_mpjpe', 'metric_mrpe', 'metric_pck', 'get_bboxes', 'loss_cum_pose_changes', 'loss_pose_changes', 'loss_weighted_loc_2d_loc_rot_3d', 'abs_from_abs_loc',
 ]
 
 FILES_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), '..',
@@ -527,3 +527,38 @@ def metric_pck(pred, gt, gt_projection_2d=None, norm='bbox', threshold=0.05, mas
     normalize = normalize[(slice(None),) * normalize.ndim + (None,) * (pred.ndim - normalize.ndim)]
     dist = torch.linalg.norm((pred - gt) / normalize, dim=-1, ord=2)
     return int(torch.sum(dist[mask] < threshold)), int(dist[mask].numel())
+
+
+def normalize_with_extractor(sample, extractor='hips_neck_bbox', hips=HIPS, neck=NECK, near_zero=1e-5):
+    """Normalizer (normalizer.py:20-41, dim=2) with BBoxExtractor (bbox_extractor.py:6-18) or
+    HipsNeckBBoxFallbackExtractor (hips_neck_bbox_fallback_extractor.py:21-46)."""
+    xy = sample[..., 0:2]
+    boxes = get_bboxes(xy, near_zero)
+    bb_shift = boxes.mean(dim=-2)
+    bb_scale_pt = torch.stack((boxes.mean(dim=-2)[..., 0], boxes.min(dim=-2)[0][..., 1]), dim=-1)
+    bb_scale = torch.linalg.norm(bb_scale_pt - bb_shift, dim=bb_shift.ndim - 1, ord=2)
+    if extractor == 'bbox':
+        shift, scale = bb_shift, bb_scale
+    else:
+        hn_shift = xy[..., (hips,), :].mean(dim=-2)
+        hn_neck = xy[..., (neck,), :].mean(dim=-2)
+        hn_scale = torch.linalg.norm(hn_neck - hn_shift, dim=hn_shift.ndim - 1, ord=2)
+        missing_hips = torch.all(hn_shift < near_zero, dim=-1)
+        shift = hn_shift.clone()
+        if torch.any(missing_hips):      # :27-31: chained indexing assigns into a copy -- no effect on `shift`
+            shift[missing_hips][:, 0] = bb_shift[missing_hips][:, 0] + bb_scale[missing_hips] * 0.0
+            shift[missing_hips][:, 1] = bb_shift[missing_hips][:, 1] + bb_scale[missing_hips] * -0.1059
+        missing_neck = torch.all(hn_neck < near_zero, dim=-1)
+        scale = hn_scale.clone()
+        if torch.any(missing_hips):
+            scale[missing_hips] = bb_scale[missing_hips] * 0.5748
+        if torch.any(missing_neck):
+            scale[missing_neck] = bb_scale[missing_neck] * 0.5748
+    out = torch.empty_like(sample)
+    out[..., 0:2] = (xy - torch.unsqueeze(shift, -2)) / scale[(...,) + (None,) * 2]
+    if sample.shape[-1] > 2:
+        out[..., 2] = sample[..., 2]
+    out = torch.nan_to_num(out, nan=0, posinf=0, neginf=0)
+    if out.shape[-1] > 2:
+        out[..., 0:2] = out[..., 0:2].where(out[..., 2:] >= near_zero, torch.tensor(0.0, dtype=out.dtype))
+    return out

@@ -79,6 +79,8 @@ _SIGS = {
                                       C.c_int32, C.c_float, _P, _P, _P, C.c_int32, _P]),
     'p2c_renormalize_bwd': (C.c_int, [_P, _P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                                       C.c_int32, C.c_float, _P, _P, C.c_int32, _P]),
+    'p2c_normalize_extractor_fwd': (C.c_int, [_P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
+                                              C.c_int32, C.c_float, _P]),
     'p2c_metric_workspace_floats': (C.c_int64, []),
     'p2c_mpjpe_sum': (C.c_int, [_P, _P, C.c_int64, C.c_int32, C.c_int32, _P, _P, C.c_int32, _P]),
     'p2c_mrpe_sum': (C.c_int, [_P, _P, _P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, _P, _P, C.c_int32, _P]),

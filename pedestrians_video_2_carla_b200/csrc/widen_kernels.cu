@@ -51,24 +51,25 @@ __global__ void __launch_bounds__(CT) cum_changes_fwd_staged_kernel(const float*
     const int k = threadIdx.x / B, b = threadIdx.x - k * B;
     const bool worker = threadIdx.x < nk * B;
     float2 pre[CPF];
+    long base[CPF];   // float offset of this thread's r-th float2 in frame 0 (the frame adds t * B * 9): no per-frame division
+#pragma unroll
+    for (int r = 0; r < CPF; ++r) {
+        const int i = threadIdx.x + r * CT;
+        const int kk = i / row2, w = i - kk * row2;
+        base[r] = (i < total2) ? (long)(n0 + kk) * L * B * 9 + 2 * w : -1;
+    }
+    const int frame = B * 9;
     auto fetch = [&](int t) {
 #pragma unroll
-        for (int r = 0; r < CPF; ++r) {
-            const int i = threadIdx.x + r * CT;
-            if (i < total2) {
-                const int kk = i / row2, w = i - kk * row2;
-                pre[r] = __ldg(reinterpret_cast<const float2*>(c + ((long)(n0 + kk) * L + t) * B * 9) + w);
-            }
-        }
+        for (int r = 0; r < CPF; ++r)
+            if (base[r] >= 0) pre[r] = __ldg(reinterpret_cast<const float2*>(c + base[r] + (long)t * frame));
     };
     M3 p = m3_identity();
     fetch(0);
     for (int t = 0; t < L; ++t) {
 #pragma unroll
-        for (int r = 0; r < CPF; ++r) {
-            const int i = threadIdx.x + r * CT;
-            if (i < total2) tile2[i] = pre[r];
-        }
+        for (int r = 0; r < CPF; ++r)
+            if (base[r] >= 0) tile2[threadIdx.x + r * CT] = pre[r];
         __syncthreads();
         if (t + 1 < L) fetch(t + 1);
         if (worker) {
@@ -78,13 +79,9 @@ __global__ void __launch_bounds__(CT) cum_changes_fwd_staged_kernel(const float*
         }
         __syncthreads();
 #pragma unroll
-        for (int r = 0; r < CPF; ++r) {
-            const int i = threadIdx.x + r * CT;
-            if (i < total2) {
-                const int kk = i / row2, w = i - kk * row2;
-                reinterpret_cast<float2*>(out + ((long)(n0 + kk) * L + t) * B * 9)[w] = tile2[i];
-            }
-        }
+        for (int r = 0; r < CPF; ++r)
+            if (base[r] >= 0)
+                *reinterpret_cast<float2*>(out + base[r] + (long)t * frame) = tile2[threadIdx.x + r * CT];
         __syncthreads();
     }
 }
@@ -515,6 +512,64 @@ int chunk_grid(long m) {
     return (int)blocks;
 }
 
+// ---- Normalizer with the BBoxExtractor / HipsNeckBBoxFallbackExtractor (bbox_extractor.py:6-18,
+//      hips_neck_bbox_fallback_extractor.py:10-46; utils/tensors.py:12-26) -- forward only: these normalise dataset
+//      INPUTS (`hips_neck_bbox` is the reference's default CLI transform, base_datamodule.py:61,276).
+//      extractor 1: shift = centre of the box around the detected points, scale = |y_min - y_centre|;
+//      extractor 2: hips / neck as usual, but scale = 0.5748 * the box scale when hips or neck are undetected
+//      (the reference's fallback SHIFT is written into a temporary and has no effect, :27-31 -- reproduced).
+__global__ void __launch_bounds__(WARPS * 32) normalize_extractor_kernel(const float* __restrict__ in,
+                                                                        float* __restrict__ out, long M, int J, int C,
+                                                                        int hips, int neck, int extractor,
+                                                                        float near_zero) {
+    const int lane = threadIdx.x & 31;
+    const float inf = __builtin_huge_valf();
+    const long wstride = (long)gridDim.x * WARPS;
+    for (long m = (long)blockIdx.x * WARPS + (threadIdx.x >> 5); m < M; m += wstride) {
+        const float* p = in + m * J * C;
+        float* o = out + m * J * C;
+        float lox = inf, loy = inf, hix = -inf, hiy = -inf;
+        for (int j = lane; j < J; j += 32) {
+            const float x = p[j * C], y = p[j * C + 1];
+            if (!(x < near_zero && y < near_zero)) {   // detected
+                lox = fminf(lox, x); hix = fmaxf(hix, x);
+                loy = fminf(loy, y); hiy = fmaxf(hiy, y);
+            }
+        }
+        for (int s = 16; s > 0; s >>= 1) {
+            lox = fminf(lox, __shfl_xor_sync(FULL_MASK, lox, s)); hix = fmaxf(hix, __shfl_xor_sync(FULL_MASK, hix, s));
+            loy = fminf(loy, __shfl_xor_sync(FULL_MASK, loy, s)); hiy = fmaxf(hiy, __shfl_xor_sync(FULL_MASK, hiy, s));
+        }
+        const float cx = (lox + hix) / 2.f, cy = (loy + hiy) / 2.f;
+        // |(cx, y_min) - (cx, cy)|_2 as torch.linalg.norm forms it
+        const float ddx = cx - cx, ddy = loy - cy;
+        const float bb_scale = sqrtf(ddx * ddx + ddy * ddy);
+        float sx, sy, scale;
+        if (extractor == 1) {
+            sx = cx; sy = cy; scale = bb_scale;
+        } else {
+            const float hx = __ldg(p + hips * C), hy = __ldg(p + hips * C + 1);
+            const float nx = __ldg(p + neck * C), ny = __ldg(p + neck * C + 1);
+            sx = hx; sy = hy;
+            scale = sqrtf((nx - hx) * (nx - hx) + (ny - hy) * (ny - hy));
+            const bool missing_hips = hx < near_zero && hy < near_zero;
+            const bool missing_neck = nx < near_zero && ny < near_zero;
+            if (missing_hips || missing_neck) scale = bb_scale * 0.5748f;
+        }
+        for (int j = lane; j < J; j += 32) {
+            float nx = nan_to_zero((p[j * C] - sx) / scale);
+            float ny = nan_to_zero((p[j * C + 1] - sy) / scale);
+            if (C > 2) {
+                const float q = nan_to_zero(p[j * C + 2]);
+                if (!(q >= near_zero)) { nx = 0.f; ny = 0.f; }
+                o[j * C + 2] = q;
+            }
+            o[j * C] = nx;
+            o[j * C + 1] = ny;
+        }
+    }
+}
+
 int warp_grid(long units) {
     long blocks = (units + WARPS - 1) / WARPS;
     if (blocks > 148L * 64) blocks = 148L * 64;
@@ -643,6 +698,19 @@ extern "C" int p2c_quaternion_to_matrix_bwd(const float* quat, const float* g_ou
     if (!quat || !g_out || !g_quat) return P2C_E_NULL;
     if ((reinterpret_cast<uintptr_t>(quat) | reinterpret_cast<uintptr_t>(g_quat)) & 15) return P2C_E_UNSUPPORTED;
     quat_bwd_kernel<<<(unsigned)((n + QT - 1) / QT), QT, 0, (cudaStream_t)stream>>>(quat, g_out, g_quat, (long)n);
+    P2C_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int p2c_normalize_extractor_fwd(const float* sample, float* out, int64_t m, int32_t j, int32_t c,
+                                           int32_t hips, int32_t neck, int32_t extractor, float near_zero,
+                                           void* stream) {
+    if (m < 0 || j < 1 || (c != 2 && c != 3) || (extractor != 1 && extractor != 2)) return P2C_E_BADARG;
+    if (hips < 0 || hips >= j || neck < 0 || neck >= j) return P2C_E_BADARG;
+    if (m == 0) return 0;
+    if (!sample || !out) return P2C_E_NULL;
+    normalize_extractor_kernel<<<warp_grid(m), WARPS * 32, 0, (cudaStream_t)stream>>>(sample, out, (long)m, j, c, hips,
+                                                                                   neck, extractor, near_zero);
     P2C_LAUNCH_CHECK();
     return 0;
 }

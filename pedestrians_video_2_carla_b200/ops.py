@@ -275,6 +275,17 @@ def hips_neck_normalize(sample, hips, neck, near_zero=1e-5):
     return _HipsNeckNormalize.apply(sample, hips, neck, near_zero)
 
 
+def normalize_extractor(sample, hips, neck, extractor, near_zero=1e-5):
+    """Normalizer(BBoxExtractor) (extractor 1) / Normalizer(HipsNeckBBoxFallbackExtractor) (extractor 2) over
+    (..., J, 2|3) samples; forward only (dataset inputs carry no gradient)."""
+    s = _f32c(sample.detach(), 'sample')
+    out = torch.empty_like(s)
+    j, c = s.shape[-2], s.shape[-1]
+    check(_lib.load().p2c_normalize_extractor_fwd(ptr(s), ptr(out), s.numel() // (j * c), j, c, hips, neck, extractor,
+                                                  near_zero, stream()), 'normalize_extractor_fwd')
+    return out
+
+
 class _MaskedMSE(torch.autograd.Function):
     """nn.MSELoss('mean') over [..., :c_used] of the joints kept by utils/tensors.py:29-40."""
 

@@ -13,6 +13,11 @@ class Normalizer(object):
         return '%s(extractor=%s)' % (self.__class__.__name__, self.extractor.__class__.__name__)
 
     def __call__(self, sample, dim=2, *args, **kwargs):
+        kind = getattr(self.extractor, 'kind', 0)
+        if kind:   # bbox / hips_neck_bbox: dataset-input transforms, forward only
+            if dim != 2:
+                raise NotImplementedError('the bounding-box extractors are 2-D (bbox_extractor.py:12-18)')
+            return ops.normalize_extractor(sample, self.extractor.hips, self.extractor.neck, kind, self._near_zero)
         if dim == 2 and sample.shape[-1] in (2, 3):
             return ops.hips_neck_normalize(sample, self.extractor.hips, self.extractor.neck, self._near_zero)
         if dim == 3 and sample.shape[-1] == 3 and sample.dim() >= 3:   # absolute locations (denormaliser entry)

@@ -165,6 +165,22 @@ def main():
         m.update(preds, tgts)
         out['metric/pck_' + name] = torch.stack((m.correct.double(), m.total.double(), m.compute().double()))
 
+    # -- 5. Normalizer with the bbox / hips_neck_bbox extractors (dataset-input transforms, base_datamodule.py:61,276)
+    from pedestrians_video_2_carla.transforms.pose.normalization.bbox_extractor import BBoxExtractor
+    from pedestrians_video_2_carla.transforms.pose.normalization.hips_neck_bbox_fallback_extractor import \
+        HipsNeckBBoxFallbackExtractor
+    xin = tproj.detach().clone()
+    xin[..., 2] = torch.rand((N, L, 26), generator=g)              # confidences
+    undetected = torch.rand((N, L, 26), generator=g) < 0.15
+    xin[undetected] = 0.0
+    xin[0, 0, CARLA_SKELETON.crl_hips__C.value] = 0.0               # undetected hips -> fallback scale
+    xin[0, 1, CARLA_SKELETON.crl_neck__C.value] = 0.0               # undetected neck -> fallback scale
+    xin[2, 3] = 0.0                                                 # nothing detected at all
+    out['ext/x'] = xin
+    out['ext/bbox'] = Normalizer(BBoxExtractor(CARLA_SKELETON))(xin)
+    out['ext/hips_neck_bbox'] = Normalizer(HipsNeckBBoxFallbackExtractor(CARLA_SKELETON))(xin)
+    out['ext/hips_neck_bbox_2ch'] = Normalizer(HipsNeckBBoxFallbackExtractor(CARLA_SKELETON))(xin[..., :2].contiguous())
+
     skel_id = [ref.CARLA_REFERENCE_SKELETON_TYPES.index((a, s)) for a, s in zip(ages, genders)]
     arrays = {k: v.detach().numpy() for k, v in out.items()}
     arrays['skeleton_id'] = np.asarray(skel_id, dtype=np.int32)

@@ -324,3 +324,20 @@ def test_metrics_large_batch_against_oracle():
     p.update({'projection_2d': p2.float().to(DEV)}, {'projection_2d': g2.float().to(DEV)})
     assert float(p.state[1]) == total
     assert abs(float(p.state[0]) - correct) <= 3
+
+
+def test_bbox_extractors_against_reference_golden(api, gold):
+    """Normalizer(BBoxExtractor) and Normalizer(HipsNeckBBoxFallbackExtractor) (the reference's default
+    `hips_neck_bbox` transform) incl. undetected hips / neck / whole frames."""
+    from pedestrians_video_2_carla_b200.transforms.pose.normalization.bbox_extractor import BBoxExtractor
+    from pedestrians_video_2_carla_b200.transforms.pose.normalization.hips_neck_bbox_fallback_extractor import \
+        HipsNeckBBoxFallbackExtractor
+    x = gold['ext/x'].to(DEV)
+    N = api['Normalizer']
+    assert_close('bbox', N(BBoxExtractor())(x), gold['ext/bbox'])
+    assert_close('hips_neck_bbox', N(HipsNeckBBoxFallbackExtractor())(x), gold['ext/hips_neck_bbox'])
+    assert_close('hips_neck_bbox 2ch', N(HipsNeckBBoxFallbackExtractor())(x[..., :2].contiguous()),
+                 gold['ext/hips_neck_bbox_2ch'])
+    # with hips and neck detected everywhere it equals the plain hips/neck normaliser (SURVEY 8a row a11)
+    y = gold['den/x2'].to(DEV)
+    assert_close('== hips_neck', N(HipsNeckBBoxFallbackExtractor())(y), N()(y), 1e-6)

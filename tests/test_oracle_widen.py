@@ -121,3 +121,11 @@ def test_metrics_against_reference_golden(gold):
         correct, total = O.metric_pck(*args)
         want = gold['metric/pck_' + name]
         assert (correct, total) == (int(want[0]), int(want[1])), name
+
+
+def test_bbox_extractors_against_reference_golden(gold):
+    x = gold['ext/x']
+    assert_close('bbox', O.normalize_with_extractor(x, 'bbox'), gold['ext/bbox'], 1e-6)
+    assert_close('hips_neck_bbox', O.normalize_with_extractor(x, 'hips_neck_bbox'), gold['ext/hips_neck_bbox'], 1e-6)
+    assert_close('hips_neck_bbox 2ch', O.normalize_with_extractor(x[..., :2].contiguous(), 'hips_neck_bbox'),
+                 gold['ext/hips_neck_bbox_2ch'], 1e-6)
