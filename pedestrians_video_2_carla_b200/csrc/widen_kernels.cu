@@ -105,6 +105,71 @@ __global__ void __launch_bounds__(128) cum_changes_bwd_kernel(const float* __res
     }
 }
 
+
+// Staged backward: the same CTA / row mapping as the staged forward, three input tiles per frame (C[t], g_out[t],
+// P[t-1]), walking the frames backwards; g_C[t] replaces g_out[t] in its tile and leaves as coalesced float2.
+__global__ void __launch_bounds__(CT) cum_changes_bwd_staged_kernel(const float* __restrict__ c,
+                                                                   const float* __restrict__ cum,
+                                                                   const float* __restrict__ g_out,
+                                                                   float* __restrict__ g_c, int N, int L, int B,
+                                                                   int ck) {
+    extern __shared__ float2 tile2[];                 // 3 tiles of ck * row2 float2
+    const int row2 = B * 9 / 2;
+    const int n0 = blockIdx.x * ck;
+    const int nk = min(ck, N - n0);
+    const int total2 = nk * row2;
+    float2* t_c = tile2;
+    float2* t_g = tile2 + ck * row2;
+    float2* t_p = tile2 + 2 * ck * row2;
+    const int k = threadIdx.x / B, b = threadIdx.x - k * B;
+    const bool worker = threadIdx.x < nk * B;
+    float2 pc[CPF], pg[CPF], pp[CPF];
+    long base[CPF];
+#pragma unroll
+    for (int r = 0; r < CPF; ++r) {
+        const int i = threadIdx.x + r * CT;
+        const int kk = i / row2, w = i - kk * row2;
+        base[r] = (i < total2) ? (long)(n0 + kk) * L * B * 9 + 2 * w : -1;
+    }
+    const int frame = B * 9;
+    auto fetch = [&](int t) {
+#pragma unroll
+        for (int r = 0; r < CPF; ++r)
+            if (base[r] >= 0) {
+                const long e = base[r] + (long)t * frame;
+                pc[r] = __ldg(reinterpret_cast<const float2*>(c + e));
+                pg[r] = __ldg(reinterpret_cast<const float2*>(g_out + e));
+                if (t > 0) pp[r] = __ldg(reinterpret_cast<const float2*>(cum + e - frame));
+            }
+    };
+    M3 g = m3_zero();
+    fetch(L - 1);
+    for (int t = L - 1; t >= 0; --t) {
+#pragma unroll
+        for (int r = 0; r < CPF; ++r)
+            if (base[r] >= 0) {
+                const int i = threadIdx.x + r * CT;
+                t_c[i] = pc[r]; t_g[i] = pg[r]; t_p[i] = pp[r];
+            }
+        __syncthreads();
+        if (t > 0) fetch(t - 1);
+        if (worker) {
+            const int o = (k * B + b) * 9;
+            float* mg = reinterpret_cast<float*>(t_g) + o;
+            m3_acc(g, m3_from(mg));
+            const M3 prev = (t > 0) ? m3_from(reinterpret_cast<const float*>(t_p) + o) : m3_identity();
+            m3_to(mg, m3_mul_at(prev, g));
+            g = m3_mul_bt(g, m3_from(reinterpret_cast<const float*>(t_c) + o));
+        }
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < CPF; ++r)
+            if (base[r] >= 0)
+                *reinterpret_cast<float2*>(g_c + base[r] + (long)t * frame) = t_g[threadIdx.x + r * CT];
+        __syncthreads();
+    }
+}
+
 // ---- Normalizer (optional) followed by DeNormalizer.from_reference (optional) ------------------
 // one warp per pose, lanes stride over joints.  DIM = channels that are shifted and scaled (2: projections, 3:
 // absolute locations); C = channels per joint (DIM, or 3 with DIM 2: channel 2 is carried through).
@@ -621,6 +686,17 @@ extern "C" int p2c_cum_changes_bwd(const float* changes, const float* cumulative
     const long units = (long)n_clips * n_bones;
     if (units == 0) return 0;
     if (!changes || !cumulative || !g_cumulative || !g_changes) return P2C_E_NULL;
+    const bool aligned = ((reinterpret_cast<uintptr_t>(changes) | reinterpret_cast<uintptr_t>(cumulative) |
+                           reinterpret_cast<uintptr_t>(g_cumulative) | reinterpret_cast<uintptr_t>(g_changes)) & 7) == 0;
+    if (aligned && (n_bones * 9) % 2 == 0 && CK * n_bones <= CT && CK * n_bones * 9 / 2 <= CT * CPF) {
+        int ck = CK;
+        while (ck > 1 && (n_clips + ck - 1) / ck < 2 * 148) ck >>= 1;
+        const size_t smem = (size_t)3 * ck * n_bones * 9 * sizeof(float);
+        cum_changes_bwd_staged_kernel<<<(unsigned)((n_clips + ck - 1) / ck), CT, smem, (cudaStream_t)stream>>>(
+            changes, cumulative, g_cumulative, g_changes, n_clips, clip_len, n_bones, ck);
+        P2C_LAUNCH_CHECK();
+        return 0;
+    }
     cum_changes_bwd_kernel<<<(unsigned)((units + 127) / 128), 128, 0, (cudaStream_t)stream>>>(
         changes, cumulative, g_cumulative, g_changes, units, clip_len, n_bones);
     P2C_LAUNCH_CHECK();
