@@ -36,7 +36,26 @@ __global__ void __launch_bounds__(WARPS * 32) metric_partial_kernel(MetricArgs a
     float s0 = 0.f, s1 = 0.f;  // (sum, count) or (correct, total)
     if (a.kind == 0) {  // MPJPE has no per-pose structure: a flat grid-stride loop over joints
         const long total = a.M * a.J;
-        for (long i = (long)blockIdx.x * (WARPS * 32) + threadIdx.x; i < total; i += (long)gridDim.x * (WARPS * 32)) {
+        const long tid = (long)blockIdx.x * (WARPS * 32) + threadIdx.x, nthreads = (long)gridDim.x * (WARPS * 32);
+        long done = 0;
+        if (C == 3 && ((reinterpret_cast<uintptr_t>(a.pred) | reinterpret_cast<uintptr_t>(a.gt)) & 15) == 0) {
+            // four joints = 48 bytes = three float4 per operand and thread: six 16-byte loads in flight per thread
+            const long groups = total >> 2;
+            const float4* p4 = reinterpret_cast<const float4*>(a.pred);
+            const float4* g4 = reinterpret_cast<const float4*>(a.gt);
+            for (long i = tid; i < groups; i += nthreads) {
+                const float4 p0 = __ldg(p4 + 3 * i), p1 = __ldg(p4 + 3 * i + 1), p2 = __ldg(p4 + 3 * i + 2);
+                const float4 g0 = __ldg(g4 + 3 * i), g1 = __ldg(g4 + 3 * i + 1), g2 = __ldg(g4 + 3 * i + 2);
+                const float d[12] = {p0.x - g0.x, p0.y - g0.y, p0.z - g0.z, p0.w - g0.w, p1.x - g1.x, p1.y - g1.y,
+                                     p1.z - g1.z, p1.w - g1.w, p2.x - g2.x, p2.y - g2.y, p2.z - g2.z, p2.w - g2.w};
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    s0 += sqrtf(fmaf(d[3 * j + 2], d[3 * j + 2], fmaf(d[3 * j + 1], d[3 * j + 1], d[3 * j] * d[3 * j])));
+                s1 += 4.f;
+            }
+            done = groups << 2;
+        }
+        for (long i = done + tid; i < total; i += nthreads) {
             float q = 0.f;
             for (int c = 0; c < C; ++c) { const float d = __ldg(a.pred + i * C + c) - __ldg(a.gt + i * C + c); q = fmaf(d, d, q); }
             s0 += sqrtf(q);

@@ -399,8 +399,8 @@ __device__ __forceinline__ void pose_consts(PoseConst<DIM>& c, const float* p, l
     for (int k = 0; k < DIM; ++k) {
         c.s[k] = 0.f; c.rh[k] = 0.f; c.d[k] = 0.f; c.hx[k] = 0.f; c.kx[k] = 0.f;
         if (a.autonormalize) {
-            c.s[k] = __ldg(p + a.hips * DIM + k);
-            c.d[k] = __ldg(p + a.neck * DIM + k) - c.s[k];
+            c.s[k] = p[a.hips * DIM + k];      // plain loads: p may point into shared memory
+            c.d[k] = p[a.neck * DIM + k] - c.s[k];
             q = fmaf(c.d[k], c.d[k], q);
         }
     }
@@ -453,19 +453,24 @@ __global__ void __launch_bounds__(RTH) renorm_flat_fwd_kernel(const float* __res
             const float4 v = __ldg(reinterpret_cast<const float4*>(src) + i);
             float r[4] = {v.x, v.y, v.z, v.w};
             // floor(e / JC) through the reciprocal: exact, the quotient is >= 0.5 / JC away from an integer boundary
-            const int pose = (int)(((float)(4 * i) + 0.5f) * inv_jc);
+            int pose = (int)(((float)(4 * i) + 0.5f) * inv_jc);
             int rem = 4 * i - pose * JC;
-            const PoseConst<DIM>& c0 = cs[pose];
-            const PoseConst<DIM>& c1 = cs[min(pose + 1, np - 1)];   // a float4 straddles at most one pose boundary
             int k = rem % DIM;
+            // the pose's constants in registers, reloaded only where the float4 crosses into the next pose
+            float A = cs[pose].A, bk[DIM], rh[DIM];
+#pragma unroll
+            for (int d = 0; d < DIM; ++d) { bk[d] = cs[pose].bk[d]; rh[d] = cs[pose].rh[d]; }
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
-                const bool nxt = rem >= JC;
-                const PoseConst<DIM>& c = nxt ? c1 : c0;
-                const int kk = nxt ? (rem - JC) % DIM : k;
-                r[q] = value(r[q], c.A, pick<DIM>(c.bk, kk), pick<DIM>(c.rh, kk));
-                ++rem;
+                r[q] = value(r[q], A, pick<DIM>(bk, k), pick<DIM>(rh, k));
                 k = (k + 1 == DIM) ? 0 : k + 1;
+                if (++rem == JC) {
+                    rem = 0;
+                    pose = min(pose + 1, np - 1);
+                    A = cs[pose].A;
+#pragma unroll
+                    for (int d = 0; d < DIM; ++d) { bk[d] = cs[pose].bk[d]; rh[d] = cs[pose].rh[d]; }
+                }
             }
             reinterpret_cast<float4*>(dst)[i] = make_float4(r[0], r[1], r[2], r[3]);
         }
@@ -478,22 +483,38 @@ __global__ void __launch_bounds__(RTH) renorm_flat_fwd_kernel(const float* __res
     }
 }
 
+// Backward: the chunk's x and g rows are staged in shared memory by ONE coalesced float4 pass (all loads of a thread
+// in flight together); the per-pose sums over joints and the output pass then read shared memory.  (The first version
+// re-read global memory in a warp-per-pose reduction: eight dependent load / shuffle rounds per warp and chunk.)
 template <int DIM>
 __global__ void __launch_bounds__(RTH) renorm_flat_bwd_kernel(const float* __restrict__ in,
                                                              const float* __restrict__ g_out,
                                                              float* __restrict__ g_in, Renorm a) {
     __shared__ PoseConst<DIM> cs[RP];
+    extern __shared__ __align__(16) float stage[];    // x rows, then g rows: 2 * RP * JC floats
     const int JC = a.J * DIM;
+    float* sx = stage;
+    float* sg_ = stage + RP * JC;
     const float inv_jc = 1.0f / (float)JC;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (long chunk = blockIdx.x; chunk * RP < a.M; chunk += gridDim.x) {
         const long m0 = chunk * RP;
         const int np = (int)min((long)RP, a.M - m0);
-        if (threadIdx.x < np) pose_consts<DIM>(cs[threadIdx.x], in + (m0 + threadIdx.x) * JC, m0 + threadIdx.x, a);
-        __syncthreads();
         const float* src = in + m0 * JC;
         const float* gsrc = g_out + m0 * JC;
         float* dst = g_in + m0 * JC;
+        const int nf = np * JC;
+        const bool vec = ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(gsrc) |
+                           reinterpret_cast<uintptr_t>(dst)) & 15) == 0 && ((RP * JC) & 3) == 0;
+        const int n4 = vec ? (nf >> 2) : 0;
+        for (int i = threadIdx.x; i < n4; i += RTH) {
+            reinterpret_cast<float4*>(sx)[i] = __ldg(reinterpret_cast<const float4*>(src) + i);
+            reinterpret_cast<float4*>(sg_)[i] = __ldg(reinterpret_cast<const float4*>(gsrc) + i);
+        }
+        for (int e = (n4 << 2) + threadIdx.x; e < nf; e += RTH) { sx[e] = __ldg(src + e); sg_[e] = __ldg(gsrc + e); }
+        __syncthreads();
+        if (threadIdx.x < np) pose_consts<DIM>(cs[threadIdx.x], sx + threadIdx.x * JC, m0 + threadIdx.x, a);
+        __syncthreads();
         // the upstream gradient of one normalised element (zero where nan_to_zero or a degenerate scale cut it);
         // r = (x - s_k) / scale through the pose's reciprocal
         auto upstream = [&](float x, float g, float sk, float inv, float rs, float& r) {
@@ -510,8 +531,7 @@ __global__ void __launch_bounds__(RTH) renorm_flat_bwd_kernel(const float* __res
                 for (int e = lane; e < JC; e += 32) {
                     const int k = e % DIM;
                     float r;
-                    const float gy = upstream(__ldg(src + pose * JC + e), __ldg(gsrc + pose * JC + e),
-                                              pick<DIM>(c.s, k), inv, rs, r);
+                    const float gy = upstream(sx[pose * JC + e], sg_[pose * JC + e], pick<DIM>(c.s, k), inv, rs, r);
 #pragma unroll
                     for (int kk = 0; kk < DIM; ++kk) sg[kk] += (kk == k) ? gy : 0.f;
                     sgn = fmaf(gy, nan_to_zero(r), sgn);
@@ -531,40 +551,50 @@ __global__ void __launch_bounds__(RTH) renorm_flat_bwd_kernel(const float* __res
             }
             __syncthreads();
         }
-        const int nf = np * JC;
-        const bool vec = ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(gsrc) |
-                           reinterpret_cast<uintptr_t>(dst)) & 15) == 0;
-        const int n4 = vec ? (nf >> 2) : 0;
-        auto value = [&](float x, float g, const PoseConst<DIM>& c, int rem) {
-            if (!a.autonormalize) return g * c.rs;
-            const int joint = rem / DIM, k = rem - joint * DIM;
+        // output pass: the pose's constants live in registers and are reloaded only where a float4 crosses into the
+        // next pose; channel and joint of an element advance incrementally (no division per element)
+        struct PoseReg { float s[DIM], hx[DIM], kx[DIM], inv, rs; };
+        auto load_reg = [&](PoseReg& q, int pose) {
+            const PoseConst<DIM>& c = cs[pose];
+#pragma unroll
+            for (int k = 0; k < DIM; ++k) { q.s[k] = c.s[k]; q.hx[k] = c.hx[k]; q.kx[k] = c.kx[k]; }
+            q.inv = c.inv;
+            q.rs = (a.autonormalize && !c.ok) ? 0.f : c.rs;
+        };
+        auto value = [&](float x, float g, const PoseReg& q, int joint, int k) {
+            if (!a.autonormalize) return g * q.rs;
             float r;
-            const float gy = upstream(x, g, pick<DIM>(c.s, k), c.inv, c.ok ? c.rs : 0.f, r);
-            float o = gy * c.inv;
-            if (joint == a.hips) o += pick<DIM>(c.hx, k);
-            if (joint == a.neck) o += pick<DIM>(c.kx, k);
+            const float gy = upstream(x, g, pick<DIM>(q.s, k), q.inv, q.rs, r);
+            float o = gy * q.inv;
+            if (joint == a.hips) o += pick<DIM>(q.hx, k);
+            if (joint == a.neck) o += pick<DIM>(q.kx, k);
             return o;
         };
         for (int i = threadIdx.x; i < n4; i += RTH) {
-            const float4 v = __ldg(reinterpret_cast<const float4*>(src) + i);
-            const float4 w = __ldg(reinterpret_cast<const float4*>(gsrc) + i);
+            const float4 v = reinterpret_cast<const float4*>(sx)[i];
+            const float4 w = reinterpret_cast<const float4*>(sg_)[i];
             const float x[4] = {v.x, v.y, v.z, v.w}, g[4] = {w.x, w.y, w.z, w.w};
             float r[4];
-            const int pose = (int)(((float)(4 * i) + 0.5f) * inv_jc);
-            int rem = 4 * i - pose * JC;
-            const PoseConst<DIM>& c0 = cs[pose];
-            const PoseConst<DIM>& c1 = cs[min(pose + 1, np - 1)];
+            int pose = (int)(((float)(4 * i) + 0.5f) * inv_jc);
+            const int rem = 4 * i - pose * JC;
+            int joint = rem / DIM, k = rem - joint * DIM;
+            PoseReg q;
+            load_reg(q, pose);
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const bool nxt = rem >= JC;
-                r[q] = value(x[q], g[q], nxt ? c1 : c0, nxt ? rem - JC : rem);
-                ++rem;
+            for (int e = 0; e < 4; ++e) {
+                r[e] = value(x[e], g[e], q, joint, k);
+                if (++k == DIM) {
+                    k = 0;
+                    if (++joint == a.J) { joint = 0; load_reg(q, min(++pose, np - 1)); }
+                }
             }
             reinterpret_cast<float4*>(dst)[i] = make_float4(r[0], r[1], r[2], r[3]);
         }
         for (int e = (n4 << 2) + threadIdx.x; e < nf; e += RTH) {
-            const int pose = e / JC;
-            dst[e] = value(__ldg(src + e), __ldg(gsrc + e), cs[pose], e - pose * JC);
+            const int pose = e / JC, rem = e - pose * JC;
+            PoseReg q;
+            load_reg(q, pose);
+            dst[e] = value(sx[e], sg_[e], q, rem / DIM, rem % DIM);
         }
         __syncthreads();
     }
@@ -740,12 +770,14 @@ extern "C" int p2c_renormalize_bwd(const float* sample, const float* g_out, floa
     if (rc) return rc;
     if (m == 0) return 0;
     if (!sample || !g_out || !g_sample) return P2C_E_NULL;
-    if (c == dim) {
+    if (c == dim && (size_t)2 * RP * j * dim * sizeof(float) <= 40 * 1024) {   // else: the warp-per-pose kernels
         a.ref_shift = nullptr;   // the shift does not enter the gradient
         if (dim == 2)
-            renorm_flat_bwd_kernel<2><<<chunk_grid(m), RTH, 0, (cudaStream_t)stream>>>(sample, g_out, g_sample, a);
+            renorm_flat_bwd_kernel<2><<<chunk_grid(m), RTH, (size_t)2 * RP * j * 2 * sizeof(float), (cudaStream_t)stream>>>(
+                sample, g_out, g_sample, a);
         else
-            renorm_flat_bwd_kernel<3><<<chunk_grid(m), RTH, 0, (cudaStream_t)stream>>>(sample, g_out, g_sample, a);
+            renorm_flat_bwd_kernel<3><<<chunk_grid(m), RTH, (size_t)2 * RP * j * 3 * sizeof(float), (cudaStream_t)stream>>>(
+                sample, g_out, g_sample, a);
         P2C_LAUNCH_CHECK();
         return 0;
     }

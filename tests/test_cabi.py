@@ -68,3 +68,24 @@ def test_cpu_tensors_are_refused(lib):
         ops.rotation_6d_to_matrix(torch.zeros(2, 6))
     with pytest.raises(RuntimeError, match='no CPU fallback'):
         ops.hips_neck_normalize(torch.zeros(2, 26, 3), 1, 8)
+
+
+def test_widened_entry_points_validate_arguments_without_gpu(lib):
+    """SURVEY 8f entry points: argument validation precedes any CUDA call; empty batches are a no-op (rc 0)."""
+    l = lib.load()
+    assert l.p2c_cum_changes_fwd(None, None, 4, 0, 26, None) == -1          # clip_len < 1
+    assert l.p2c_cum_changes_fwd(None, None, 4, 16, 26, None) == -3         # NULL tensors
+    assert l.p2c_cum_changes_fwd(None, None, 0, 16, 26, None) == 0          # empty batch
+    assert l.p2c_cum_changes_bwd(None, None, None, None, 0, 16, 26, None) == 0
+    assert l.p2c_renormalize_fwd(None, None, 8, 26, 3, 4, 1, 8, 1, 1e-5, None, None, None, 16, None) == -1   # dim 4
+    assert l.p2c_renormalize_fwd(None, None, 8, 26, 2, 3, 1, 8, 1, 1e-5, None, None, None, 16, None) == -1   # c < dim
+    assert l.p2c_renormalize_fwd(None, None, 8, 26, 3, 3, 1, 40, 1, 1e-5, None, None, None, 16, None) == -1  # neck >= J
+    assert l.p2c_renormalize_fwd(None, None, 8, 26, 3, 3, 1, 8, 1, 1e-5, None, None, None, 16, None) == -3
+    assert l.p2c_renormalize_fwd(None, None, 0, 26, 3, 3, 1, 8, 1, 1e-5, None, None, None, 16, None) == 0
+    assert l.p2c_quaternion_to_matrix_fwd(None, None, -1, None) == -1
+    assert l.p2c_quaternion_to_matrix_fwd(None, None, 5, None) == -3
+    assert l.p2c_normalize_extractor_fwd(None, None, 8, 26, 3, 1, 8, 0, 1e-5, None) == -1   # extractor 0 is the plain op
+    assert l.p2c_normalize_extractor_fwd(None, None, 8, 26, 3, 1, 8, 2, 1e-5, None) == -3
+    assert l.p2c_mpjpe_sum(None, None, 8, 0, 3, None, None, 1, None) == -1
+    assert l.p2c_pck_count(None, None, None, 8, 26, 3, 0, 1, 1, 8, 2, 0.05, 1e-5, None, None, 1, None) == -1  # norm kind
+    assert l.p2c_metric_workspace_floats() > 0

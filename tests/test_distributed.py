@@ -54,3 +54,36 @@ def test_sharded_loss_sums_allreduce_gloo():
         assert abs(ret[r][2] - float(want['loc_2d'])) < 1e-9 * max(1.0, abs(float(want['loc_2d'])))
         assert abs(ret[r][3] - float(want['loc_3d'])) < 1e-9 * max(1.0, abs(float(want['loc_3d'])))
         assert abs(ret[r][4] - float(want['loc_2d_3d'])) < 1e-9 * max(1.0, abs(float(want['loc_2d_3d'])))
+
+
+def _metric_worker(rank, world, port, ret):
+    os.environ.update(MASTER_ADDR='127.0.0.1', MASTER_PORT=str(port))
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    import oracle as O
+    from pedestrians_video_2_carla_b200.metrics import MPJPE
+    from pedestrians_video_2_carla_b200.utils.distributed import shard_range
+    g = torch.Generator().manual_seed(5)
+    gt = torch.randn((7, 4, 26, 3), generator=g, dtype=torch.float64)
+    pred = gt + torch.randn((7, 4, 26, 3), generator=g, dtype=torch.float64) * 0.05
+    lo, hi = shard_range(7, rank, world)
+    m = MPJPE()
+    # the accumulators a rank's kernel launches would have left (the oracle stands in for the kernel on CPU):
+    # (sum of joint distances, number of them) over the rank's clips
+    dists = torch.linalg.norm(pred[lo:hi] - gt[lo:hi], dim=-1)
+    m.state = torch.tensor([float(dists.sum()), float(dists.numel())], dtype=torch.float64)
+    m.sync()                                          # dist_reduce_fx="sum" of the torchmetrics original
+    ret[rank] = float(m.compute())
+    dist.destroy_process_group()
+
+
+def test_metric_state_allreduce_gloo():
+    """MPJPE over uneven shards (4 + 3 clips): the all-reduced accumulators give the unsharded metric on every rank."""
+    import oracle as O
+    g = torch.Generator().manual_seed(5)
+    gt = torch.randn((7, 4, 26, 3), generator=g, dtype=torch.float64)
+    pred = gt + torch.randn((7, 4, 26, 3), generator=g, dtype=torch.float64) * 0.05
+    want = float(O.metric_mpjpe(pred, gt))
+    ret = mp.Manager().dict()
+    mp.spawn(_metric_worker, args=(2, 29613, ret), nprocs=2, join=True)
+    for r in (0, 1):
+        assert abs(ret[r] - want) < 1e-5 * want
