@@ -341,3 +341,40 @@ def test_bbox_extractors_against_reference_golden(api, gold):
     # with hips and neck detected everywhere it equals the plain hips/neck normaliser
     y = gold['den/x2'].to(DEV)
     assert_close('== hips_neck', N(HipsNeckBBoxFallbackExtractor())(y), N()(y), 1e-6)
+
+
+def test_device_target_generator(api):
+    """Carla2D3DIterableDataset.generate_batch on the device: the distribution's invariants and, given the drawn Euler
+    changes, parity of every target with the oracle's ProjectionModule / Normalizer."""
+    from pedestrians_video_2_carla_b200.data.carla.datasets.carla_2d3d_dataset import Carla2D3DIterableDataset
+    ds = Carla2D3DIterableDataset(batch_size=12, clip_length=9, random_changes_each_frame=3, max_change_in_deg=5,
+                                  max_world_rot_change_in_deg=2, max_initial_world_rot_change_in_deg=30,
+                                  transform='hips_neck', device=DEV, seed=22742)
+    x, t, meta = ds.generate_batch()
+    assert x.shape == (12, 9, 26, 2) and len(meta['age']) == 12
+    e = t['euler_pose_changes']
+    changed = (e.abs().sum(-1) > 0).sum(-1)
+    assert int(changed.min()) == 3 and int(changed.max()) == 3           # exactly 3 distinct bones per frame
+    assert float(e.abs().max()) <= np.deg2rad(5) + 1e-7
+    assert float(t['world_loc_changes'].abs().max()) == 0.0
+    # the deterministic part against the oracle, from the generator's own draws
+    loc, rot, _, par = O.reference_tensors(torch.float64)
+    sid = torch.tensor([TYPES.index((a, g)) for a, g in zip(meta['age'], meta['gender'])])
+    mats = O.euler_angles_to_matrix(e.double().cpu())
+    assert_close('pose_changes', t['pose_changes'], mats)
+    wr = O.euler_angles_to_matrix(torch.stack((torch.zeros(12, 9), torch.zeros(12, 9),
+                                               torch.atan2(t['world_rot_changes'][..., 1, 0],
+                                                           t['world_rot_changes'][..., 0, 0]).cpu()), -1).double())
+    assert_close('world yaw only', t['world_rot_changes'], wr)
+    proj, out = O.projection_module_forward(mats, loc[sid], rot[sid], par, O.training_camera(),
+                                            torch.zeros((12, 9, 3), dtype=torch.float64), wr)
+    assert_close('absolute_pose_loc', t['absolute_pose_loc'], out['absolute_pose_loc'])
+    assert_close('projection_2d', t['projection_2d'], proj[..., :2])
+    assert_close('projection_2d_transformed', t['projection_2d_transformed'], O.hips_neck_normalize(proj)[..., :2])
+    assert torch.equal(x, t['projection_2d_transformed'])
+    # same seed, same batch; and the iterator yields per-clip items
+    ds2 = Carla2D3DIterableDataset(batch_size=12, clip_length=9, max_world_rot_change_in_deg=2,
+                                   max_initial_world_rot_change_in_deg=30, transform='hips_neck', device=DEV, seed=22742)
+    assert torch.equal(ds2.generate_batch()[0], x)
+    item = next(iter(ds2))
+    assert item[0].shape == (9, 26, 2) and item[1]['absolute_pose_loc'].shape == (9, 26, 3)
