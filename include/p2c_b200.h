@@ -223,6 +223,14 @@ int p2c_renormalize_bwd(const float* sample, const float* g_out, float* g_sample
 int p2c_normalize_extractor_fwd(const float* sample, float* out, int64_t m, int32_t j, int32_t c,
                                 int32_t hips, int32_t neck, int32_t extractor, float near_zero, void* stream);
 
+/* ---- Extractor.get_shift_scale alone (transforms/pose/normalization/extractor.py:23-36 with hips_neck_extractor.py,
+ *      bbox_extractor.py, hips_neck_bbox_fallback_extractor.py): the values Normalizer.shift / Normalizer.scale report
+ *      after a call (normalizer.py:43-49; read by data/base/mixins/dataset/projection_2d_mixin.py:229-230).
+ *      sample (M,J,c); shift out (M,dim), scale out (M); extractor 0 = hips/neck (dim 2 or 3), 1 = bbox, 2 = hips_neck_bbox. */
+int p2c_extractor_shift_scale(const float* sample, float* shift, float* scale, int64_t m, int32_t j, int32_t c,
+                              int32_t dim, int32_t hips, int32_t neck, int32_t extractor, float near_zero,
+                              void* stream);
+
 /* ---- Evaluation metrics on the step's output buffers: MPJPE (metrics/mpjpe.py:29-45), MRPE (metrics/mrpe.py:38-76),
  *      PCK (metrics/pck.py:54-97 with utils/tensors.py:12-40).  pred / gt (M,J,c).  `partials`: caller-owned workspace
  *      of p2c_metric_workspace_floats() floats; `out`: two DOUBLES on the device, (sum of distances, number of
@@ -241,6 +249,8 @@ int p2c_pck_count(const float* pred, const float* gt, const float* mask_src, int
                   int32_t accumulate, void* stream);
 
 const char* p2c_version(void);
+/* test hook: re-read the P2C_* debug switches from the environment (they are read once per process otherwise) */
+void p2c_debug_reload_env(void);
 
 #ifdef __cplusplus
 }

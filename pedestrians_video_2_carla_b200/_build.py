@@ -25,16 +25,19 @@ def _stale():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False):
-    """Compile every .cu under csrc/ into one shared library. Returns the library path."""
-    if not force and not _stale():
+def build(force=False, verbose=False, defines=(), out=None):
+    """Compile every .cu under csrc/ into one shared library. Returns the library path.
+    `defines` / `out`: experiment builds (tools/variants.py) -- extra -D flags into another .so beside the product's."""
+    lib_path = out or LIB_PATH
+    if not force and not out and not _stale():
         return LIB_PATH
     nvcc = shutil.which('nvcc') or '/usr/local/cuda/bin/nvcc'
     flags = [f for f in NVCC_FLAGS if f != '--use_fast_math=false']
     if os.environ.get('P2C_BUILD_CLOCKS') == '1':   # debug build: phase clocks of the tile kernel (tools/tile_clocks.py)
         flags.append('-DP2C_CLOCKS_BUILD')
+    flags += ['-D' + d for d in defines]
     objs = []
-    build_dir = os.path.join(PKG_DIR, 'build')
+    build_dir = os.path.join(PKG_DIR, 'build' if not out else 'build_' + os.path.basename(out).replace('.', '_'))
     os.makedirs(build_dir, exist_ok=True)
     procs = []
     for src in sources():
@@ -48,12 +51,15 @@ def build(force=False, verbose=False):
             print(out)
         if p.returncode != 0:
             raise RuntimeError('nvcc failed: %s\n%s' % (' '.join(cmd), out))
-    cmd = [nvcc, '-shared', '-o', LIB_PATH + '.tmp'] + objs + ['-gencode', 'arch=compute_100a,code=sm_100a']
+    # the SHARED CUDA runtime (the one PyTorch has already loaded; /usr/local/cuda as the fallback search path): the
+    # artefact then carries none of the runtime's own entry points
+    cmd = [nvcc, '-shared', '--cudart', 'shared', '-o', lib_path + '.tmp'] + objs + [
+        '-gencode', 'arch=compute_100a,code=sm_100a', '-Xlinker', '-rpath,/usr/local/cuda/lib64']
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:
         raise RuntimeError('link failed: %s\n%s' % (' '.join(cmd), r.stdout))
-    os.replace(LIB_PATH + '.tmp', LIB_PATH)
-    return LIB_PATH
+    os.replace(lib_path + '.tmp', lib_path)
+    return lib_path
 
 
 if __name__ == '__main__':

@@ -81,19 +81,23 @@ _SIGS = {
                                       C.c_int32, C.c_float, _P, _P, C.c_int32, _P]),
     'p2c_normalize_extractor_fwd': (C.c_int, [_P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                                               C.c_int32, C.c_float, _P]),
+    'p2c_extractor_shift_scale': (C.c_int, [_P, _P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
+                                            C.c_int32, C.c_float, _P]),
     'p2c_metric_workspace_floats': (C.c_int64, []),
     'p2c_mpjpe_sum': (C.c_int, [_P, _P, C.c_int64, C.c_int32, C.c_int32, _P, _P, C.c_int32, _P]),
     'p2c_mrpe_sum': (C.c_int, [_P, _P, _P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, _P, _P, C.c_int32, _P]),
     'p2c_pck_count': (C.c_int, [_P, _P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                                 C.c_int32, C.c_int32, C.c_float, C.c_float, _P, _P, C.c_int32, _P]),
     'p2c_version': (C.c_char_p, []),
+    'p2c_debug_reload_env': (None, []),
 }
 
 _lib = None
 
 
 def lib_path():
-    return _build.LIB_PATH
+    """The in-tree library; P2C_LIB names an experiment build of the same sources (tools/variants.py)."""
+    return os.environ.get('P2C_LIB') or _build.LIB_PATH
 
 
 def load():

@@ -26,6 +26,7 @@
 #include <stdlib.h>
 
 #include "common.cuh"
+#include "host_util.h"
 
 namespace {
 
@@ -870,18 +871,7 @@ struct Plan {
     size_t smem;
 };
 
-int g_sms = 0;
-int sm_count() {
-    if (!g_sms) {
-        int dev = 0, n = 0;
-        if (cudaGetDevice(&dev) == cudaSuccess &&
-            cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
-            g_sms = n;
-        else
-            g_sms = 148;
-    }
-    return g_sms;
-}
+int sm_count() { return p2c_sm_count(); }   // of the current device (host_util.cu)
 
 size_t smem_bytes(int gl, int B, int warps, int want_norm) {
     return (size_t)smem_plan(gl, B, warps, want_norm).total * sizeof(float);
@@ -934,13 +924,12 @@ Plan make_plan(const p2c_fused_step_t* p) {
     const size_t t8 = (size_t)staged_plan(pl.gl, B, p->gt_2d_channels, 8, want_norm).total * sizeof(float);
     const size_t t16 = (size_t)staged_plan(pl.gl, B, p->gt_2d_channels, 16, want_norm).total * sizeof(float);
     const size_t s8 = smem_bytes(pl.gl, B, 8, want_norm), s16 = smem_bytes(pl.gl, B, 16, want_norm);
-    const char* no_tma = getenv("P2C_DISABLE_TMA");  // test hook: the register-staged variant
-    const bool allow_staged = !(no_tma && no_tma[0] == '1');
+    const P2cEnv& env = p2c_env();
+    const bool allow_staged = !env.disable_tma;  // test hook: the register-staged variant
     const long groups_ = p->mode == P2C_MODE_POSE_CHANGES ? p->n_clips : (total + pl.gl - 1) / pl.gl;
     const size_t tslim = (size_t)staged_plan(pl.gl, B, p->gt_2d_channels, 8, want_norm, 1).total * sizeof(float);
-    const char* no_slim = getenv("P2C_DISABLE_SLIM");
-    if (allow_staged && !(no_slim && no_slim[0] == '1') && p->gt_2d_channels == 3 && 4 * (tslim + 1024) <= 228 * 1024 &&
-        (groups_ >= 3L * sm_count() || (getenv("P2C_FORCE_SLIM") && getenv("P2C_FORCE_SLIM")[0] == '1'))) {
+    if (allow_staged && !env.disable_slim && p->gt_2d_channels == 3 && 4 * (tslim + 1024) <= 228 * 1024 &&
+        (groups_ >= 3L * sm_count() || env.force_slim)) {
         pl.warps = 8; pl.smem = tslim; pl.staged = 1; pl.slim = 1;   // many clips: 4 CTAs (32 warps) per SM
     } else if (allow_staged && (2 * (t8 + 1024) <= cap || pl.gl <= 8) && t8 + 1024 <= cap) {
         pl.warps = 8; pl.smem = t8; pl.staged = 1;       // TMA-staged, two CTAs per SM
@@ -966,8 +955,7 @@ Plan make_plan(const p2c_fused_step_t* p) {
 }  // namespace
 
 extern "C" int p2c_fused_fast_supported(const p2c_fused_step_t* p) {
-    const char* off = getenv("P2C_DISABLE_FAST");  // test hook: force the exact generic composite
-    if (off && off[0] == '1') return 0;
+    if (p2c_env().disable_fast) return 0;  // test hook: force the exact generic composite
     if (!p->input_6d) return 0;  // arbitrary 3x3 input is not assumed to be a rotation: exact generic path
     if (p->mode != P2C_MODE_POSE_CHANGES && p->mode != P2C_MODE_RELATIVE_ROT) return 0;
     if (p->mode == P2C_MODE_POSE_CHANGES && !p->ref_rot) return 0;
@@ -1018,13 +1006,7 @@ extern "C" int p2c_fused_fast(const p2c_fused_step_t* p, void* stream) {
     else
         k = pl.warps == 8 ? (carla ? fast_kernel<8, 26> : fast_kernel<8, 0>)
                           : (carla ? fast_kernel<16, 26> : fast_kernel<16, 0>);
-    static kern_t configured[10] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    const int ki = pl.slim ? 8 + (carla ? 0 : 1) : (pl.staged ? 4 : 0) + (pl.warps == 8 ? 0 : 2) + (carla ? 0 : 1);
-    if (configured[ki] != k) {
-        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
-        if (e != cudaSuccess) return (int)e;
-        configured[ki] = k;
-    }
+    if (const int e = p2c_allow_big_smem(reinterpret_cast<const void*>(k), 227 * 1024 - 1024)) return e;
     k<<<pl.grid, pl.warps * 32, pl.smem, st>>>(args);
     P2C_LAUNCH_CHECK();
     return 0;

@@ -33,6 +33,7 @@
 #include <stdlib.h>
 
 #include "common.cuh"
+#include "host_util.h"
 
 namespace {
 
@@ -537,11 +538,14 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         mbar_init(bars + 2, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (a.count_inline) {
-        // (one tile per CTA) everything in global memory may come from the previous kernel of the stream: wait for it,
-        // then let the next kernel's CTAs take the SMs as this grid's CTAs retire
+    if (a.count_inline || !a.mask) {
+        // No count pre-pass in front of this launch (one tile per CTA, or the mask is off): the kernel is launched with
+        // programmatic stream serialization, so the previous kernel of the stream may still be running (a one-tile-
+        // per-CTA step triggers its dependents at its very top).  Everything in global memory -- the inputs, the
+        // self-resetting workspace header -- may come from it: wait until it is complete and flushed.
         asm volatile("griddepcontrol.wait;" ::: "memory");
-        asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+        // (one tile per CTA) let the next kernel's CTAs take the SMs as this grid's CTAs retire
+        if (a.count_inline) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     }
     if (tma) {
         if ((int)blockIdx.x < ntiles) {
@@ -1244,18 +1248,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     DEBUG_CLOCK(if (a.clocks && threadIdx.x == 0 && blockIdx.x < 1024) g_cta_times[blockIdx.x * 2 + 1] = globaltimer();)
 }
 
-int g_sms = 0;
-int sm_count() {
-    if (!g_sms) {
-        int dev = 0, n = 0;
-        if (cudaGetDevice(&dev) == cudaSuccess &&
-            cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
-            g_sms = n;
-        else
-            g_sms = 148;
-    }
-    return g_sms;
-}
+int sm_count() { return p2c_sm_count(); }   // of the current device (host_util.cu)
 
 // parents of the bone tree (parents precede children: pose.py:41-47)
 bool tree_tables(const p2c_tree_t& t, TileArgs& a) {
@@ -1312,7 +1305,7 @@ TileLaunch make_launch(const p2c_fused_step_t* p, const TileArgs& a) {   // a: t
     if (per_sm * t.threads > 896) per_sm = 896 / t.threads;   // 72 registers per thread (launch bounds 832 x 1)
     if (per_sm > 4) per_sm = 4;
     if (per_sm < 1) per_sm = 1;
-    if (getenv("P2C_TILE_ONE_CTA") && getenv("P2C_TILE_ONE_CTA")[0] == '1') per_sm = 1;   // debug: no co-resident CTA
+    if (p2c_env().tile_one_cta) per_sm = 1;   // debug: no co-resident CTA
     const long slots = (long)sm_count() * per_sm;
     t.grid = (int)(ntiles < slots ? ntiles : slots);
     t.dynamic = ntiles > t.grid ? 1 : 0;
@@ -1321,17 +1314,12 @@ TileLaunch make_launch(const p2c_fused_step_t* p, const TileArgs& a) {   // a: t
     return t;
 }
 
-bool env_on(const char* name) {
-    const char* v = getenv(name);
-    return v && v[0] == '1';
-}
-
 }  // namespace
 
 extern "C" int p2c_fused_tile_supported(const p2c_fused_step_t* p) {
     // test hooks: the older kernel variants stay reachable
-    if (env_on("P2C_DISABLE_TILE") || env_on("P2C_DISABLE_FAST") || env_on("P2C_FORCE_SLIM") || env_on("P2C_DISABLE_TMA"))
-        return 0;
+    const P2cEnv& env = p2c_env();
+    if (env.disable_tile || env.disable_fast || env.force_slim || env.disable_tma) return 0;
     if (!p->input_6d) return 0;   // arbitrary 3x3 input is not assumed to be a rotation: exact generic path
     if (p->mode != P2C_MODE_POSE_CHANGES && p->mode != P2C_MODE_RELATIVE_ROT) return 0;
     if (p->mode == P2C_MODE_POSE_CHANGES && !p->ref_rot) return 0;
@@ -1362,8 +1350,8 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     if (!t.ok) return P2C_E_UNSUPPORTED;
     const int B = p->tree.n_bones;
     a.N = p->n_clips; a.L = p->clip_len; a.P = t.P; a.PS = t.PS; a.slices = t.slices;
-    a.clock_cta = getenv("P2C_TILE_CTA") ? atoi(getenv("P2C_TILE_CTA")) : 0;
-    a.clocks = getenv("P2C_TILE_CLOCKS") ? atoi(getenv("P2C_TILE_CLOCKS")) : 0;   // n: record the n-th tile of CTA 0
+    a.clock_cta = p2c_env().tile_cta;
+    a.clocks = p2c_env().tile_clocks;   // n: record the n-th tile of CTA 0
     a.scan = p->mode == P2C_MODE_POSE_CHANGES;
     a.hips = p->hips; a.neck = p->neck; a.normalize = p->normalize; a.mask = p->mask_missing_joints;
     a.d6 = p->pose_in; a.ref_loc = p->ref_loc; a.ref_rot = p->ref_rot; a.ref_index = p->ref_index;
@@ -1405,12 +1393,7 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
                      : ki == 3 ? tile_kernel<26, 2, false, true>
                      : ki == 4 ? tile_kernel<0, 0, false, false>
                                : tile_kernel<0, 0, true, false>;
-    static bool configured[6] = {false, false, false, false, false, false};
-    if (!configured[ki]) {
-        cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024 - 1024);
-        if (e != cudaSuccess) return (int)e;
-        configured[ki] = true;
-    }
+    if (const int e = p2c_allow_big_smem(reinterpret_cast<const void*>(k), 227 * 1024 - 1024)) return e;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(t.grid);
     cfg.blockDim = dim3(t.threads);
@@ -1428,7 +1411,7 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     // One tile per CTA with the mask on: the CTAs wait for each other's joint counts inside the kernel, so the launch
     // is COOPERATIVE (the whole grid is resident at once or the launch fails: two such kernels on two streams cannot
     // starve each other).
-    cfg.numAttrs = (a.mask && a.count_inline && !env_on("P2C_TILE_NO_COOP")) ? 2 : 1;
+    cfg.numAttrs = (a.mask && a.count_inline && !p2c_env().tile_no_coop) ? 2 : 1;
     cudaError_t le = cudaLaunchKernelEx(&cfg, k, a);
     if (le != cudaSuccess && cfg.numAttrs == 2) {   // (the two attributes together are refused: cooperative only)
         (void)cudaGetLastError();

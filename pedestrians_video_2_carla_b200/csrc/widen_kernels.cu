@@ -665,6 +665,55 @@ __global__ void __launch_bounds__(WARPS * 32) normalize_extractor_kernel(const f
     }
 }
 
+// ---- Extractor.get_shift_scale alone (extractor.py:23-36 and the three extractors): what Normalizer.shift / .scale
+//      report after a call (normalizer.py:43-49, read by data/base/mixins/dataset/projection_2d_mixin.py:229-230).
+//      extractor 0: hips / neck over `dim` channels; 1 / 2: the bounding-box extractors above (dim 2).
+__global__ void __launch_bounds__(WARPS * 32) shift_scale_kernel(const float* __restrict__ in, float* __restrict__ shift,
+                                                                float* __restrict__ scale, long M, int J, int C, int dim,
+                                                                int hips, int neck, int extractor, float near_zero) {
+    const int lane = threadIdx.x & 31;
+    const float inf = __builtin_huge_valf();
+    const long wstride = (long)gridDim.x * WARPS;
+    for (long m = (long)blockIdx.x * WARPS + (threadIdx.x >> 5); m < M; m += wstride) {
+        const float* p = in + m * J * C;
+        float s[3] = {0.f, 0.f, 0.f}, sc;
+        float d2 = 0.f;
+        for (int k = 0; k < dim; ++k) {
+            s[k] = __ldg(p + hips * C + k);
+            const float d = __ldg(p + neck * C + k) - s[k];
+            d2 = fmaf(d, d, d2);
+        }
+        sc = sqrtf(d2);
+        if (extractor != 0) {
+            float lox = inf, loy = inf, hix = -inf, hiy = -inf;
+            for (int j = lane; j < J; j += 32) {
+                const float x = p[j * C], y = p[j * C + 1];
+                if (!(x < near_zero && y < near_zero)) {
+                    lox = fminf(lox, x); hix = fmaxf(hix, x);
+                    loy = fminf(loy, y); hiy = fmaxf(hiy, y);
+                }
+            }
+            for (int o = 16; o > 0; o >>= 1) {
+                lox = fminf(lox, __shfl_xor_sync(FULL_MASK, lox, o)); hix = fmaxf(hix, __shfl_xor_sync(FULL_MASK, hix, o));
+                loy = fminf(loy, __shfl_xor_sync(FULL_MASK, loy, o)); hiy = fmaxf(hiy, __shfl_xor_sync(FULL_MASK, hiy, o));
+            }
+            const float cx = (lox + hix) / 2.f, cy = (loy + hiy) / 2.f;
+            const float ddx = cx - cx, ddy = loy - cy;   // (as torch.linalg.norm forms it: NaN boxes stay NaN)
+            const float bb_scale = sqrtf(ddx * ddx + ddy * ddy);
+            if (extractor == 1) {
+                s[0] = cx; s[1] = cy; sc = bb_scale;
+            } else {
+                const bool missing_hips = s[0] < near_zero && s[1] < near_zero;
+                const float nx = __ldg(p + neck * C), ny = __ldg(p + neck * C + 1);
+                const bool missing_neck = nx < near_zero && ny < near_zero;
+                if (missing_hips || missing_neck) sc = bb_scale * 0.5748f;
+            }
+        }
+        if (lane < dim) shift[m * dim + lane] = s[lane];
+        if (lane == 0) scale[m] = sc;
+    }
+}
+
 int warp_grid(long units) {
     long blocks = (units + WARPS - 1) / WARPS;
     if (blocks > 148L * 64) blocks = 148L * 64;
@@ -819,6 +868,20 @@ extern "C" int p2c_normalize_extractor_fwd(const float* sample, float* out, int6
     if (!sample || !out) return P2C_E_NULL;
     normalize_extractor_kernel<<<warp_grid(m), WARPS * 32, 0, (cudaStream_t)stream>>>(sample, out, (long)m, j, c, hips,
                                                                                    neck, extractor, near_zero);
+    P2C_LAUNCH_CHECK();
+    return 0;
+}
+
+extern "C" int p2c_extractor_shift_scale(const float* sample, float* shift, float* scale, int64_t m, int32_t j, int32_t c,
+                                         int32_t dim, int32_t hips, int32_t neck, int32_t extractor, float near_zero,
+                                         void* stream) {
+    if (m < 0 || j < 1 || (dim != 2 && dim != 3) || c < dim || extractor < 0 || extractor > 2) return P2C_E_BADARG;
+    if (extractor != 0 && dim != 2) return P2C_E_BADARG;
+    if (hips < 0 || hips >= j || neck < 0 || neck >= j) return P2C_E_BADARG;
+    if (m == 0) return 0;
+    if (!sample || !shift || !scale) return P2C_E_NULL;
+    shift_scale_kernel<<<warp_grid(m), WARPS * 32, 0, (cudaStream_t)stream>>>(sample, shift, scale, (long)m, j, c, dim, hips,
+                                                                           neck, extractor, near_zero);
     P2C_LAUNCH_CHECK();
     return 0;
 }

@@ -2,6 +2,7 @@
 of the (transformed) projection and of the target, over the joints kept by utils/tensors.py:29-40.  The boolean-mask
 gather + mse_loss of the reference is one masked two-stage reduction kernel here."""
 from .. import ops
+from ._criterion import require_mse
 from ..data.carla.skeleton import CARLA_SKELETON, get_root_point
 
 
@@ -11,6 +12,7 @@ class Loc2DPoseLoss(object):
         if input_nodes is not output_nodes:
             raise NotImplementedError('cross-skeleton index mapping (get_common_indices) is outside the accelerated '
                                       'path: input and output skeletons must match')
+        require_mse(criterion, 'loc_2d')
         self._mask = mask_missing_joints
         self._hips = get_root_point() if input_nodes is CARLA_SKELETON else input_nodes.get_hips_point().value
 

@@ -3,10 +3,12 @@
 import warnings
 
 from .. import ops
+from ._criterion import require_mse
 
 
 def calculate_loss_loc_3d(criterion=None, input_nodes=None, output_nodes=None, absolute_pose_loc=None, targets=None,
                           **kwargs):
+    require_mse(criterion, 'loc_3d')
     if input_nodes is not output_nodes:
         raise NotImplementedError('cross-skeleton index mapping is outside the accelerated path')
     try:

@@ -54,6 +54,10 @@ class ProjectionModule(nn.Module):
         if 'reference_pose' in meta and not isinstance(meta['reference_pose'][0], type):
             loc, rot = zip(*[p.tensors for p in meta['reference_pose']])
             self._ref, self._ref_index = (torch.stack(loc), torch.stack(rot)), None
+        elif torch.is_tensor(meta.get('skeleton_index')):
+            # (device data generators) the row of the reference table per clip, already on the device: no host loop
+            self._ref = R.get_relative_tensors(device)
+            self._ref_index = meta['skeleton_index'].to(device=device, dtype=torch.int32)
         else:
             self._ref = R.get_relative_tensors(device)
             idx = [R.skeleton_index(meta['age'][i], meta['gender'][i]) for i in range(n)]
@@ -146,7 +150,15 @@ class ProjectionModule(nn.Module):
         world_loc = world_rot = None
         if world_loc_change_batch is not None or world_rot_change_batch is not None:
             world_loc, world_rot = self._world((n, l), device, world_loc_change_batch, world_rot_change_batch)
-        normalize = transform is not None
+        # modules/flow/pose_lifting.py:167-170 applies dm.transform_callable: only the hips/neck normaliser is fused.
+        # 'hips_neck_bbox' (the CLI default, HipsNeckBBoxFallbackExtractor) differs from it only when hips or neck are
+        # UNDETECTED (pixel coordinates below near_zero), which cannot happen for a projected skeleton in front of the
+        # camera; 'bbox' or a user callable is a different normalisation and is refused here (unfused path:
+        # forward() + Normalizer(BBoxExtractor()) + the loss mirrors).
+        if transform not in (None, 'none', 'hips_neck', 'hips_neck_bbox'):
+            raise NotImplementedError("fused_step fuses transform None / 'hips_neck' / 'hips_neck_bbox' only, got %r; "
+                                      'use forward() + the transform + the loss mirrors for anything else' % (transform,))
+        normalize = transform not in (None, 'none')
         gt2 = targets['projection_2d_transformed' if normalize else 'projection_2d']
         w = loss_weights or {}
         ref_loc, ref_rot = self._ref

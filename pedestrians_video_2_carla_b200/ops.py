@@ -286,6 +286,20 @@ def normalize_extractor(sample, hips, neck, extractor, near_zero=1e-5):
     return out
 
 
+def extractor_shift_scale(sample, dim, hips, neck, extractor=0, near_zero=1e-5):
+    """Extractor.get_shift_scale (extractor.py:23-36) of (..., J, C) samples: shift (..., dim), scale (...,).
+    extractor 0 = hips/neck, 1 = bbox, 2 = hips_neck_bbox.  No gradient (reported values)."""
+    s = _f32c(sample.detach(), 'sample')
+    j, c = s.shape[-2], s.shape[-1]
+    lead = s.shape[:-2]
+    m = s.numel() // (j * c) if s.numel() else 0
+    shift = torch.empty(lead + (dim,), device=s.device)
+    scale = torch.empty(lead, device=s.device)
+    check(_lib.load().p2c_extractor_shift_scale(ptr(s), ptr(shift), ptr(scale), m, j, c, dim, hips, neck, extractor,
+                                                near_zero, stream()), 'extractor_shift_scale')
+    return shift, scale
+
+
 class _MaskedMSE(torch.autograd.Function):
     """nn.MSELoss('mean') over [..., :c_used] of the joints kept by utils/tensors.py:29-40."""
 
@@ -435,10 +449,31 @@ class FusedStepResult(object):
             x.grad = g if x.grad is None else x.grad + g
 
 
+def _gt2_records(gt2):
+    """The 2-D target as the kernels want it: contiguous (N,L,B,C) fp32 records.  The reference hands over
+    `projection[..., :2]` (data/base/mixins/dataset/projection_2d_mixin.py:224-228), a stride-3 VIEW of 3-channel
+    records: that is passed as the 3-channel tensor it lives in (no copy, and the layout the tile kernel takes)."""
+    if (gt2 is not None and gt2.is_cuda and gt2.dtype == torch.float32 and gt2.dim() >= 2 and gt2.shape[-1] == 2
+            and not gt2.is_contiguous() and gt2.numel() > 0):
+        want = [1] * gt2.dim()
+        want[-1], acc = 1, 3
+        for d in range(gt2.dim() - 2, -1, -1):
+            want[d] = acc
+            acc *= gt2.shape[d]
+        if list(gt2.stride()) == want and \
+                gt2.storage_offset() + acc <= gt2.untyped_storage().nbytes() // gt2.element_size():
+            return gt2.as_strided(tuple(gt2.shape[:-1]) + (3,), gt2.stride())
+    return _f32c(gt2, 'gt_2d')
+
+
 class _FusedStep(torch.autograd.Function):
     """ProjectionModule.forward -> Normalizer -> loc_2d / loc_3d / loc_2d_3d with the gradient w.r.t. the pose
     input produced in the SAME launch sequence (modules/flow/pose_lifting.py:121-195, flow/base.py:440-469).
-    forward returns the three losses; backward only scales the stored gradient by the upstream scalars."""
+    Outputs: the three losses and the module's tensors (relative_pose_rot, absolute_pose_rot, absolute_pose_loc,
+    projection_2d, projection_2d_transformed), ALL with an autograd edge back to pose_in.  backward: the fused sum
+    only scales the gradient the step kernel already produced; an upstream gradient on any of the module tensors
+    (a caller adding another loss on them, e.g. rot_3d on absolute_pose_rot) is chained through the exact backward
+    kernels (p2c_hips_neck_normalize_bwd, p2c_fk_bwd, p2c_rot6d_to_matrix_bwd) and added."""
 
     @staticmethod
     def forward(ctx, pose_in, cfg):
@@ -446,7 +481,7 @@ class _FusedStep(torch.autograd.Function):
         pose_in = _f32c(pose_in, 'pose_in')
         N, L, B = pose_in.shape[:3]
         dev = pose_in.device
-        gt2, gt3 = _f32c(cfg['gt_2d'], 'gt_2d'), _f32c(cfg['gt_3d'], 'gt_3d')
+        gt2, gt3 = _gt2_records(cfg['gt_2d']), _f32c(cfg['gt_3d'], 'gt_3d')
         ref_index = cfg.get('ref_index')
         out = cfg.get('out') or {}
         input_6d = 1 if pose_in.shape[-1] == 6 and pose_in.dim() == 4 else 0
@@ -462,6 +497,7 @@ class _FusedStep(torch.autograd.Function):
         if plan is not None and plan[0] == key:
             _, a, rel_rot, abs_rot, abs_loc, proj, proj_norm, g_in, losses, keep = plan
             a.pose_in, a.gt_2d, a.gt_3d, a.ref_index = ptr(pose_in), ptr(gt2), ptr(gt3), ptr(ref_index)
+            ws, ref_loc, ref_rot, world_loc, world_rot = keep[:5]
         else:
             a = _lib.FusedStep()
             a.tree, a.hips, a.neck = cfg['tree'], cfg['hips'], cfg['neck']
@@ -498,26 +534,70 @@ class _FusedStep(torch.autograd.Function):
                 out['_plan'] = (key, a, rel_rot, abs_rot, abs_loc, proj, proj_norm, g_in, losses,
                                 (ws, ref_loc, ref_rot, world_loc, world_rot, cfg['tree'], cfg['camera']))
         check(lib.p2c_fused_step(a, stream()), 'fused_step')
-        ctx.save_for_backward(g_in)
+        # fresh tensor objects over the (possibly preallocated, reused) buffers: autograd attaches this call's node to
+        # the objects it is handed
+        o_rel, o_absr, o_absl, o_proj = rel_rot.detach(), abs_rot.detach(), abs_loc.detach(), proj.detach()
+        o_pn = proj_norm.detach() if proj_norm is not None else pose_in.new_empty(0)
+        ctx.save_for_backward(g_in, pose_in, ref_loc, ref_rot, ref_index, world_loc, world_rot, o_rel, o_absr, o_absl,
+                              o_proj)
+        ctx.cfg = (cfg['tree'], cfg['camera'], cfg['mode'], cfg['hips'], cfg['neck'], input_6d, proj_norm is not None)
         ctx.set_materialize_grads(False)
         res = cfg.setdefault('_result', FusedStepResult())
         res.losses, res.grad_pose_in = losses, g_in
-        res.relative_pose_rot, res.absolute_pose_rot, res.absolute_pose_loc = rel_rot, abs_rot, abs_loc
-        res.projection_2d, res.projection_2d_transformed = proj, proj_norm
-        # loc_2d / loc_3d are reported values (views of the losses buffer, no autograd edge); the fused sum is the one
-        # differentiable output
+        # loc_2d / loc_3d are reported values (views of the losses buffer, no autograd edge: for one of them alone call
+        # with weight_3d = 0 or weight_2d = 0); the fused sum and the module tensors are differentiable
         l2, l3 = losses[0], losses[1]
         ctx.mark_non_differentiable(l2, l3)
-        return l2, l3, losses[2].clone()
+        if proj_norm is None:
+            ctx.mark_non_differentiable(o_pn)
+        return l2, l3, losses[2].clone(), o_rel, o_absr, o_absl, o_proj, o_pn
 
     @staticmethod
-    def backward(ctx, g2d, g3d, g23):
-        # g_pose_in holds d(w2*loc_2d + w3*loc_3d)/d pose_in: the backward is a pure scale by the upstream scalar.
-        # (For loc_2d or loc_3d alone call fused_step with weight_3d=0 or weight_2d=0.)
-        if g23 is None:
-            return None, None
-        (g_in,) = ctx.saved_tensors
-        return g_in * g23, None
+    def backward(ctx, g2d, g3d, g23, g_rel, g_absr, g_absl, g_proj, g_pn):
+        g_in, pose_in, ref_loc, ref_rot, ref_index, world_loc, world_rot, rel_rot, abs_rot, abs_loc, proj = \
+            ctx.saved_tensors
+        tree, camera, mode, hips, neck, input_6d, has_pn = ctx.cfg
+        if not has_pn:
+            g_pn = None
+        # g_pose_in holds d(w2*loc_2d + w3*loc_3d)/d pose_in: for the fused sum the backward is a pure scale
+        total = g_in * g23 if g23 is not None else None
+        if any(g is not None for g in (g_rel, g_absr, g_absl, g_proj, g_pn)):
+            # another loss on the module tensors: the exact chain rule through the standalone backward kernels
+            lib = _lib.load()
+            N, L, B = pose_in.shape[:3]
+            g_proj = _f32c(g_proj, 'g_proj')
+            if g_pn is not None:
+                gp = torch.empty_like(proj)
+                check(lib.p2c_hips_neck_normalize_bwd(ptr(proj), ptr(_f32c(g_pn, 'g_proj_norm')), ptr(gp), N * L, B, 3,
+                                                      hips, neck, 1e-5, stream()), 'hips_neck_normalize_bwd')
+                g_proj = gp if g_proj is None else g_proj + gp
+            mats = pose_in
+            if input_6d:
+                mats = torch.empty((N, L, B, 3, 3), device=pose_in.device)
+                check(lib.p2c_rot6d_to_matrix_fwd(ptr(pose_in), ptr(mats), N * L * B, stream()), 'rot6d_to_matrix_fwd')
+            a = _lib.FkBwd()
+            a.tree, a.n_clips, a.clip_len, a.mode = tree, N, L, mode
+            a.pose_in, a.ref_loc, a.ref_index = ptr(mats), ptr(ref_loc), ptr(ref_index)
+            a.ref_rot = ptr(ref_rot) if mode == _lib.MODE_POSE_CHANGES else None
+            a.world_loc, a.world_rot, a.camera = ptr(world_loc), ptr(world_rot), camera
+            a.rel_rot = ptr(rel_rot) if mode == _lib.MODE_POSE_CHANGES else None
+            a.abs_rot, a.abs_loc = ptr(abs_rot), ptr(abs_loc)
+            g_rel = _f32c(g_rel, 'g_rel_rot')
+            g_absr, g_absl = _f32c(g_absr, 'g_abs_rot'), _f32c(g_absl, 'g_abs_loc')
+            a.g_rel_rot = ptr(g_rel) if mode == _lib.MODE_POSE_CHANGES else None
+            a.g_abs_rot, a.g_abs_loc, a.g_proj = ptr(g_absr), ptr(g_absl), ptr(g_proj)
+            g_mats = torch.empty_like(mats)
+            a.g_pose_in = ptr(g_mats)
+            check(lib.p2c_fk_bwd(a, stream()), 'fk_bwd')
+            if mode != _lib.MODE_POSE_CHANGES and g_rel is not None:
+                g_mats = g_mats + g_rel   # relative_rot mode: rel_rot IS the input matrix (no scan)
+            extra = g_mats
+            if input_6d:
+                extra = torch.empty_like(pose_in)
+                check(lib.p2c_rot6d_to_matrix_bwd(ptr(pose_in), ptr(g_mats), ptr(extra), N * L * B, stream()),
+                      'rot6d_to_matrix_bwd')
+            total = extra if total is None else total + extra
+        return total, None
 
 
 def fused_step_buffers(n_clips, clip_len, n_bones, device, input_6d=True, transformed=False):
@@ -538,13 +618,19 @@ def fused_step(pose_in, tree, camera, ref_loc, ref_rot, gt_2d, gt_3d, ref_index=
                mode=_lib.MODE_POSE_CHANGES, hips=1, neck=8, normalize=True, mask_missing_joints=True, weight_2d=1.0,
                weight_3d=1.0, want_transformed=True, out=None):
     """One pose_lifting step of the hot path in one call.  pose_in: (N,L,B,6) rotation_6d model output or
-    (N,L,B,3,3) matrices.  Returns FusedStepResult; .loc_2d_3d (= weight_2d*loc_2d + weight_3d*loc_3d) carries
-    the autograd edge back to pose_in.  `out` may hold preallocated buffers (CUDA-graph friendly)."""
+    (N,L,B,3,3) matrices.  Returns FusedStepResult; .loc_2d_3d (= weight_2d*loc_2d + weight_3d*loc_3d) and the module
+    tensors (.relative_pose_rot, .absolute_pose_rot, .absolute_pose_loc, .projection_2d, .projection_2d_transformed)
+    carry autograd edges back to pose_in (.loc_2d / .loc_3d are reported values).  `out` may hold preallocated
+    buffers (CUDA-graph friendly; the outputs of step i are then overwritten by step i+1, so any extra loss on them
+    must be back-propagated before the next call)."""
     cfg = dict(tree=tree, camera=camera, ref_loc=ref_loc, ref_rot=ref_rot, gt_2d=gt_2d, gt_3d=gt_3d,
                ref_index=ref_index, world_loc=world_loc, world_rot=world_rot, mode=mode, hips=hips, neck=neck,
                normalize=normalize, mask_missing_joints=mask_missing_joints, weight_2d=weight_2d,
                weight_3d=weight_3d, want_transformed=want_transformed, out=out)
-    l2, l3, l23 = _FusedStep.apply(pose_in, cfg)
+    l2, l3, l23, rel_rot, abs_rot, abs_loc, proj, proj_norm = _FusedStep.apply(pose_in, cfg)
     res = cfg['_result']
     res.loc_2d, res.loc_3d, res.loc_2d_3d, res.pose_in = l2, l3, l23, pose_in
+    res.relative_pose_rot, res.absolute_pose_rot, res.absolute_pose_loc = rel_rot, abs_rot, abs_loc
+    res.projection_2d = proj
+    res.projection_2d_transformed = proj_norm if (want_transformed and normalize) else None
     return res
