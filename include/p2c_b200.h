@@ -9,7 +9,8 @@
  * Conventions
  *   - every pointer is a DEVICE pointer to contiguous row-major fp32 unless stated;
  *     the caller (PyTorch's caching allocator) owns all buffers incl. workspaces;
- *     the library never allocates, frees, or synchronises.
+ *     the library never allocates, frees, or synchronises (one exception, at set-up time:
+ *     the 8 KB IPC-shareable exchange block of p2c_exchange_create / _destroy).
  *   - work is enqueued on `stream` (a cudaStream_t passed as void*); pass PyTorch's
  *     current stream so autograd ordering holds.
  *   - rotation matrices act on ROW vectors from the right (p' = p R + t); the bone axis is
@@ -143,6 +144,19 @@ int p2c_masked_mse_bwd(const float* pred, const float* gt, const float* out, con
                        float* g_pred, int64_t m, int32_t j, int32_t c_pred, int32_t c_gt,
                        int32_t c_used, int32_t mask_hips, void* stream);
 
+/* ---- The autoencoder flow's step on this path (modules/flow/autoencoder.py:102-112: the model emits 2-D poses, the
+ *      loss is Loc2DPoseLoss, loss/loc_2d.py:69-89): the masked MSE of p2c_masked_mse_fwd over two channels AND
+ *      d(upstream * loss)/d pred in ONE cooperative launch -- predictions and targets read once, gradient written once.
+ *      pred, g_pred (M,J,2), 16-byte aligned; gt (M,J,c_gt), c_gt 2 (16-byte aligned) or 3 (8-byte aligned).
+ *      workspace: p2c_loc2d_step_workspace_floats() floats whose first 16 are self-resetting counters (zero them once).
+ *      out[4] = {loss, sum_sq, count, 0}.  exchange: as in p2c_fused_step_t (publishes {sum_sq, count, 0, 0}) or NULL.
+ *      p2c_loc2d_step_supported == 0 (the errors of the batch do not fit on chip): use p2c_masked_mse_fwd / _bwd.      */
+int64_t p2c_loc2d_step_workspace_floats(void);
+int p2c_loc2d_step_supported(int64_t m, int32_t j, int32_t c_gt);
+int p2c_loc2d_step(const float* pred, const float* gt, int64_t m, int32_t j, int32_t c_gt, int32_t mask_hips,
+                   float upstream, float* g_pred, float* workspace, float* out, float* exchange,
+                   int32_t exchange_rank, int32_t exchange_world, void* stream);
+
 /* ---- One pose_lifting step of the hot path, fused: ProjectionModule.forward
  *      (modules/layers/projection.py:73-123) -> Normalizer (modules/flow/pose_lifting.py:167-170) ->
  *      loc_2d, loc_3d, loc_2d_3d (modules/flow/base.py:440-469; loss/loc_2d.py, loc_3d.py, loc_2d_3d.py)
@@ -179,11 +193,37 @@ typedef struct {
                                     are self-resetting counters: zero them ONCE before the first call, every call
                                     leaves them zero again; do not share one workspace between concurrent streams */
     float* losses;               /* out, 8 floats                                                    */
+    /* data-parallel ranks (one process per GPU, clips sharded by batch): when `exchange` is a block made by
+       p2c_exchange_create + p2c_exchange_set_peers, the kernel that finishes the loss sums also stores this rank's
+       {sum_sq_2d, count_2d, sum_sq_3d, count_3d} into every rank's block (peer stores over NVLink; no collective
+       kernel, nothing waits for a peer).  NULL: single rank.  One block per stream, like the workspace.            */
+    float* exchange;
+    int32_t exchange_rank, exchange_world;
 } p2c_fused_step_t;
 int64_t p2c_fused_step_workspace_floats(int64_t n_poses, int32_t n_bones, int32_t input_6d);
 int p2c_fused_step(const p2c_fused_step_t* p, void* stream);
 /* number of kernels p2c_fused_step(p) enqueues (for launch accounting; < 0 = bad argument) */
 int p2c_fused_step_launches(const p2c_fused_step_t* p);
+
+/* ---- The path's only cross-GPU exchange (replaces Lightning's DDP-side reduction of the logged losses,
+ *      modules/flow/base.py:467-468 with sync_dist; README.md:74-75 run shape): every rank owns one small block in its
+ *      own HBM, maps the blocks of its peers (CUDA IPC), and the step kernels write their four loss sums into all of
+ *      them.  p2c_exchange_create allocates the block (the ONE allocation this library makes: IPC-shareable memory
+ *      cannot come from a sub-allocating caller) and returns its 64-byte IPC handle for the peers;
+ *      p2c_exchange_open maps a peer's block; p2c_exchange_set_peers stores the table of mapped pointers (entry r =
+ *      rank r's block as this process addresses it; entry `rank` = the own block); p2c_exchange_read sums the entries
+ *      of step `seq` (1-based count of steps published through the block; 0 = the latest) over the ranks IN RANK ORDER:
+ *      out[8] = {sum_sq_2d, count_2d, sum_sq_3d, count_3d, ranks whose entry carries `seq`, global loc_2d,
+ *      global loc_3d, seq}.  The reader never waits: a rank that has not published yet is simply not counted (the
+ *      caller orders its read after the peers' steps, e.g. behind the barrier it already has).                       */
+int64_t p2c_exchange_block_bytes(void);
+int32_t p2c_exchange_max_ranks(void);
+int p2c_exchange_create(void** block, unsigned char* ipc_handle /* 64 bytes out, or NULL */);
+int p2c_exchange_open(const unsigned char* ipc_handle, void** peer_block);
+int p2c_exchange_close(void* peer_block);
+int p2c_exchange_destroy(void* block);
+int p2c_exchange_set_peers(void* block, void* const* peer_blocks, int32_t world);
+int p2c_exchange_read(const void* block, int32_t world, uint32_t seq, float* out, void* stream);
 
 /* ---- pytorch3d 0.6.0 quaternion_to_matrix (real part first, not normalised first): the quaternion entry the
  *      north star names next to euler_angles_to_matrix (walker_control/p3d_pose.py:54) and rotation_6d_to_matrix

@@ -529,10 +529,14 @@ def metric_pck(pred, gt, gt_projection_2d=None, norm='bbox', threshold=0.05, mas
     return int(torch.sum(dist[mask] < threshold)), int(dist[mask].numel())
 
 
-def normalize_with_extractor(sample, extractor='hips_neck_bbox', hips=HIPS, neck=NECK, near_zero=1e-5):
-    """Normalizer (normalizer.py:20-41, dim=2) with BBoxExtractor (bbox_extractor.py:6-18) or
-    HipsNeckBBoxFallbackExtractor (hips_neck_bbox_fallback_extractor.py:21-46)."""
+def extractor_shift_scale(sample, extractor='hips_neck_bbox', hips=HIPS, neck=NECK, near_zero=1e-5):
+    """Extractor.get_shift_scale of the 2-D extractors: BBoxExtractor (bbox_extractor.py:6-18),
+    HipsNeckBBoxFallbackExtractor (hips_neck_bbox_fallback_extractor.py:21-46) or HipsNeckExtractor ('hips_neck');
+    these are the values Normalizer.shift / .scale hold after a call (normalizer.py:39-49)."""
     xy = sample[..., 0:2]
+    if extractor == 'hips_neck':
+        shift, scale = get_shift_scale(xy, hips, neck)
+        return shift, scale
     boxes = get_bboxes(xy, near_zero)
     bb_shift = boxes.mean(dim=-2)
     bb_scale_pt = torch.stack((boxes.mean(dim=-2)[..., 0], boxes.min(dim=-2)[0][..., 1]), dim=-1)
@@ -554,6 +558,14 @@ def normalize_with_extractor(sample, extractor='hips_neck_bbox', hips=HIPS, neck
             scale[missing_hips] = bb_scale[missing_hips] * 0.5748
         if torch.any(missing_neck):
             scale[missing_neck] = bb_scale[missing_neck] * 0.5748
+    return shift, scale
+
+
+def normalize_with_extractor(sample, extractor='hips_neck_bbox', hips=HIPS, neck=NECK, near_zero=1e-5):
+    """Normalizer (normalizer.py:20-41, dim=2) with BBoxExtractor (bbox_extractor.py:6-18) or
+    HipsNeckBBoxFallbackExtractor (hips_neck_bbox_fallback_extractor.py:21-46)."""
+    xy = sample[..., 0:2]
+    shift, scale = extractor_shift_scale(sample, extractor, hips, neck, near_zero)
     out = torch.empty_like(sample)
     out[..., 0:2] = (xy - torch.unsqueeze(shift, -2)) / scale[(...,) + (None,) * 2]
     if sample.shape[-1] > 2:

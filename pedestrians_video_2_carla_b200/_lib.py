@@ -45,7 +45,8 @@ class FusedStep(C.Structure):
                 ('world_rot', _P), ('camera', Camera), ('gt_2d', _P), ('gt_2d_channels', C.c_int32),
                 ('gt_3d', _P), ('weight_2d', C.c_float), ('weight_3d', C.c_float),
                 ('rel_rot', _P), ('abs_rot', _P), ('abs_loc', _P), ('proj', _P), ('proj_norm', _P),
-                ('g_pose_in', _P), ('workspace', _P), ('losses', _P)]
+                ('g_pose_in', _P), ('workspace', _P), ('losses', _P),
+                ('exchange', _P), ('exchange_rank', C.c_int32), ('exchange_world', C.c_int32)]
 
 
 _SIGS = {
@@ -68,9 +69,21 @@ _SIGS = {
                                      _P, _P]),
     'p2c_masked_mse_bwd': (C.c_int, [_P, _P, _P, _P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                                      C.c_int32, _P]),
+    'p2c_loc2d_step_workspace_floats': (C.c_int64, []),
+    'p2c_loc2d_step_supported': (C.c_int, [C.c_int64, C.c_int32, C.c_int32]),
+    'p2c_loc2d_step': (C.c_int, [_P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_float, _P, _P, _P, _P,
+                                 C.c_int32, C.c_int32, _P]),
     'p2c_fused_step_workspace_floats': (C.c_int64, [C.c_int64, C.c_int32, C.c_int32]),
     'p2c_fused_step': (C.c_int, [C.POINTER(FusedStep), _P]),
     'p2c_fused_step_launches': (C.c_int, [C.POINTER(FusedStep)]),
+    'p2c_exchange_block_bytes': (C.c_int64, []),
+    'p2c_exchange_max_ranks': (C.c_int32, []),
+    'p2c_exchange_create': (C.c_int, [C.POINTER(_P), C.c_char_p]),
+    'p2c_exchange_open': (C.c_int, [C.c_char_p, C.POINTER(_P)]),
+    'p2c_exchange_close': (C.c_int, [_P]),
+    'p2c_exchange_destroy': (C.c_int, [_P]),
+    'p2c_exchange_set_peers': (C.c_int, [_P, C.POINTER(_P), C.c_int32]),
+    'p2c_exchange_read': (C.c_int, [_P, C.c_int32, C.c_uint32, _P, _P]),
     'p2c_quaternion_to_matrix_fwd': (C.c_int, [_P, _P, C.c_int64, _P]),
     'p2c_quaternion_to_matrix_bwd': (C.c_int, [_P, _P, _P, C.c_int64, _P]),
     'p2c_cum_changes_fwd': (C.c_int, [_P, _P, C.c_int32, C.c_int32, C.c_int32, _P]),

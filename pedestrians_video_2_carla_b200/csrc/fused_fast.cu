@@ -62,6 +62,7 @@ struct FastArgs {
     int* count2;           // self-resetting, filled by count_kernel when mask is on
     float* losses;
     double count3;
+    XchgArgs xchg;   // data-parallel ranks: where the finishing thread publishes the four loss sums
 };
 
 struct GS {
@@ -441,6 +442,7 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 8 ? 2 : 1)) fast_kernel(
             a.losses[0] = l2; a.losses[1] = l3; a.losses[2] = a.w2 * l2 + a.w3 * l3;
             a.losses[3] = (float)d2; a.losses[4] = (float)c2; a.losses[5] = (float)d3; a.losses[6] = (float)a.count3;
             a.losses[7] = 0.f;
+            exchange_publish(a.xchg, (float)d2, (float)c2, (float)d3, (float)a.count3);
             *a.ticket = 0u;   // self-resetting workspace header: ready for the next launch
             *a.count2 = 0;
         }
@@ -860,6 +862,7 @@ __global__ void __launch_bounds__(WARPS * 32, (SLIM ? 4 : (WARPS == 8 ? 2 : 1)))
             a.losses[0] = l2; a.losses[1] = l3; a.losses[2] = a.w2 * l2 + a.w3 * l3;
             a.losses[3] = (float)d2; a.losses[4] = (float)c2; a.losses[5] = (float)d3; a.losses[6] = (float)a.count3;
             a.losses[7] = 0.f;
+            exchange_publish(a.xchg, (float)d2, (float)c2, (float)d3, (float)a.count3);
             *a.ticket = 0u;
             *a.count2 = 0;
         }
@@ -987,6 +990,7 @@ extern "C" int p2c_fused_fast(const p2c_fused_step_t* p, void* stream) {
     args.count2 = reinterpret_cast<int*>(p->workspace) + 1;
     args.partials = p->workspace + 16;
     args.losses = p->losses;
+    args.xchg = XchgArgs{p->exchange, p->exchange_rank, p->exchange_world};
     const long total = (long)p->n_clips * p->clip_len;
     args.count3 = (double)total * B * 3;
     cudaStream_t st = (cudaStream_t)stream;

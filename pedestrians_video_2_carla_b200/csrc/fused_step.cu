@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(WARPS * 32) loss_fwd_kernel(const LossArgs a) 
 
 // shared with fused_carla.cu: partials (nblocks x 4: sum_sq_2d, count_2d, sum_sq_3d, -) -> losses[8]
 __global__ void p2c_loss_finalize_kernel(const float* __restrict__ partials, int nblocks, double count3, float w2,
-                                         float w3, float* __restrict__ losses) {
+                                         float w3, float* __restrict__ losses, const XchgArgs xchg) {
     double s2 = 0.0, c2 = 0.0, s3 = 0.0;
     for (int i = threadIdx.x; i < nblocks; i += 32) {
         s2 += (double)partials[i * 4];
@@ -133,6 +133,7 @@ __global__ void p2c_loss_finalize_kernel(const float* __restrict__ partials, int
         losses[0] = l2; losses[1] = l3; losses[2] = w2 * l2 + w3 * l3;
         losses[3] = (float)s2; losses[4] = (float)c2; losses[5] = (float)s3; losses[6] = (float)count3;
         losses[7] = 0.f;
+        exchange_publish(xchg, (float)s2, (float)c2, (float)s3, (float)count3);
     }
 }
 
@@ -219,6 +220,9 @@ extern "C" int p2c_fused_step(const p2c_fused_step_t* p, void* stream) {
     if (p->n_clips == 0) return 0;
     if (!p->pose_in || !p->ref_loc || !p->gt_2d || !p->gt_3d || !p->g_pose_in || !p->workspace || !p->losses)
         return P2C_E_NULL;
+    if (p->exchange && (p->exchange_world < 1 || p->exchange_world > XCHG_MAX_RANKS || p->exchange_rank < 0 ||
+                        p->exchange_rank >= p->exchange_world || (reinterpret_cast<uintptr_t>(p->exchange) & 15)))
+        return P2C_E_BADARG;
     if (p2c_fused_tile_supported(p)) return p2c_fused_tile(p, stream);
     if (p2c_fused_fast_supported(p)) return p2c_fused_fast(p, stream);
 
@@ -258,7 +262,7 @@ extern "C" int p2c_fused_step(const p2c_fused_step_t* p, void* stream) {
     loss_fwd_kernel<<<(int)blocks, WARPS * 32, 0, st>>>(a);
     P2C_LAUNCH_CHECK();
     p2c_loss_finalize_kernel<<<1, 32, 0, st>>>(partials, (int)blocks, (double)M * B * 3, p->weight_2d, p->weight_3d,
-                                               p->losses);
+                                               p->losses, XchgArgs{p->exchange, p->exchange_rank, p->exchange_world});
     P2C_LAUNCH_CHECK();
     loss_bwd_kernel<<<(int)blocks, WARPS * 32, 0, st>>>(a);
     P2C_LAUNCH_CHECK();

@@ -71,10 +71,16 @@ struct TileArgs {
     int dynamic;           // more tiles than CTAs: tiles beyond a CTA's first are drawn from `next`
     float* losses;
     double count3;
+    XchgArgs xchg;         // data-parallel ranks: where the finishing thread publishes the four loss sums
 };
 
 // MUFU approximations (rel. error ~2^-22, well inside the 1e-4 parity bar); ftz only touches denormals, which the
 // clamps below keep out of rsqrt and which make no difference to 1/z or the hips-neck scale
+#ifdef P2C_IEEE_MATH   // experiment build (tools/variants.py): correctly rounded division and square root
+__device__ __forceinline__ float frcp(float x) { return __fdiv_rn(1.f, x); }
+__device__ __forceinline__ float frsqrt(float x) { return __fdiv_rn(1.f, __fsqrt_rn(x)); }
+__device__ __forceinline__ float fsqrt(float x) { return __fsqrt_rn(x); }
+#else
 __device__ __forceinline__ float frcp(float x) {
     float r;
     asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
@@ -90,6 +96,12 @@ __device__ __forceinline__ float fsqrt(float x) {
     asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
 }
+#endif
+#ifdef P2C_SUMS_DOUBLE   // experiment build: the running values of the subtree-sum walks in double
+typedef double acc_t;
+#else
+typedef float acc_t;
+#endif
 
 struct GS {
     V3 b1, b2, b3;
@@ -449,6 +461,7 @@ struct FoldArgs {   // (by value: a reference to the kernel parameters would for
     double count3, all2;
     float w2, w3;
     int mask;
+    XchgArgs xchg;
 };
 __device__ __noinline__ void finish_losses(const FoldArgs a, double d2, double d3) {   // one thread
     const double c2 = a.mask ? (double)__ldcg(reinterpret_cast<const int*>(a.header) + 2) : a.all2;
@@ -456,6 +469,7 @@ __device__ __noinline__ void finish_losses(const FoldArgs a, double d2, double d
     a.losses[0] = l2; a.losses[1] = l3; a.losses[2] = a.w2 * l2 + a.w3 * l3;
     a.losses[3] = (float)d2; a.losses[4] = (float)c2; a.losses[5] = (float)d3; a.losses[6] = (float)a.count3;
     a.losses[7] = 0.f;
+    exchange_publish(a.xchg, (float)d2, (float)c2, (float)d3, (float)a.count3);
     a.header[0] = 0u;   // self-resetting workspace header: ready for the next launch
     a.header[2] = 0u;
     a.header[3] = 0u;
@@ -570,6 +584,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         FoldArgs f;
         f.losses = a.losses; f.partials = a.partials; f.header = a.ticket;
         f.count3 = a.count3; f.all2 = (double)total * B * 2; f.w2 = a.w2; f.w3 = a.w3; f.mask = a.mask;
+        f.xchg = a.xchg;
         return f;
     };
     auto finish = [&](double d2, double d3) { finish_losses(fold_args(), d2, d3); };
@@ -1059,10 +1074,10 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 const int grp = warp / 3, k = warp - 3 * grp;
                 float* rx = XR + k * PS + lane;
                 float* rg = GV + k * PS + lane;
-                float cx = 0.f, cg = 0.f;
+                acc_t cx = 0.f, cg = 0.f;
 #define P2C_SUMS(HI, LO)                                                                      \
     _Pragma("unroll") for (int c = HI; c >= LO; --c) {                                        \
-        float vx = rx[c * 3 * PS], vg = rg[c * 3 * PS];                                       \
+        acc_t vx = rx[c * 3 * PS], vg = rg[c * 3 * PS];                                       \
         bool changed = false;                                                                 \
         if (c + 1 <= HI && carla_parent(c + 1) == c) { vx += cx; vg += cg; changed = true; }  \
         if (LO == 0 && c == 3) {                                                              \
@@ -1074,10 +1089,11 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             vx += rx[16 * 3 * PS] + rx[21 * 3 * PS];                                          \
             vg += rg[16 * 3 * PS] + rg[21 * 3 * PS];                                          \
         }                                                                                     \
-        if (changed || (LO == 0 && (c == 3 || c == 1))) { rx[c * 3 * PS] = vx; rg[c * 3 * PS] = vg; } \
+        if (changed || (LO == 0 && (c == 3 || c == 1))) { rx[c * 3 * PS] = (float)vx; rg[c * 3 * PS] = (float)vg; } \
         if (c > LO) {                                                                         \
             if (carla_parent(c) == c - 1) { cx = vx; cg = vg; }                               \
-            else { rx[carla_parent(c) * 3 * PS] += vx; rg[carla_parent(c) * 3 * PS] += vg; }  \
+            else { rx[carla_parent(c) * 3 * PS] = (float)(rx[carla_parent(c) * 3 * PS] + vx);   \
+                   rg[carla_parent(c) * 3 * PS] = (float)(rg[carla_parent(c) * 3 * PS] + vg); } \
         }                                                                                     \
     }
                 if (grp == 0) {
@@ -1095,18 +1111,18 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             const int k = warp % 6, col = (warp / 6) * 32 + lane;
             float* rowp = (k < 3 ? XR + k * PS : GV + (k - 3) * PS) + col;
             if (BT == 26) {
-                float carry = 0.f;
+                acc_t carry = 0.f;
 #pragma unroll
                 for (int c = 25; c >= 0; --c) {
                     const bool have = c + 1 < 26 && carla_parent(c + 1) == c;   // the next bone is this one's child
-                    float v = rowp[c * 3 * PS];
+                    acc_t v = rowp[c * 3 * PS];
                     if (have) {
                         v += carry;
-                        rowp[c * 3 * PS] = v;
+                        rowp[c * 3 * PS] = (float)v;
                     }
                     if (c > 0) {
                         if (carla_parent(c) == c - 1) carry = v;
-                        else rowp[carla_parent(c) * 3 * PS] += v;
+                        else rowp[carla_parent(c) * 3 * PS] = (float)(rowp[carla_parent(c) * 3 * PS] + v);
                     }
                 }
             } else {
@@ -1370,6 +1386,7 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     // (p2c_fused_step_workspace_floats: 16 header words, then >= 6 * n_bones * n_poses floats of scratch)
     a.partials = p->workspace + 16;
     a.losses = p->losses;
+    a.xchg = XchgArgs{p->exchange, p->exchange_rank, p->exchange_world};
     const long total = (long)p->n_clips * p->clip_len;
     a.count3 = (double)total * B * 3;
     cudaStream_t st = (cudaStream_t)stream;

@@ -3,6 +3,8 @@
 PyTorch here is plumbing only (device memory, streams, autograd graph); every forward and
 backward below is a hand-written sm_100a kernel.  There is no CPU fallback: CPU tensors raise.
 """
+import ctypes as C
+
 import torch
 
 from . import _lib
@@ -336,6 +338,68 @@ def masked_mse(pred, gt, c_used, mask_hips=-1):
     return _MaskedMSE.apply(pred, gt, c_used, mask_hips)
 
 
+class _Loc2dStep(torch.autograd.Function):
+    """Loc2DPoseLoss forward + its gradient in one cooperative launch (p2c_loc2d_step): the autoencoder flow's step
+    (modules/flow/autoencoder.py:102-112, loss/loc_2d.py:69-89).  backward only scales the stored gradient."""
+
+    @staticmethod
+    def forward(ctx, pred, gt, mask_hips, exchange, out):
+        lib = _lib.load()
+        j = pred.shape[-2]
+        m = pred.numel() // (j * 2)
+        out = out or {}
+        g = out.get('g_pred') if out.get('g_pred') is not None else torch.empty_like(pred)
+        ws = out.get('workspace')
+        if ws is None:
+            ws = _loc2d_workspace(pred.device)
+        res = out.get('losses') if out.get('losses') is not None else torch.empty(4, device=pred.device)
+        xb, xr, xw = (C.c_void_p(exchange.block), exchange.rank, exchange.world) if exchange is not None else (None, 0, 0)
+        check(lib.p2c_loc2d_step(ptr(pred), ptr(gt), m, j, gt.shape[-1], mask_hips, 1.0, ptr(g), ptr(ws), ptr(res), xb, xr,
+                                 xw, stream()), 'loc2d_step')
+        if exchange is not None:
+            exchange.steps += 1
+        ctx.save_for_backward(g)
+        return res[0].clone(), res
+
+    @staticmethod
+    def backward(ctx, g_loss, _):
+        (g,) = ctx.saved_tensors
+        return g * g_loss, None, None, None, None
+
+
+_LOC2D_WS = {}
+
+
+def _loc2d_workspace(dev):
+    key = (dev.type, dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    ws = _LOC2D_WS.get(key)
+    if ws is None:
+        ws = torch.zeros(int(_lib.load().p2c_loc2d_step_workspace_floats()), device=dev)
+        _LOC2D_WS[key] = ws
+    return ws
+
+
+def loc2d_loss(pred, gt, mask_hips=-1, exchange=None, out=None, with_sums=False):
+    """loc_2d of (..., J, >=2) predictions against (..., J, >=2) targets over the first two channels (mask_hips < 0: no
+    missing-joints mask).  Contiguous 2-channel predictions that want a gradient take the one-launch fused
+    forward + backward (p2c_loc2d_step); everything else the two-stage reduction with its separate backward."""
+    p = pred
+    fused = (p.is_cuda and p.dtype == torch.float32 and p.shape[-1] == 2 and p.is_contiguous() and p.requires_grad
+             and p.numel() > 0 and p.data_ptr() % 16 == 0)
+    if fused:
+        g = _gt2_records(gt.detach())
+        if g.shape[-1] not in (2, 3) or g.data_ptr() % (16 if g.shape[-1] == 2 else 8) != 0:
+            fused = False
+    if fused:
+        j = p.shape[-2]
+        fused = bool(_lib.load().p2c_loc2d_step_supported(p.numel() // (j * 2), j, g.shape[-1]))
+    if not fused:
+        loss = masked_mse(pred, gt, 2, mask_hips)
+        return (loss, None) if with_sums else loss
+    loss, sums = _Loc2dStep.apply(p, g, mask_hips, exchange, out)
+    return (loss, sums) if with_sums else loss
+
+
 class _CumChanges(torch.autograd.Function):
     """Per-bone cumulative product of pose changes over frames (loss/cum_pose_changes.py:26-48)."""
 
@@ -492,7 +556,8 @@ class _FusedStep(torch.autograd.Function):
                bool(cfg.get('want_transformed', True)), id(cfg['tree']), id(cfg['camera']),
                cfg['ref_loc'].data_ptr(), cfg['ref_rot'].data_ptr(),
                None if cfg.get('world_loc') is None else cfg['world_loc'].data_ptr(),
-               None if cfg.get('world_rot') is None else cfg['world_rot'].data_ptr(), _lib.raw_stream())
+               None if cfg.get('world_rot') is None else cfg['world_rot'].data_ptr(), _lib.raw_stream(),
+               None if cfg.get('exchange') is None else cfg['exchange'].block)
         plan = out.get('_plan')
         if plan is not None and plan[0] == key:
             _, a, rel_rot, abs_rot, abs_loc, proj, proj_norm, g_in, losses, keep = plan
@@ -511,6 +576,8 @@ class _FusedStep(torch.autograd.Function):
             a.world_loc, a.world_rot, a.camera = ptr(world_loc), ptr(world_rot), cfg['camera']
             a.gt_2d, a.gt_2d_channels, a.gt_3d = ptr(gt2), gt2.shape[-1], ptr(gt3)
             a.weight_2d, a.weight_3d = float(cfg.get('weight_2d', 1.0)), float(cfg.get('weight_3d', 1.0))
+            if cfg.get('exchange') is not None:
+                cfg['exchange'].attach(a)
             rel_rot = out.get('rel_rot') if out.get('rel_rot') is not None else torch.empty((N, L, B, 3, 3), device=dev)
             abs_rot = out.get('abs_rot') if out.get('abs_rot') is not None else torch.empty((N, L, B, 3, 3), device=dev)
             abs_loc = out.get('abs_loc') if out.get('abs_loc') is not None else torch.empty((N, L, B, 3), device=dev)
@@ -534,6 +601,8 @@ class _FusedStep(torch.autograd.Function):
                 out['_plan'] = (key, a, rel_rot, abs_rot, abs_loc, proj, proj_norm, g_in, losses,
                                 (ws, ref_loc, ref_rot, world_loc, world_rot, cfg['tree'], cfg['camera']))
         check(lib.p2c_fused_step(a, stream()), 'fused_step')
+        if cfg.get('exchange') is not None:
+            cfg['exchange'].steps += 1
         # fresh tensor objects over the (possibly preallocated, reused) buffers: autograd attaches this call's node to
         # the objects it is handed
         o_rel, o_absr, o_absl, o_proj = rel_rot.detach(), abs_rot.detach(), abs_loc.detach(), proj.detach()
@@ -616,17 +685,18 @@ def fused_step_buffers(n_clips, clip_len, n_bones, device, input_6d=True, transf
 
 def fused_step(pose_in, tree, camera, ref_loc, ref_rot, gt_2d, gt_3d, ref_index=None, world_loc=None, world_rot=None,
                mode=_lib.MODE_POSE_CHANGES, hips=1, neck=8, normalize=True, mask_missing_joints=True, weight_2d=1.0,
-               weight_3d=1.0, want_transformed=True, out=None):
+               weight_3d=1.0, want_transformed=True, out=None, exchange=None):
     """One pose_lifting step of the hot path in one call.  pose_in: (N,L,B,6) rotation_6d model output or
     (N,L,B,3,3) matrices.  Returns FusedStepResult; .loc_2d_3d (= weight_2d*loc_2d + weight_3d*loc_3d) and the module
     tensors (.relative_pose_rot, .absolute_pose_rot, .absolute_pose_loc, .projection_2d, .projection_2d_transformed)
     carry autograd edges back to pose_in (.loc_2d / .loc_3d are reported values).  `out` may hold preallocated
     buffers (CUDA-graph friendly; the outputs of step i are then overwritten by step i+1, so any extra loss on them
-    must be back-propagated before the next call)."""
+    must be back-propagated before the next call).  `exchange`: a LossExchange (exchange.py) -- the step then also
+    publishes its four loss sums to every data-parallel rank."""
     cfg = dict(tree=tree, camera=camera, ref_loc=ref_loc, ref_rot=ref_rot, gt_2d=gt_2d, gt_3d=gt_3d,
                ref_index=ref_index, world_loc=world_loc, world_rot=world_rot, mode=mode, hips=hips, neck=neck,
                normalize=normalize, mask_missing_joints=mask_missing_joints, weight_2d=weight_2d,
-               weight_3d=weight_3d, want_transformed=want_transformed, out=out)
+               weight_3d=weight_3d, want_transformed=want_transformed, out=out, exchange=exchange)
     l2, l3, l23, rel_rot, abs_rot, abs_loc, proj, proj_norm = _FusedStep.apply(pose_in, cfg)
     res = cfg['_result']
     res.loc_2d, res.loc_3d, res.loc_2d_3d, res.pose_in = l2, l3, l23, pose_in

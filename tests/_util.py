@@ -5,21 +5,75 @@ import torch
 import oracle as O
 
 REL_TOL = 1e-4  # BASELINE.json north_star: 1e-4 relative in fp32 for locations, projections, loss, gradients
+FP32_SLACK = 3.0  # gradient groups may be this many times further from fp64 than the fp32 reference evaluation is
 
 
-def scaled_err(got, ref):
+def _pair(got, ref):
     got = torch.as_tensor(np.asarray(got.detach().cpu() if torch.is_tensor(got) else got)).double()
     ref = torch.as_tensor(np.asarray(ref.detach().cpu() if torch.is_tensor(ref) else ref)).double()
     assert got.shape == ref.shape, (got.shape, ref.shape)
+    return got, ref
+
+
+def scaled_err(got, ref):
+    """max|got - ref| / max|ref| over the WHOLE tensor (kept for scalars and bit-level property checks)."""
+    got, ref = _pair(got, ref)
     if ref.numel() == 0:
         return 0.0
     return float((got - ref).abs().max() / max(float(ref.abs().max()), 1e-12))
 
 
-def assert_close(name, got, ref, tol=REL_TOL):
-    """|got - ref| <= tol * max|ref| (scale-relative: fp32 cannot hold an elementwise 1e-4 on near-zero entries)."""
-    e = scaled_err(got, ref)
-    assert e <= tol, '%s: scaled max error %.3e > %.1e' % (name, e, tol)
+def group_err(got, ref, keep):
+    """max|got - ref| / max|ref| per group: both maxima over every axis NOT in `keep`.  Returns a tensor shaped like
+    the kept axes (groups whose reference is identically zero report their absolute error)."""
+    got, ref = _pair(got, ref)
+    red = [a for a in range(ref.dim()) if a not in keep]
+    err = (got - ref).abs()
+    scale = ref.abs()
+    if red:
+        err, scale = err.amax(dim=red), scale.amax(dim=red)
+    return err / scale.clamp_min(1e-300).where(scale > 0, torch.ones_like(scale))
+
+
+def _layout(ref):
+    """(channel axes, bone axis) of the path's tensors: (..., B, C) records or (..., B, 3, 3) matrices."""
+    d = ref.dim()
+    if d >= 3 and tuple(ref.shape[-2:]) == (3, 3):
+        return (d - 2, d - 1), (d - 3 if d >= 4 else None)
+    if d >= 2:
+        return (d - 1,), (d - 2 if d >= 3 else None)
+    return (), None
+
+
+def close_report(got, ref, tol=REL_TOL, floor=1e-2):
+    """Per-CHANNEL and per-BONE comparison (reference tests/walker_control/test_pose.py:31-52 compares bone by bone):
+    every (bone, channel) group must satisfy  max|got - ref| <= tol * max(scale(bone, channel), floor * scale(channel)),
+    scales being max|ref| over the group / over the whole channel.  Channels are never mixed (pixels ~400 next to
+    1/z ~0.3 in projection_2d; a trunk bone's gradient next to a finger's), and `floor` only keeps a bone whose values
+    are ~0 by construction (root / hips location, a lateral coordinate of the spine) from being held to 1e-4 of
+    rounding noise.  Returns (worst ratio err / allowed, where)."""
+    got, ref = _pair(got, ref)
+    if ref.numel() == 0:
+        return 0.0, None
+    chan, bone = _layout(ref)
+    err, mag = (got - ref).abs(), ref.abs()
+    keep_bc = tuple(chan) + ((bone,) if bone is not None else ())
+    red_bc = [a for a in range(ref.dim()) if a not in keep_bc]
+    red_c = [a for a in range(ref.dim()) if a not in chan]
+    e = err.amax(dim=red_bc, keepdim=True) if red_bc else err
+    s_bc = mag.amax(dim=red_bc, keepdim=True) if red_bc else mag
+    s_c = mag.amax(dim=red_c, keepdim=True) if red_c else mag
+    allowed = tol * torch.maximum(s_bc, floor * s_c).clamp_min(1e-300)
+    ratio = e / allowed
+    worst = float(ratio.max())
+    idx = np.unravel_index(int(ratio.argmax()), ratio.shape)
+    return worst, tuple(int(i) for i in idx)
+
+
+def assert_close(name, got, ref, tol=REL_TOL, floor=1e-2):
+    """See close_report: tol relative to the scale of each (bone, channel) group, not of the whole tensor."""
+    worst, where = close_report(got, ref, tol, floor)
+    assert worst <= 1.0, '%s: error is %.2f x the allowed %.1e of the group scale at group %s' % (name, worst, tol, where)
 
 
 def carla(dtype=torch.float64):
@@ -92,11 +146,25 @@ def cast_case(c, dtype):
     return d
 
 
-def assert_close_fp32_aware(name, got, ref64, ref32, tol=REL_TOL, slack=3.0):
-    """Gradients of the trunk bones are sums of large cancelling terms: the reference's own float32 evaluation
-    deviates from float64 by ~1e-4 of the gradient scale there.  The CUDA path must be within `tol` of the float64
-    oracle, or no further from it than `slack` x the float32 oracle (= the reference PyTorch path in fp32) is."""
-    e = scaled_err(got, ref64)
-    e32 = scaled_err(ref32, ref64)
-    assert e <= max(tol, slack * e32), '%s: scaled max error %.3e > max(%.1e, %.1f x fp32-reference error %.3e)' % (
-        name, e, tol, slack, e32)
+def assert_close_fp32_aware(name, got, ref64, ref32, tol=REL_TOL, slack=FP32_SLACK):
+    """Gradients of the trunk bones are sums of large cancelling terms (all later frames x all descendants): the
+    reference's own float32 evaluation deviates from float64 by ~1e-4 of the bone's gradient scale there.  Per bone and
+    channel group (close_report), the CUDA path must be within `tol` of the float64 oracle, or no further from it than
+    `slack` x the float32 oracle (= the reference PyTorch path in fp32) is IN THE SAME GROUP."""
+    got, ref64 = _pair(got, ref64)
+    ref32 = _pair(ref32, ref64)[0]
+    chan, bone = _layout(ref64)
+    keep = tuple(chan) + ((bone,) if bone is not None else ())
+    red = [a for a in range(ref64.dim()) if a not in keep]
+    red_c = [a for a in range(ref64.dim()) if a not in chan]
+    mag = ref64.abs()
+    s_bc = mag.amax(dim=red, keepdim=True) if red else mag
+    s_c = mag.amax(dim=red_c, keepdim=True) if red_c else mag
+    scale = torch.maximum(s_bc, 1e-2 * s_c).clamp_min(1e-300)
+    e = ((got - ref64).abs().amax(dim=red, keepdim=True) if red else (got - ref64).abs()) / scale
+    e32 = ((ref32 - ref64).abs().amax(dim=red, keepdim=True) if red else (ref32 - ref64).abs()) / scale
+    bad = e > torch.maximum(torch.full_like(e, tol), slack * e32)
+    if bool(bad.any()):
+        i = np.unravel_index(int((e / torch.maximum(torch.full_like(e, tol), slack * e32)).argmax()), e.shape)
+        raise AssertionError('%s: group %s: scaled error %.3e > max(%.1e, %.1f x fp32-reference error %.3e)' % (
+            name, tuple(int(v) for v in i), float(e[i]), tol, slack, float(e32[i])))

@@ -228,3 +228,38 @@ def test_masked_mse(ops, mask):
     assert_close('loc_2d bwd', ca.grad, a.grad)
     # loc_3d: plain MSE over 3 channels
     assert_close('loc_3d', ops.masked_mse(cu(pred), cu(gt), 3, -1), O.loss_loc_3d(pred, gt))
+
+
+@pytest.mark.parametrize('shape,c_gt,mask', [((256, 16, 26), 2, True), ((7, 3, 26), 3, True), ((5, 1, 25), 2, False),
+                                             ((8192, 16, 26), 2, True), ((1, 1, 1), 2, True)])
+def test_loc2d_step_fused_forward_backward(ops, shape, c_gt, mask):
+    """p2c_loc2d_step (the autoencoder flow's step, BASELINE configs[2]): loss and gradient of Loc2DPoseLoss from one
+    cooperative launch against the oracle's value and autograd; odd joint counts, 3-channel target records, mask off."""
+    g = torch.Generator().manual_seed(sum(shape) + c_gt)
+    pred = torch.randn(shape + (2,), generator=g, dtype=torch.float64)
+    gt = torch.randn(shape + (c_gt,), generator=g, dtype=torch.float64)
+    gt[torch.rand(shape, generator=g) < 0.15] = 0
+    hips = 1 % shape[-1]
+    p64 = pred.clone().requires_grad_(True)
+    want = O.loss_loc_2d(p64, gt, mask, hips)
+    (3.0 * want).backward()
+    x = cu(pred).requires_grad_(True)
+    loss, sums = ops.loc2d_loss(x, cu(gt), hips if mask else -1, with_sums=True)
+    assert sums is not None, 'the fused kernel declined a shape it should take'
+    (3.0 * loss).backward()
+    assert_close('loc_2d', loss, want)
+    assert_close('grad', x.grad, p64.grad)
+    kept = O.missing_joints_mask(gt[..., :2], hips) if mask else torch.ones(shape, dtype=torch.bool)
+    assert float(sums[2]) == float(2 * kept.sum())
+    again, _ = ops.loc2d_loss(cu(pred).requires_grad_(True), cu(gt), hips if mask else -1, with_sums=True)
+    assert torch.equal(again, loss)     # fixed grid, fixed order: bitwise repeatable
+
+
+def test_loc2d_step_declines_what_it_cannot_hold(ops):
+    """No gradient wanted, 3-channel predictions: the two-stage kernels; same value."""
+    g = torch.Generator().manual_seed(12)
+    pred = torch.randn((9, 4, 26, 3), generator=g, dtype=torch.float64)
+    gt = torch.randn((9, 4, 26, 3), generator=g, dtype=torch.float64)
+    loss, sums = ops.loc2d_loss(cu(pred).requires_grad_(True), cu(gt), 1, with_sums=True)
+    assert sums is None
+    assert_close('loc_2d', loss, O.loss_loc_2d(pred, gt, True, 1))

@@ -343,6 +343,37 @@ def test_bbox_extractors_against_reference_golden(api, gold):
     assert_close('== hips_neck', N(HipsNeckBBoxFallbackExtractor())(y), N()(y), 1e-6)
 
 
+def test_normalizer_reports_shift_and_scale(api, gold):
+    """Normalizer.shift / .scale after a call (reference normalizer.py:39-49, read by projection_2d_mixin.py:229-230)
+    for the three extractors, incl. undetected hips / neck / whole frames (NaN / inf scales compare as such)."""
+    from pedestrians_video_2_carla_b200.transforms.pose.normalization.bbox_extractor import BBoxExtractor
+    from pedestrians_video_2_carla_b200.transforms.pose.normalization.hips_neck_bbox_fallback_extractor import \
+        HipsNeckBBoxFallbackExtractor
+    N = api['Normalizer']
+    x = gold['ext/x']
+    for name, ext in (('hips_neck', None), ('bbox', BBoxExtractor()), ('hips_neck_bbox', HipsNeckBBoxFallbackExtractor())):
+        n = N(ext) if ext is not None else N()
+        with pytest.raises(RuntimeError):
+            n.scale
+        n(x.to(DEV))
+        shift, scale = O.extractor_shift_scale(x.double(), name)
+        got_shift, got_scale = n.shift.double().cpu(), n.scale.double().cpu()
+        assert got_shift.shape == shift.shape and got_scale.shape == scale.shape
+        fin = torch.isfinite(scale)
+        assert torch.equal(torch.isfinite(got_scale), fin), name
+        assert_close(name + ' scale', got_scale[fin], scale[fin])
+        fs = torch.isfinite(shift).all(-1)
+        assert torch.equal(torch.isfinite(got_shift).all(-1), fs), name
+        assert_close(name + ' shift', got_shift[fs], shift[fs])
+    # dim = 3 (absolute locations): hips / neck over three channels
+    x3 = gold['den/x3'].to(DEV)
+    n3 = N()
+    n3(x3, dim=3)
+    s3, c3 = O.get_shift_scale(gold['den/x3'].double())
+    assert_close('shift dim3', n3.shift, s3)
+    assert_close('scale dim3', n3.scale, c3.reshape(n3.scale.shape))
+
+
 def test_device_target_generator(api):
     """Carla2D3DIterableDataset.generate_batch on the device: the distribution's invariants and, given the drawn Euler
     changes, parity of every target with the oracle's ProjectionModule / Normalizer."""

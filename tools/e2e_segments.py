@@ -12,7 +12,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import bench  # noqa: E402
 
 dev = torch.device('cuda', 0)
-sh = bench.Shard(dev, 256, 16, 1, want_bytes=1, max_sets=2, capture=False)
+sh = bench.FusedShard(dev, 256, 16, 1, want_bytes=1, max_sets=2)
 ops = sh.ops
 s = sh.sets[0]
 v = {k: s[k].clone() for k in ('d6', 'gt2', 'gt3', 'sid')}

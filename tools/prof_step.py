@@ -7,7 +7,7 @@ import bench
 n, l = int(sys.argv[1]), int(sys.argv[2])
 iters = int(sys.argv[3]) if len(sys.argv) > 3 else 5
 dev = torch.device('cuda', 0)
-sh = bench.Shard(dev, n, l, 1, want_bytes=1, max_sets=2, capture=False)
+sh = bench.FusedShard(dev, n, l, 1, want_bytes=1, max_sets=2)
 for k in os.environ.get('P2C_PROF_DROP', '').split(','):   # experiment: drop outputs (rel_rot,abs_rot,abs_loc,proj)
     if k:
         for st in sh.sets:

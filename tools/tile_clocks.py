@@ -8,7 +8,7 @@ import torch
 import bench
 from pedestrians_video_2_carla_b200 import _lib
 n, l = int(sys.argv[1]), int(sys.argv[2])
-sh = bench.Shard(torch.device('cuda', 0), n, l, 1, want_bytes=1, max_sets=2, capture=False)
+sh = bench.FusedShard(torch.device('cuda', 0), n, l, 1, want_bytes=1, max_sets=2)
 for i in range(3):
     sh.launch(i)
 torch.cuda.synchronize()
