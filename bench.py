@@ -115,8 +115,8 @@ class ClockSampler(object):
 # ------------------------------------------------------------------------------------------ the b200 arm
 class GraphedSteps(object):
     """Steps over `n_sets` rotating buffer sets (their footprint together exceeds L2, so every timed step streams from
-    HBM), replayed as CUDA graphs.  ANY step count runs the same way: whole rounds (one graph = n_sets consecutive
-    steps, one per buffer set) plus one graph holding the remaining steps; inside a graph consecutive steps chain
+    HBM), replayed as CUDA graphs.  ANY step count runs the same way: one graph holds the steps back to back (cycling
+    through the buffer sets; long runs are cut into graphs of CHUNK steps); inside a graph consecutive steps chain
     through programmatic dependent launch where the kernel supports it.  Nothing but the step's own kernels is ever
     on the stream: no collective, no host work between steps."""
 
@@ -144,21 +144,21 @@ class GraphedSteps(object):
             cache[count] = g
         return cache[count]
 
+    CHUNK = 240   # steps per graph for long runs (a multiple of every n_sets used here: 2, 3, 4, 12, 16 -> 240)
+
+    def _plan(self, count):
+        """Graph sizes whose replays make `count` steps: chunks of CHUNK steps, then ONE graph with the rest, so any
+        step count (the driver's 20 as well as 400) is a handful of graph launches of back-to-back chained steps."""
+        return [self.CHUNK] * (count // self.CHUNK) + ([count % self.CHUNK] if count % self.CHUNK else [])
+
     def prepare(self, count):
         """Capture (untimed) every graph run_steps(count) replays."""
-        if count >= self.n_sets:
-            self._graph(self.n_sets)
-        if count % self.n_sets:
-            self._graph(count % self.n_sets)
+        for c in set(self._plan(count)):
+            self._graph(c)
 
     def run_steps(self, count):
-        rounds, rest = divmod(count, self.n_sets)
-        if rounds:
-            g = self._graph(self.n_sets)
-            for _ in range(rounds):
-                g.replay()
-        if rest:
-            self._graph(rest).replay()
+        for c in self._plan(count):
+            self._graph(c).replay()
 
     def drop_graphs(self):
         self.__dict__.pop('_graphs', None)
@@ -569,8 +569,7 @@ def main():
     note = 'timed region'
     if ms < 400.0:   # microsecond steps: keep the same load running until NVML has been polled enough (the number
         # of extra rounds comes from the max-reduced time, so every rank does the same)
-        rounds = int(400.0 / max(ms / args.steps * shard.n_sets, 1e-3)) + 1
-        shard.run_steps(rounds * shard.n_sets)
+        shard.run_steps((int(400.0 / max(ms / args.steps, 1e-4)) // shard.CHUNK + 1) * shard.CHUNK)
         torch.cuda.synchronize()
         note = 'timed region + the same step loop continued for ~0.4 s (region shorter than the NVML poll)'
     sampler.stop()
@@ -705,16 +704,42 @@ def separate_ops_step(dev, args, steps=20, warm=5):
     for _ in range(warm):
         one()
     torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(steps):
-        one()
-    e1.record()
-    torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / steps
-    return {'config': 'module-API step (separate ops: rot6d -> ProjectionModule.forward -> Normalizer -> loc_2d + loc_3d '
-                      '-> autograd backward), %dx%d, eager' % (n, l), 'ms_per_step': round(ms, 5),
-            'poses_per_s': round(n * l / (ms * 1e-3), 1)}
+
+    def timed(fn):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / steps
+    eager_ms = timed(one)
+    out = {'config': 'module-API step (separate ops: rot6d -> ProjectionModule.forward -> Normalizer -> loc_2d + loc_3d '
+                     '-> autograd backward), %dx%d' % (n, l), 'eager_ms_per_step': round(eager_ms, 5),
+           'eager_note': 'host-bound: ~25 autograd nodes / allocator calls per step'}
+    try:   # the same step as ONE CUDA graph (forward + autograd backward captured): the device time of its kernels
+        side = torch.cuda.Stream(dev)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                one()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        x.grad = None
+        with torch.cuda.graph(graph):
+            one()
+        torch.cuda.synchronize()
+        for _ in range(warm):
+            graph.replay()
+        torch.cuda.synchronize()
+        ms = timed(graph.replay)
+        out.update(ms_per_step=round(ms, 5), poses_per_s=round(n * l / (ms * 1e-3), 1),
+                   timing='one CUDA graph per step (device time of the step\'s kernels), CUDA events')
+    except Exception as e:   # noqa: BLE001
+        out.update(ms_per_step=round(eager_ms, 5), poses_per_s=round(n * l / (eager_ms * 1e-3), 1),
+                   timing='eager (graph capture failed: %r)' % (e,))
+    return out
 
 
 if __name__ == '__main__':

@@ -24,7 +24,7 @@ __all__ = [
     'projection_module_forward', 'hips_neck_normalize', 'missing_joints_mask', 'loss_loc_2d',
     'loss_loc_3d', 'loss_loc_2d_3d', 'full_step', 'HIPS', 'NECK',
     'normalize', 'get_shift_scale', 'denormalize', 'reference_denormalize', 'cumulative_changes', 'loss_rot_3d',
-    'quaternion_to_matrix', 'normalize_with_extractor', 'metric_mpjpe', 'metric_mrpe', 'metric_pck', 'get_bboxes', 'loss_cum_pose_changes', 'loss_pose_changes', 'loss_weighted_loc_2d_loc_rot_3d', 'abs_from_abs_loc',
+    'quaternion_to_matrix', 'normalize_with_extractor', 'extractor_shift_scale', 'metric_mpjpe', 'metric_mrpe', 'metric_pck', 'get_bboxes', 'loss_cum_pose_changes', 'loss_pose_changes', 'loss_weighted_loc_2d_loc_rot_3d', 'abs_from_abs_loc',
 ]
 
 FILES_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), '..',

@@ -417,6 +417,10 @@ int grid_for_warps(long units) {
 
 }  // namespace
 
+// the pose-per-lane tile kernels (fk_tile.cu): preferred whenever they take the call
+extern "C" int p2c_fk_tile_fwd(const p2c_fk_fwd_t* p, void* stream, int* rc);
+extern "C" int p2c_fk_tile_bwd(const p2c_fk_bwd_t* p, void* stream, int* rc);
+
 extern "C" int p2c_fk_fwd(const p2c_fk_fwd_t* p, void* stream) {
     if (!p) return P2C_E_NULL;
     FkArgs a{};
@@ -432,6 +436,12 @@ extern "C" int p2c_fk_fwd(const p2c_fk_fwd_t* p, void* stream) {
     a.world_loc = p->world_loc; a.world_rot = p->world_rot; a.cam = p->camera;
     a.rel_rot = p->rel_rot; a.abs_rot = p->abs_rot; a.abs_loc = p->abs_loc; a.proj = p->proj;
     cudaStream_t st = (cudaStream_t)stream;
+    {
+        int trc = 0;
+        const int took = p2c_fk_tile_fwd(p, stream, &trc);
+        if (took < 0) return trc;
+        if (took > 0) return 0;
+    }
     if (p->mode == P2C_MODE_POSE_CHANGES)
         fk_fwd_kernel<true><<<grid_for_warps(a.N), WARPS * 32, 0, st>>>(a);
     else
@@ -465,6 +475,12 @@ extern "C" int p2c_fk_bwd(const p2c_fk_bwd_t* p, void* stream) {
     a.g_pose_in = p->g_pose_in; a.g_ref_rot = p->g_ref_rot; a.g_ref_loc = p->g_ref_loc;
     a.g_world_loc = p->g_world_loc; a.g_world_rot = p->g_world_rot;
     cudaStream_t st = (cudaStream_t)stream;
+    {
+        int trc = 0;
+        const int took = p2c_fk_tile_bwd(p, stream, &trc);
+        if (took < 0) return trc;
+        if (took > 0) return 0;
+    }
     if (p->mode == P2C_MODE_POSE_CHANGES)
         fk_bwd_kernel<true><<<grid_for_warps(a.N), WARPS * 32, 0, st>>>(a);
     else

@@ -285,7 +285,7 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 8 ? 2 : 1)) fast_kernel(
                 c = v3_mul_m(wp, camR);
                 c.x += a.cam.T[0]; c.y += a.cam.T[1]; c.z += a.cam.T[2];
             }
-            const float iz = __fdividef(1.0f, c.z);
+            const float iz = (1.0f / c.z);
             const V3 p{fmaf(-camf * c.x, iz, a.cam.px), fmaf(-camf * c.y, iz, a.cam.py), iz};
             if (act) {
                 m3_to(As + f * slot + lane * 9, A);
@@ -305,7 +305,7 @@ __global__ void __launch_bounds__(WARPS * 32, (WARPS == 8 ? 2 : 1)) fast_kernel(
                 dy = __shfl_sync(FULL_MASK, p.y, a.neck) - sy;
                 const float scale = sqrtf(fmaf(dx, dx, dy * dy));
                 okn = scale > 0.f && scale <= 3.402823466e38f;
-                inv = __fdividef(1.0f, scale);
+                inv = (1.0f / scale);
                 const float rx = (p.x - sx) * inv, ry = (p.y - sy) * inv;
                 lx = fabsf(rx) <= 3.402823466e38f;
                 ly = fabsf(ry) <= 3.402823466e38f;
@@ -698,7 +698,7 @@ __global__ void __launch_bounds__(WARPS * 32, (SLIM ? 4 : (WARPS == 8 ? 2 : 1)))
                 c = v3_mul_m(wp, camR);
                 c.x += a.cam.T[0]; c.y += a.cam.T[1]; c.z += a.cam.T[2];
             }
-            const float iz = __fdividef(1.0f, c.z);
+            const float iz = (1.0f / c.z);
             const V3 p{fmaf(-camf * c.x, iz, a.cam.px), fmaf(-camf * c.y, iz, a.cam.py), iz};
             if (act) {
                 m3_to(As + f * slot + lane * 9, A);
@@ -717,7 +717,7 @@ __global__ void __launch_bounds__(WARPS * 32, (SLIM ? 4 : (WARPS == 8 ? 2 : 1)))
                 dy = __shfl_sync(FULL_MASK, p.y, a.neck) - sy;
                 const float scale = sqrtf(fmaf(dx, dx, dy * dy));
                 okn = scale > 0.f && scale <= 3.402823466e38f;
-                inv = __fdividef(1.0f, scale);
+                inv = (1.0f / scale);
                 const float rx = (p.x - sx) * inv, ry = (p.y - sy) * inv;
                 lx = fabsf(rx) <= 3.402823466e38f;
                 ly = fabsf(ry) <= 3.402823466e38f;

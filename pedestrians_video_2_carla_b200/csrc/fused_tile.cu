@@ -34,6 +34,7 @@
 
 #include "common.cuh"
 #include "host_util.h"
+#include "tile_common.cuh"
 
 namespace {
 
@@ -74,35 +75,6 @@ struct TileArgs {
     XchgArgs xchg;         // data-parallel ranks: where the finishing thread publishes the four loss sums
 };
 
-// MUFU approximations (rel. error ~2^-22, well inside the 1e-4 parity bar); ftz only touches denormals, which the
-// clamps below keep out of rsqrt and which make no difference to 1/z or the hips-neck scale
-#ifdef P2C_IEEE_MATH   // experiment build (tools/variants.py): correctly rounded division and square root
-__device__ __forceinline__ float frcp(float x) { return __fdiv_rn(1.f, x); }
-__device__ __forceinline__ float frsqrt(float x) { return __fdiv_rn(1.f, __fsqrt_rn(x)); }
-__device__ __forceinline__ float fsqrt(float x) { return __fsqrt_rn(x); }
-#else
-__device__ __forceinline__ float frcp(float x) {
-    float r;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-    return r;
-}
-__device__ __forceinline__ float frsqrt(float x) {
-    float r;
-    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-    return r;
-}
-__device__ __forceinline__ float fsqrt(float x) {
-    float r;
-    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
-    return r;
-}
-#endif
-#ifdef P2C_SUMS_DOUBLE   // experiment build: the running values of the subtree-sum walks in double
-typedef double acc_t;
-#else
-typedef float acc_t;
-#endif
-
 struct GS {
     V3 b1, b2, b3;
     float inv1, inv2, s;
@@ -138,47 +110,6 @@ __device__ __forceinline__ void gram_schmidt_bwd_tangent(const GS& r, const V3& 
     out[3] = e3 * r.b3.x;
     out[4] = e3 * r.b3.y;
     out[5] = e3 * r.b3.z;
-}
-
-// 64-bit shared accesses as PTX: the two parity branches of lds9/sts9 read the same nine floats, and with plain
-// float2 casts the optimiser merges them into ONE sequence (keeping one branch's alignment assumption), which
-// faults on the other parity.  Opaque asm keeps the branches apart.
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ float2 lds64(const float* p) {
-    float2 v;
-    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(smem_u32(p)) : "memory");
-    return v;
-}
-__device__ __forceinline__ void sts64(float* p, float x, float y) {
-    asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(smem_u32(p)), "f"(x), "f"(y) : "memory");
-}
-// 9-word bone record b of an AoS pose record (b is warp-uniform at every call site: the parity branch does not diverge)
-// (64-bit accesses: half the wavefronts of scalar ones; the pose stride, 117 x 8 bytes, is conflict free)
-__device__ __forceinline__ M3 lds9(const float* pose, int b) {
-    const float* p = pose + 9 * b;
-    M3 r;
-    if (b & 1) {
-        r.m[0] = p[0];
-        const float2 v0 = lds64(p + 1), v1 = lds64(p + 3), v2 = lds64(p + 5), v3 = lds64(p + 7);
-        r.m[1] = v0.x; r.m[2] = v0.y; r.m[3] = v1.x; r.m[4] = v1.y; r.m[5] = v2.x; r.m[6] = v2.y; r.m[7] = v3.x; r.m[8] = v3.y;
-    } else {
-        const float2 v0 = lds64(p), v1 = lds64(p + 2), v2 = lds64(p + 4), v3 = lds64(p + 6);
-        r.m[0] = v0.x; r.m[1] = v0.y; r.m[2] = v1.x; r.m[3] = v1.y; r.m[4] = v2.x; r.m[5] = v2.y; r.m[6] = v3.x; r.m[7] = v3.y;
-        r.m[8] = p[8];
-    }
-    return r;
-}
-__device__ __forceinline__ void sts9(float* pose, int b, const M3& a) {
-    float* p = pose + 9 * b;
-    if (b & 1) {
-        p[0] = a.m[0];
-        sts64(p + 1, a.m[1], a.m[2]); sts64(p + 3, a.m[3], a.m[4]);
-        sts64(p + 5, a.m[5], a.m[6]); sts64(p + 7, a.m[7], a.m[8]);
-    } else {
-        sts64(p, a.m[0], a.m[1]); sts64(p + 2, a.m[2], a.m[3]);
-        sts64(p + 4, a.m[4], a.m[5]); sts64(p + 6, a.m[6], a.m[7]);
-        p[8] = a.m[8];
-    }
 }
 
 // utils/tensors.py:29-40 count of kept (joint, channel) pairs of the 2-D targets (integer => order independent).
@@ -217,37 +148,6 @@ __global__ void __launch_bounds__(256) tile_count_kernel(const float* __restrict
         if (t) atomicAdd(count, t);
     }
 }
-
-// ---- TMA / mbarrier primitives (cp.async.bulk, sm_90+)
-__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
-    uint32_t ok;
-    asm volatile(
-        "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
-        : "=r"(ok)
-        : "r"(smem_u32(bar)), "r"(parity)
-        : "memory");
-    return ok != 0;
-}
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                     smem_u32(dst)),
-                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
-}
-__device__ __forceinline__ void bulk_s2g(void* dst, const void* src, uint32_t bytes) {
-    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src)), "r"(bytes)
-                 : "memory");
-}
-__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
-__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
-__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // shared-memory plan (floats); every region starts 16-byte aligned (PS is a multiple of 32)
 struct TilePlan {
@@ -359,13 +259,6 @@ __device__ __forceinline__ V3 bone_loss(const TileArgs& a, int b, const V3& t, f
     return V3{fmaf(cx.k3, e.x, gp.x), fmaf(cx.k3, e.y, gp.y), fmaf(cx.k3, e.z, gp.z)};
 }
 
-// CARLA_SKELETON parents (the reference's skeleton table, utils/unreal.py: crl_root, hips, spine, spine01, left arm,
-// neck/head/eyes, right arm, right leg, left leg); folds to a constant in the fully unrolled walks of the BT == 26
-// kernels, which the launcher only picks when the call's tree equals this table
-__host__ __device__ __forceinline__ constexpr int carla_parent(int b) {
-    return b == 0 ? -1 : b == 8 || b == 12 ? 3 : b == 11 ? 9 : b == 16 || b == 21 ? 1 : b - 1;
-}
-
 __device__ long long g_tile_clocks[64];
 __device__ unsigned long long g_cta_times[2 * 1024];   // debug (P2C_TILE_CLOCKS): globaltimer at entry / exit of every CTA
 #ifdef P2C_CLOCKS_BUILD
@@ -388,62 +281,6 @@ __device__ __forceinline__ unsigned long long globaltimer() {
 #define TILE_CLOCK(k)                                                              \
     if (a.clocks && (int)blockIdx.x == a.clock_cta && (int)it == a.clocks - 1 && tid == 0) g_tile_clocks[k] = clock64();
 #endif
-
-__device__ __forceinline__ void named_arrive(int id, int threads) {
-    asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(threads) : "memory");
-}
-__device__ __forceinline__ void named_barrier(int id, int threads) {
-    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
-}
-__device__ __forceinline__ float4 lds128(const float* p) {
-    float4 v;
-    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
-                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-                 : "r"(smem_u32(p))
-                 : "memory");
-    return v;
-}
-__device__ __forceinline__ void sts128(float* p, float x, float y, float z, float w) {
-    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(p)), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
-}
-// 6-word bone record b of a 16-byte aligned AoS pose record (6-D / gradient records): 128 + 64 bits, order by parity
-__device__ __forceinline__ void lds6(const float* pose, int b, float* d) {
-    const float* p = pose + 6 * b;
-    if (b & 1) {
-        const float2 u = lds64(p);
-        const float4 v = lds128(p + 2);
-        d[0] = u.x; d[1] = u.y; d[2] = v.x; d[3] = v.y; d[4] = v.z; d[5] = v.w;
-    } else {
-        const float4 v = lds128(p);
-        const float2 u = lds64(p + 4);
-        d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w; d[4] = u.x; d[5] = u.y;
-    }
-}
-__device__ __forceinline__ void sts6(float* pose, int b, const float* d) {
-    float* p = pose + 6 * b;
-    if (b & 1) {
-        sts64(p, d[0], d[1]);
-        sts128(p + 2, d[2], d[3], d[4], d[5]);
-    } else {
-        sts128(p, d[0], d[1], d[2], d[3]);
-        sts64(p + 4, d[4], d[5]);
-    }
-}
-// 3-word bone record b of an 8-byte aligned AoS pose record (locations, projections, 3-channel targets)
-__device__ __forceinline__ V3 lds3(const float* pose, int b) {
-    const float* p = pose + 3 * b;
-    return V3{p[0], p[1], p[2]};
-}
-__device__ __forceinline__ void sts3(float* pose, int b, const V3& v) {
-    float* p = pose + 3 * b;
-    if (b & 1) {
-        p[0] = v.x;
-        sts64(p + 1, v.y, v.z);
-    } else {
-        sts64(p, v.x, v.y);
-        p[2] = v.z;
-    }
-}
 
 // ---- loss totals (rarely executed, kept out of line: the double-precision divisions are long instruction sequences)
 // draw a ticket with RELEASE semantics (this thread's partial store is ordered before it).  __threadfence() would

@@ -263,3 +263,76 @@ def test_loc2d_step_declines_what_it_cannot_hold(ops):
     loss, sums = ops.loc2d_loss(cu(pred).requires_grad_(True), cu(gt), 1, with_sums=True)
     assert sums is None
     assert_close('loc_2d', loss, O.loss_loc_2d(pred, gt, True, 1))
+
+
+def _fk_reference(c, mats, mode, ups):
+    ins = [t.clone().requires_grad_(True) for t in (mats,)]
+    ref_loc, ref_rot = c['loc'][c['sid']], c['rot'][c['sid']]
+    n, l = c['n'], c['l']
+    wl, wr = O.calculate_world_from_changes((n, l), c['wl'], c['wr'], dtype=torch.float64)
+    if mode == 'pose_changes':
+        rl, rr, al, ar = O.abs_from_pose_changes(ins[0], ref_loc, ref_rot, c['par'])
+    else:
+        rl, rr, al, ar = O.abs_from_relative_rot(ins[0], ref_loc, c['par'])
+    proj = torch.stack([O.project(al[:, i], wl[:, i], wr[:, i], c['cam']) for i in range(l)], 1)
+    loss = (ar * ups[1]).sum() + (al * ups[2]).sum() + (proj * ups[3]).sum() * 1e-3
+    if mode == 'pose_changes':
+        loss = loss + (rr * ups[0]).sum()
+    loss.backward()
+    return dict(rr=rr, ar=ar, al=al, proj=proj, grad=ins[0].grad, wl=wl, wr=wr)
+
+
+@pytest.mark.parametrize('tile', [True, False])
+@pytest.mark.parametrize('mode', ['pose_changes', 'relative_rot'])
+@pytest.mark.parametrize('n,l,tree', [(6, 16, 'carla'), (3, 64, 'carla'), (2, 100, 'carla'), (5, 7, 'carla'), (40, 1, 'carla'),
+                                      (4, 40, 'smpl'), (300, 16, 'carla')])
+def test_fk_module_api_kernels(ops, lib, request, monkeypatch, tile, mode, n, l, tree):
+    """p2c_fk_fwd / p2c_fk_bwd as the reference's module API calls them -- 3x3 matrix input that is NOT a rotation
+    (reference tests/walker_control/test_p3d_pose.py:93-95: rand * 0.8 'changes'), indexed skeleton table, world
+    transform, upstream gradients on every output -- through the pose-per-lane tile kernels (fk_tile.cu: whole clips in
+    the lanes, clips longer than 32 frames walked tile by tile with the scan state carried, odd clip lengths declined to
+    the generic kernels) and, with P2C_DISABLE_FWD_TILE, through the generic warp-per-clip kernels."""
+    if not tile:
+        monkeypatch.setenv('P2C_DISABLE_FWD_TILE', '1')
+    lib.load().p2c_debug_reload_env()
+    request.addfinalizer(lambda: (monkeypatch.undo(), lib.load().p2c_debug_reload_env()))
+    par = None if tree == 'carla' else smpl_parents()
+    c = make_case(n, l, 13 * n + l, par=par)
+    g = c['gen']
+    b = c['b']
+    spread = 0.02 if l > 32 else 0.1      # (products of 100 non-rotations: keep them from exploding)
+    mats = O.rotation_6d_to_matrix(c['d6']) + torch.randn((n, l, b, 3, 3), generator=g, dtype=torch.float64) * spread
+    shapes = ((n, l, b, 3, 3), (n, l, b, 3, 3), (n, l, b, 3), (n, l, b, 3))
+    ups = [torch.randn(s, generator=g, dtype=torch.float64) for s in shapes]
+    ref = _fk_reference(c, mats, mode, ups)
+    x = cu(mats).requires_grad_(True)
+    m = lib.MODE_POSE_CHANGES if mode == 'pose_changes' else lib.MODE_RELATIVE_ROT
+    crr, car, cal, cproj = ops.fk_clip(x, cu(c['loc']), cu(c['rot']) if mode == 'pose_changes' else None,
+                                       c['sid'].int().to(DEV), cu(ref['wl']), cu(ref['wr']), lib.make_tree(c['par']),
+                                       cam_struct(lib, c['cam']), m, True)
+    closs = (car * cu(ups[1])).sum() + (cal * cu(ups[2])).sum() + (cproj * cu(ups[3])).sum() * 1e-3
+    if mode == 'pose_changes':
+        closs = closs + (crr * cu(ups[0])).sum()
+        assert_close('rel_rot', crr, ref['rr'])
+    closs.backward()
+    assert_close('abs_rot', car, ref['ar'])
+    assert_close('abs_loc', cal, ref['al'])
+    assert_close('proj', cproj, ref['proj'])
+    assert_close('g_pose_in', x.grad, ref['grad'])
+
+
+def test_fk_tile_partial_upstream_and_no_projection(ops, lib):
+    """Only some outputs carry an upstream gradient (the usual case: loc_3d alone, or rot_3d alone); no projection."""
+    c = make_case(10, 16, 321, world=False)
+    mats = O.rotation_6d_to_matrix(c['d6'])
+    for which in ('loc', 'rot'):
+        m64 = mats.clone().requires_grad_(True)
+        _, rr, al, ar = O.abs_from_pose_changes(m64, c['loc'][c['sid']], c['rot'][c['sid']], c['par'])
+        ((al ** 2).sum() if which == 'loc' else (ar ** 3).sum()).backward()
+        x = cu(mats).requires_grad_(True)
+        crr, car, cal, cproj = ops.fk_clip(x, cu(c['loc']), cu(c['rot']), c['sid'].int().to(DEV), None, None,
+                                           lib.make_tree(c['par']), None, lib.MODE_POSE_CHANGES, False)
+        assert cproj is None
+        ((cal ** 2).sum() if which == 'loc' else (car ** 3).sum()).backward()
+        assert_close('abs_loc', cal, al)
+        assert_close('g_pose_in (%s only)' % which, x.grad, m64.grad)
