@@ -42,6 +42,7 @@ def parse():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-sweep', action='store_true', help='skip the other BASELINE configs (C3 / C4 / C5 sizes)')
     ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--no-exchange', action='store_true', help='debug: N > 1 without the in-kernel loss-sum exchange')
     ap.add_argument('--cpu-seconds', type=float, default=12.0, help='budget of the bounded CPU sample')
     return ap.parse_args()
 
@@ -340,6 +341,7 @@ def timed_region(shard, steps, warmup, world):
     """W untimed steps, then exactly K steps between CUDA events on the launching stream, barrier + synchronize on
     both sides, max over ranks.  The timed stream carries nothing but the steps' own kernels (for N > 1 the step kernel
     itself stores the four loss sums into every rank's block: no collective, no host work between steps).
+    A fixed-length busy kernel in front of the start event keeps the host's launch latency out of the device time.
     Returns milliseconds for the K steps."""
     import torch.distributed as dist
     shard.prepare(warmup)
@@ -350,6 +352,10 @@ def timed_region(shard, steps, warmup, world):
         dist.barrier()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    # A fixed-length busy kernel (~0.2 ms) goes first, so that the K steps are already queued behind it when the start
+    # event fires: the events bracket the DEVICE time of exactly K steps, not the host's graph-launch latency (tens of
+    # microseconds, i.e. several 14 us steps, which an idle stream would otherwise spend waiting for the host).
+    torch.cuda._sleep(400000)
     e0.record()
     shard.run_steps(steps)
     e1.record()
@@ -558,7 +564,7 @@ def main():
     dev = torch.device('cuda', local)
     torch.cuda.set_device(dev)
     exchange = None
-    if world > 1:
+    if world > 1 and not args.no_exchange:
         from pedestrians_video_2_carla_b200.exchange import LossExchange
         exchange = LossExchange.distributed()
     shard = FusedShard(dev, args.clips, args.clip_len, SEED + rank, exchange=exchange)
@@ -580,10 +586,15 @@ def main():
     line = {'metric': METRIC, 'value': round(value, 1), 'unit': 'poses/s', 'n_gpus': world, 'steps': args.steps,
             'warmup': args.warmup, 'ms_per_step': round(ms_per_step, 6), 'higher_is_better': True, 'scaling': 'weak',
             'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': config_of(args, args.gpus),
-            'clocks': sampler.summary(note), 'gpu_launches': shard.launches_per_step * args.steps}
+            'clocks': sampler.summary(note), 'gpu_launches': shard.launches_per_step * args.steps,
+            'timing': 'CUDA events on the launching stream around K graph-replayed steps, queued behind a 0.2 ms busy '
+                      'kernel so the events see device time only; barrier + synchronize on both sides; max over ranks'}
     if exchange is not None:
         # every rank's steps are complete (timed_region ends with synchronize + barrier): read what the peers' kernels
         # stored into THIS rank's block for the last step
+        import torch.distributed as dist
+        torch.cuda.synchronize()
+        dist.barrier()
         got = exchange.read().cpu().tolist()
         line['exchange'] = {'kind': 'in-kernel peer stores over NVLink (CUDA IPC mapped blocks), no collective on the step path',
                             'ranks_arrived': int(got[4]), 'world': world, 'global_loc_2d': got[5], 'global_loc_3d': got[6],
@@ -616,7 +627,8 @@ def main():
         import torch.distributed as dist
         torch.cuda.synchronize()
         dist.barrier()
-        exchange.close()
+        if exchange is not None:
+            exchange.close()
         dist.destroy_process_group()
 
 

@@ -192,13 +192,19 @@ typedef struct {
     float* workspace;            /* p2c_fused_step_workspace_floats(N*L, B, input_6d) floats; its first 16 floats
                                     are self-resetting counters: zero them ONCE before the first call, every call
                                     leaves them zero again; do not share one workspace between concurrent streams */
-    float* losses;               /* out, 8 floats                                                    */
+    float* losses;               /* out, 8 floats (12 with gt_abs_rot, see below)                    */
     /* data-parallel ranks (one process per GPU, clips sharded by batch): when `exchange` is a block made by
        p2c_exchange_create + p2c_exchange_set_peers, the kernel that finishes the loss sums also stores this rank's
        {sum_sq_2d, count_2d, sum_sq_3d, count_3d} into every rank's block (peer stores over NVLink; no collective
        kernel, nothing waits for a peer).  NULL: single rank.  One block per stream, like the workspace.            */
     float* exchange;
     int32_t exchange_rank, exchange_world;
+    /* rot_3d fused (loss/rot_3d.py:9-37; loc_rot_3d, loc_2d_loc_rot_3d, weighted_loc_2d_loc_rot_3d of loss/__init__.py:
+       28-48): when gt_abs_rot = targets['absolute_pose_rot'] (N,L,B,3,3) is given, the step also forms
+       rot_3d = MSE(abs_rot, gt_abs_rot), adds weight_rot * rot_3d to losses[2] and its gradient to g_pose_in, and
+       `losses` must hold 12 floats: [8] rot_3d, [9] sum_sq_rot, [10] count_rot, [11] 0.  NULL: as before (8 floats). */
+    const float* gt_abs_rot;
+    float weight_rot;
 } p2c_fused_step_t;
 int64_t p2c_fused_step_workspace_floats(int64_t n_poses, int32_t n_bones, int32_t input_6d);
 int p2c_fused_step(const p2c_fused_step_t* p, void* stream);
@@ -287,6 +293,16 @@ int p2c_pck_count(const float* pred, const float* gt, const float* mask_src, int
                   int32_t c, int32_t c_mask, int32_t mask_hips, int32_t hips, int32_t neck,
                   int32_t norm_kind, float threshold, float near_zero, float* partials, double* out,
                   int32_t accumulate, void* stream);
+
+/* ---- The random draws of the synthetic-target generator (Carla2D3DIterableDataset.generate_batch,
+ *      data/carla/datasets/carla_2d3d_dataset.py:145-183) on the device: per frame `changes_per_frame` distinct bones get
+ *      Euler changes uniform in +-max_change (rad), world yaw changes uniform in +-max_initial_world_change (frame 0) /
+ *      +-max_world_change (later frames), one skeleton type in [0, n_types) per clip.  Counter-based (Philox4x32-10):
+ *      stateless, `offset` = the batch counter.  euler (N,L,B,3), world_euler (N,L,3), skeleton_index (N) int32 or NULL. */
+int p2c_draw_sparse_changes(uint64_t seed, uint64_t offset, int32_t n_clips, int32_t clip_len, int32_t n_bones,
+                            int32_t changes_per_frame, float max_change, float max_world_change,
+                            float max_initial_world_change, int32_t n_types, float* euler, float* world_euler,
+                            int32_t* skeleton_index, void* stream);
 
 const char* p2c_version(void);
 /* test hook: re-read the P2C_* debug switches from the environment (they are read once per process otherwise) */

@@ -19,3 +19,4 @@ Parity status (see DESIGN.md "Oracle"):
     scipy (Euler) and float64 finite differences (gradients).
 """
 from .fk_oracle import *  # noqa: F401,F403
+from .generator_oracle import *  # noqa: F401,F403

@@ -25,7 +25,7 @@ def _stale():
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force=False, verbose=False, defines=(), out=None):
+def build(force=False, verbose=False, defines=(), out=None, overrides=None):
     """Compile every .cu under csrc/ into one shared library. Returns the library path.
     `defines` / `out`: experiment builds (tools/variants.py) -- extra -D flags into another .so beside the product's."""
     lib_path = out or LIB_PATH
@@ -43,6 +43,7 @@ def build(force=False, verbose=False, defines=(), out=None):
     for src in sources():
         obj = os.path.join(build_dir, os.path.basename(src)[:-3] + '.o')
         objs.append(obj)
+        src = (overrides or {}).get(os.path.basename(src), src)   # experiment builds: another version of one file
         cmd = [nvcc] + flags + (['-Xptxas', '-v'] if verbose else []) + ['-c', src, '-o', obj]
         procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     for cmd, p in procs:

@@ -46,7 +46,8 @@ class FusedStep(C.Structure):
                 ('gt_3d', _P), ('weight_2d', C.c_float), ('weight_3d', C.c_float),
                 ('rel_rot', _P), ('abs_rot', _P), ('abs_loc', _P), ('proj', _P), ('proj_norm', _P),
                 ('g_pose_in', _P), ('workspace', _P), ('losses', _P),
-                ('exchange', _P), ('exchange_rank', C.c_int32), ('exchange_world', C.c_int32)]
+                ('exchange', _P), ('exchange_rank', C.c_int32), ('exchange_world', C.c_int32),
+                ('gt_abs_rot', _P), ('weight_rot', C.c_float)]
 
 
 _SIGS = {
@@ -101,6 +102,8 @@ _SIGS = {
     'p2c_mrpe_sum': (C.c_int, [_P, _P, _P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, _P, _P, C.c_int32, _P]),
     'p2c_pck_count': (C.c_int, [_P, _P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                                 C.c_int32, C.c_int32, C.c_float, C.c_float, _P, _P, C.c_int32, _P]),
+    'p2c_draw_sparse_changes': (C.c_int, [C.c_uint64, C.c_uint64, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_float,
+                                          C.c_float, C.c_float, C.c_int32, _P, _P, _P, _P]),
     'p2c_version': (C.c_char_p, []),
     'p2c_debug_reload_env': (None, []),
 }

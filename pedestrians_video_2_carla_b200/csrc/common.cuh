@@ -152,8 +152,10 @@ __device__ __forceinline__ void m3_to(float* s, const M3& a) {
 // ---- loss-sum exchange block (include/p2c_b200.h, p2c_exchange_*): the path's only cross-GPU step, done by the step
 //      kernel itself.  Layout of a rank's block (bytes): [0,128) 16 peer-mapped base pointers, one per rank (slot r =
 //      rank r's block as THIS rank addresses it); [128,132) sequence number of the last step this rank published;
-//      [256, ...) DEPTH x 16 entries of 8 words: {sum_sq_2d, count_2d, sum_sq_3d, count_3d, seq, -, -, -}, entry
-//      [seq % DEPTH][r] = rank r's sums of its step number `seq`.
+//      [256, ...) DEPTH x 16 entries of 8 words: {sum_sq_2d, seq, count_2d, seq, sum_sq_3d, seq, count_3d, seq}, entry
+//      [seq % DEPTH][r] = rank r's sums of its step number `seq`.  Every value travels with the sequence number in ONE
+//      aligned 8-byte store (single-copy atomic): an entry whose four sequence words equal `seq` is complete, whatever
+//      order the stores land in -- no release fence, so the publishing thread never waits for a peer's acknowledgement.
 constexpr int XCHG_DEPTH = 16;
 constexpr int XCHG_MAX_RANKS = 16;
 constexpr int XCHG_HEADER_WORDS = 64;
@@ -166,9 +168,8 @@ struct XchgArgs {   // by value in the kernel arguments; block == nullptr: no ex
 };
 
 // One thread (the one that finishes the step's loss sums) stores this rank's four sums into entry [seq][rank] of EVERY
-// rank's block -- plain stores over NVLink into peer memory, then the sequence word with release semantics at system
-// scope so a reader that sees the sequence number sees the sums.  Nothing waits for a peer.  The step counter lives in
-// the block, so CUDA-graph replays keep counting.
+// rank's block: four relaxed 8-byte (value, seq) stores per rank, over NVLink for the peers.  Fire and forget: nothing
+// waits for a peer.  The step counter lives in the block, so CUDA-graph replays keep counting.
 __device__ __forceinline__ void exchange_publish(const XchgArgs x, float s0, float s1, float s2, float s3) {
     if (!x.block) return;
     unsigned* counter = reinterpret_cast<unsigned*>(x.block) + 32;
@@ -176,11 +177,13 @@ __device__ __forceinline__ void exchange_publish(const XchgArgs x, float s0, flo
     *counter = seq;
     const unsigned long long* table = reinterpret_cast<const unsigned long long*>(x.block);
     const size_t off = XCHG_HEADER_WORDS + ((size_t)(seq % XCHG_DEPTH) * XCHG_MAX_RANKS + x.rank) * XCHG_ENTRY_WORDS;
+    const float v[4] = {s0, s1, s2, s3};
     for (int r = 0; r < x.world; ++r) {
         float* slot = reinterpret_cast<float*>(__ldcg(table + r)) + off;
-        asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(slot), "f"(s0), "f"(s1), "f"(s2), "f"(s3)
-                     : "memory");
-        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(slot + 4), "r"(seq) : "memory");
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1, %2};" ::"l"(slot + 2 * k), "r"(__float_as_uint(v[k])), "r"(seq)
+                         : "memory");
     }
 }
 

@@ -15,15 +15,14 @@ __global__ void exchange_read_kernel(const float* __restrict__ block, int world,
     if (seq == 0u) seq = __ldcg(reinterpret_cast<const unsigned*>(block) + 32);   // the last step this rank published
     float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
     int ok = 0;
-    if (lane < world) {
+    if (lane < world && seq != 0u) {
         const float* slot = block + XCHG_HEADER_WORDS + ((size_t)(seq % XCHG_DEPTH) * XCHG_MAX_RANKS + lane) * XCHG_ENTRY_WORDS;
-        unsigned got;
-        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(got) : "l"(slot + 4) : "memory");
-        if (got == seq && seq != 0u) {
-            asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];"
-                         : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-                         : "l"(slot)
-                         : "memory");
+        unsigned val[4], tag[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k)   // every (value, seq) pair is one 8-byte load of one 8-byte store: never torn
+            asm volatile("ld.relaxed.sys.global.v2.b32 {%0, %1}, [%2];" : "=r"(val[k]), "=r"(tag[k]) : "l"(slot + 2 * k) : "memory");
+        if (tag[0] == seq && tag[1] == seq && tag[2] == seq && tag[3] == seq) {
+            v = make_float4(__uint_as_float(val[0]), __uint_as_float(val[1]), __uint_as_float(val[2]), __uint_as_float(val[3]));
             ok = 1;
         }
     }

@@ -959,6 +959,7 @@ Plan make_plan(const p2c_fused_step_t* p) {
 
 extern "C" int p2c_fused_fast_supported(const p2c_fused_step_t* p) {
     if (p2c_env().disable_fast) return 0;  // test hook: force the exact generic composite
+    if (p->gt_abs_rot) return 0;           // rot_3d is fused in the tile kernel only; other shapes: generic composite
     if (!p->input_6d) return 0;  // arbitrary 3x3 input is not assumed to be a rotation: exact generic path
     if (p->mode != P2C_MODE_POSE_CHANGES && p->mode != P2C_MODE_RELATIVE_ROT) return 0;
     if (p->mode == P2C_MODE_POSE_CHANGES && !p->ref_rot) return 0;

@@ -139,6 +139,15 @@ __global__ void p2c_loss_finalize_kernel(const float* __restrict__ partials, int
 
 namespace {
 
+// rot_3d on the generic path: {loss, sum_sq, count} of the 9-channel reduction -> losses[8..11], weight into losses[2];
+// `scale` receives weight_rot (the upstream factor of the reduction's gradient kernel)
+__global__ void rot_merge_kernel(const float* __restrict__ rout, float wr, float* __restrict__ losses,
+                                 float* __restrict__ scale) {
+    losses[8] = rout[0]; losses[9] = rout[1]; losses[10] = rout[2]; losses[11] = 0.f;
+    losses[2] += wr * rout[0];
+    *scale = wr;
+}
+
 // d(w2*loc_2d + w3*loc_3d) / d(proj, abs_loc)
 __global__ void __launch_bounds__(WARPS * 32) loss_bwd_kernel(const LossArgs a) {
     const int lane = threadIdx.x & 31;
@@ -196,6 +205,8 @@ inline long align4(long x) { return (x + 3) & ~3L; }
 extern "C" int64_t p2c_fused_step_workspace_floats(int64_t n_poses, int32_t n_bones, int32_t input_6d) {
     long w = 16 + p2c_fused_fast_workspace_floats();        // zero-invariant header + fast-path partials
     w += LOSS_BLOCKS * 4;                                   // loss partials (generic path)
+    w += p2c_mse_workspace_floats(n_poses) + 4;             // rot_3d partials + result (generic path)
+    w += align4((long)n_poses * n_bones * 9);               // g_abs_rot (generic path with rot_3d)
     w += 2 * align4((long)n_poses * n_bones * 3);           // g_proj, g_abs_loc (generic path)
     if (input_6d) w += 2 * align4((long)n_poses * n_bones * 9);  // matrices, g_matrices
     return w;
@@ -208,7 +219,8 @@ extern "C" int p2c_fused_step_launches(const p2c_fused_step_t* p) {
     if (p->n_clips == 0) return 0;
     if (p2c_fused_tile_supported(p)) return p2c_fused_tile_launches(p);
     if (p2c_fused_fast_supported(p)) return p2c_fused_fast_launches(p);
-    return 5 + (p->input_6d ? 2 : 0);  // fk_fwd, loss_fwd, finalize, loss_bwd, fk_bwd (+ rot6d fwd/bwd)
+    // fk_fwd, loss_fwd, finalize, loss_bwd, fk_bwd (+ rot6d fwd/bwd) (+ rot_3d: partial, finalize, merge, gradient)
+    return 5 + (p->input_6d ? 2 : 0) + (p->gt_abs_rot ? 4 : 0);
 }
 
 extern "C" int p2c_fused_step(const p2c_fused_step_t* p, void* stream) {
@@ -267,7 +279,22 @@ extern "C" int p2c_fused_step(const p2c_fused_step_t* p, void* stream) {
     loss_bwd_kernel<<<(int)blocks, WARPS * 32, 0, st>>>(a);
     P2C_LAUNCH_CHECK();
 
+    float* g_abs_rot = nullptr;
+    if (p->gt_abs_rot) {
+        // rot_3d on the generic path: the 9-channel masked-MSE reduction (no mask) and its gradient as separate kernels,
+        // merged into the step's loss block; the gradient enters the FK backward as g_abs_rot
+        float* rpart = ws; ws += p2c_mse_workspace_floats(M);
+        float* rout = ws; ws += 4;
+        g_abs_rot = ws; ws += align4(M * B * 9);
+        rc = p2c_masked_mse_fwd(p->abs_rot, p->gt_abs_rot, M, B, 9, 9, 9, -1, rpart, rout, stream);
+        if (rc) return rc;
+        rot_merge_kernel<<<1, 1, 0, st>>>(rout, p->weight_rot, p->losses, rout + 3);
+        P2C_LAUNCH_CHECK();
+        rc = p2c_masked_mse_bwd(p->abs_rot, p->gt_abs_rot, rout, rout + 3, g_abs_rot, M, B, 9, 9, 9, -1, stream);
+        if (rc) return rc;
+    }
     p2c_fk_bwd_t b{};
+    b.g_abs_rot = g_abs_rot;
     b.tree = p->tree; b.n_clips = p->n_clips; b.clip_len = p->clip_len; b.mode = p->mode;
     b.pose_in = mats; b.ref_loc = p->ref_loc; b.ref_rot = p->ref_rot; b.ref_index = p->ref_index;
     b.world_loc = p->world_loc; b.world_rot = p->world_rot; b.camera = p->camera;

@@ -56,14 +56,15 @@ struct TileArgs {
     p2c_camera_t cam;
     const float* gt2;
     const float* gt3;
-    float w2, w3;
+    const float* gt_rot;   // targets['absolute_pose_rot'] (N,L,B,3,3) or NULL: rot_3d fused (loss/rot_3d.py:9-37)
+    float w2, w3, wr;
     float* rel_rot;
     float* abs_rot;
     float* abs_loc;
     float* proj;
     float* proj_norm;
     float* g_d6;
-    float* partials;       // tiles x 2
+    float* partials;       // tiles x 4: sum_sq_2d, sum_sq_3d, sum_sq_rot, -
     unsigned int* ticket;  // self-resetting
     int* count2;           // self-resetting, filled by count_kernel when mask is on
     unsigned int* arrive;  // self-resetting: CTAs that have added their part of count2 (count_inline)
@@ -296,14 +297,21 @@ struct FoldArgs {   // (by value: a reference to the kernel parameters would for
     const float* partials;
     unsigned int* header;   // ticket, -, count2, arrive, next
     double count3, all2;
-    float w2, w3;
-    int mask;
+    float w2, w3, wr;
+    int mask, rot;
     XchgArgs xchg;
 };
-__device__ __noinline__ void finish_losses(const FoldArgs a, double d2, double d3) {   // one thread
+__device__ __noinline__ void finish_losses(const FoldArgs a, double d2, double d3, double dr) {   // one thread
     const double c2 = a.mask ? (double)__ldcg(reinterpret_cast<const int*>(a.header) + 2) : a.all2;
     const float l2 = (float)(d2 / c2), l3 = (float)(d3 / a.count3);
-    a.losses[0] = l2; a.losses[1] = l3; a.losses[2] = a.w2 * l2 + a.w3 * l3;
+    float total = a.w2 * l2 + a.w3 * l3;
+    if (a.rot) {   // rot_3d: 9 matrix entries per bone where loc_3d has 3 coordinates
+        const double cr = a.count3 * 3.0;
+        const float lr = (float)(dr / cr);
+        total += a.wr * lr;
+        a.losses[8] = lr; a.losses[9] = (float)dr; a.losses[10] = (float)cr; a.losses[11] = 0.f;
+    }
+    a.losses[0] = l2; a.losses[1] = l3; a.losses[2] = total;
     a.losses[3] = (float)d2; a.losses[4] = (float)c2; a.losses[5] = (float)d3; a.losses[6] = (float)a.count3;
     a.losses[7] = 0.f;
     exchange_publish(a.xchg, (float)d2, (float)c2, (float)d3, (float)a.count3);
@@ -318,25 +326,29 @@ __device__ __noinline__ void warp_fold_if_last(const FoldArgs a, int ntiles, uns
     const int lane = threadIdx.x & 31;
     if (__shfl_sync(FULL_MASK, ticket, 0) != gridDim.x - 1) return;
     __threadfence();
-    double d2 = 0.0, d3 = 0.0;
+    double d2 = 0.0, d3 = 0.0, dr = 0.0;
     for (int i = lane; i < ntiles; i += 32) {
-        const float2 v = __ldcg(reinterpret_cast<const float2*>(a.partials) + i);
+        const float4 v = __ldcg(reinterpret_cast<const float4*>(a.partials) + i);
         d2 += (double)v.x;
         d3 += (double)v.y;
+        dr += (double)v.z;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         d2 += __shfl_xor_sync(FULL_MASK, d2, o);
         d3 += __shfl_xor_sync(FULL_MASK, d3, o);
+        dr += __shfl_xor_sync(FULL_MASK, dr, o);
     }
-    if (lane == 0) finish_losses(a, d2, d3);
+    if (lane == 0) finish_losses(a, d2, d3, dr);
 }
 
 // BT / SL: bones and 32-pose slices per tile at compile time (0 = read from the arguments); WORLD: a per-frame world
 // transform may be given (ZeroTrajectory, the only trajectory model of the reference, gives none); LONE: the launch
 // has at most one tile per CTA (only selects which forward walk is compiled in: the straight-line walks are most of
-// the code, and a kernel that runs every phase once per launch pays for its size in instruction fetches)
-template <int BT, int SL, bool WORLD, bool LONE>
+// the code, and a kernel that runs every phase once per launch pays for its size in instruction fetches); ROT: rot_3d is
+// fused (targets['absolute_pose_rot'] given) -- its own instances, so the plain step carries neither its code nor its
+// registers (measured: +6 % on every size when the term was a run-time branch)
+template <int BT, int SL, bool WORLD, bool LONE, bool ROT>
 __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) {
     extern __shared__ __align__(16) float smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NT = blockDim.x, W = NT >> 5;
@@ -421,13 +433,17 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         FoldArgs f;
         f.losses = a.losses; f.partials = a.partials; f.header = a.ticket;
         f.count3 = a.count3; f.all2 = (double)total * B * 2; f.w2 = a.w2; f.w3 = a.w3; f.mask = a.mask;
+        f.wr = a.wr; f.rot = a.gt_rot != nullptr;
         f.xchg = a.xchg;
         return f;
     };
-    auto finish = [&](double d2, double d3) { finish_losses(fold_args(), d2, d3); };
+    auto finish = [&](double d2, double d3, double dr) { finish_losses(fold_args(), d2, d3, dr); };
     auto fold_if_last = [&]() { warp_fold_if_last(fold_args(), ntiles, my_ticket); };
     auto take_ticket = [&]() { my_ticket = ticket_release(a.ticket); };
+    constexpr bool lone_sums = BT == 26 && LONE && SL == 1, lone_sums_early = lone_sums;
     const float k3 = a.w3 * 2.0f / (float)a.count3;
+    const float kr = a.wr * 2.0f / (float)(a.count3 * 3.0);   // rot_3d: mean over 9 entries per bone
+    __shared__ float red_r[32];
     unsigned it = 0;
     CTA_CLOCK(17)
     const int clips_full = a.P / L;
@@ -441,7 +457,11 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         const int m0 = tile * a.P;
         unsigned drawn = 0;
         if (tma && a.dynamic) drawn = atomicAdd(a.next, 1u);
-        float s2 = 0.f, s3 = 0.f;
+        if (ROT && tma) {   // the tile's rot_3d target records on their way into L2 while the forward phases run
+            const uint32_t bytes = (uint32_t)(min(a.P, total - m0) * B9) * 4u;
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.gt_rot + (size_t)m0 * B9), "r"(bytes) : "memory");
+        }
+        float s2 = 0.f, s3 = 0.f, sr = 0.f;
         const int np = min(a.P, total - m0);
         const int* row = ROW + (it & 1) * PS;
         const int tile_clips = np == a.P ? clips_full : np / L;   // (only the last tile can be short)
@@ -832,18 +852,20 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         if (tma) bulk_wait_read_all();   // rel_rot / abs_rot stores have read R and A
         __syncthreads();   // #5
         TILE_CLOCK(7)
-        if (warp == W - 2) {
+        auto store_partial = [&]() {
             // the tile's loss partial (a fixed shuffle tree over the per-warp sums: W <= 32); on this CTA's last tile
             // also its ticket, drawn now and looked at after the next phases (an L2 round trip later)
             float x = lane < W ? red[lane * 2] : 0.f, y = lane < W ? red[lane * 2 + 1] : 0.f;
+            float z = (ROT && lane < W) ? red_r[lane] : 0.f;
             x = warp_sum(x);
             y = warp_sum(y);
+            if (ROT) z = warp_sum(z);
             if (lane == 0) {
-                a.partials[tile * 2] = x;
-                a.partials[tile * 2 + 1] = y;
+                reinterpret_cast<float4*>(a.partials)[tile] = make_float4(x, y, z, 0.f);
                 if (nxt >= ntiles) take_ticket();
             }
-        }
+        };
+        if (!ROT && warp == W - 2) store_partial();   // (rot_3d fused: its sum is formed in the next pass)
         if (tma) {
             if (a.abs_loc) bulk_s2g(a.abs_loc + (size_t)m0 * B3, G3, (uint32_t)(np * B3) * 4u);
             if (a.proj) bulk_s2g(a.proj + (size_t)m0 * B3, G2, (uint32_t)(np * B3) * 4u);
@@ -891,18 +913,56 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                     g.x += gp.x; g.y += gp.y; g.z += gp.z;
                     GV[(b * 3) * PS + col] = g.x; GV[(b * 3 + 1) * PS + col] = g.y; GV[(b * 3 + 2) * PS + col] = g.z;
                 }
-                XR[(b * 3) * PS + col] = g.y * t.z - g.z * t.y;
-                XR[(b * 3 + 1) * PS + col] = g.z * t.x - g.x * t.z;
-                XR[(b * 3 + 2) * PS + col] = g.x * t.y - g.y * t.x;
+                V3 x{g.y * t.z - g.z * t.y, g.z * t.x - g.x * t.z, g.x * t.y - g.y * t.x};
+                if (ROT) {
+                    // rot_3d (loss/rot_3d.py:9-37): MSE of the absolute rotation matrices.  Turning the chain at a joint
+                    // by w turns every row of A_d in its subtree like a point (row x w), so the loss gradient G_d =
+                    // k_r (A_d - Agt_d) acts as the torque  tau_d = sum_rows G_d,i x A_d,i = k_r sum_rows A_d,i x Agt_d,i,
+                    // which joins the own part of the subtree sums.  The target record comes straight from global
+                    // memory (prefetched into L2 at the top of the tile; 36 bytes per lane, L1 keeps the lines).
+                    const int pl = min(col, np - 1);
+                    const M3 A_ = lds9(A + pl * B9, b);
+                    const float* gq = a.gt_rot + ((size_t)(m0 + pl) * B + b) * 9;
+                    float q[9];
+#pragma unroll
+                    for (int i = 0; i < 9; ++i) q[i] = __ldg(gq + i);
+                    float e2 = 0.f;
+#pragma unroll
+                    for (int i = 0; i < 9; ++i) {
+                        const float e = A_.m[i] - q[i];
+                        e2 = fmaf(e, e, e2);
+                    }
+                    if (col < np) sr += e2;
+#pragma unroll
+                    for (int i = 0; i < 3; ++i) {
+                        const float ax = A_.m[3 * i], ay = A_.m[3 * i + 1], az = A_.m[3 * i + 2];
+                        const float qx = q[3 * i], qy = q[3 * i + 1], qz = q[3 * i + 2];
+                        x.x = fmaf(kr, ay * qz - az * qy, x.x);
+                        x.y = fmaf(kr, az * qx - ax * qz, x.y);
+                        x.z = fmaf(kr, ax * qy - ay * qx, x.z);
+                    }
+                }
+                XR[(b * 3) * PS + col] = x.x;
+                XR[(b * 3 + 1) * PS + col] = x.y;
+                XR[(b * 3 + 2) * PS + col] = x.z;
             }
         }
+        if (ROT) {
+            sr = warp_sum(sr);
+            if (lane == 0) red_r[warp] = sr;
+        }
         __syncthreads();   // #5b
+        if (ROT && warp == W - 2) store_partial();
+        // few tiles: the warp that drew this CTA's ticket folds the grid's partials if it was the last -- NOW, when it has
+        // no part in the subtree walks below, so that the fold (an L2 round trip, and with data-parallel ranks the peer
+        // stores of the exchange, an NVLink round trip) sits behind the rest of the backward pass of this CTA
+        const bool fold_early = W - 2 >= (lone_sums_early ? 15 : 6 * slices);
+        if (fold_early && nxt >= ntiles && a.warp_fold && warp == W - 2) fold_if_last();
 
         // ---- subtree sums, leaves first (the bone order has parents before children, so a walk in reverse bone order
         //      meets every child before its parent):  Sx_b = sum_{d in subtree(b)} g_d x t_d (rows XR), Sg_b = sum g_d
         //      (in place over g_b).  The six components are independent: one warp each per slice, no barrier inside
         //      the walk, the running value stays in a register along chains.
-        constexpr bool lone_sums = BT == 26 && LONE && SL == 1;
         if (lone_sums) {
             // (one tile per CTA) the limbs in parallel, three warps each (component k of both sums); the limb groups
             // leave the sum of their head bone in its own row and signal, the trunk group adds those rows when it
@@ -990,7 +1050,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         }
         // (two warps without a column when W >= 6 slices + 2: both jobs wait on global memory, off the critical path)
         if (nxt < ntiles && warp == W - 1) fill_rows(nxt, (it + 1) & 1);
-        if (nxt >= ntiles && a.warp_fold && warp == W - 2) fold_if_last();   // (the ticket was drawn after the loss pass)
+        if (!fold_early && nxt >= ntiles && a.warp_fold && warp == W - 2) fold_if_last();   // (the ticket was drawn after the loss pass)
         while (!mbar_try_wait(bars + 2, it & 1u)) {}
         __syncthreads();   // #6
         TILE_CLOCK(8)
@@ -1077,24 +1137,26 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     if (last_s) {
         // every CTA has stored its partials and taken its ticket: fold them in tile order, in double, all threads
         __threadfence();
-        double d2 = 0.0, d3 = 0.0;
+        double d2 = 0.0, d3 = 0.0, dr = 0.0;
         for (int i = tid; i < ntiles; i += NT) {
-            const float2 v = __ldcg(reinterpret_cast<const float2*>(a.partials) + i);
+            const float4 v = __ldcg(reinterpret_cast<const float4*>(a.partials) + i);
             d2 += (double)v.x;
             d3 += (double)v.y;
+            dr += (double)v.z;
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             d2 += __shfl_xor_sync(FULL_MASK, d2, o);
             d3 += __shfl_xor_sync(FULL_MASK, d3, o);
+            dr += __shfl_xor_sync(FULL_MASK, dr, o);
         }
         double* dred = reinterpret_cast<double*>(R);   // (no bulk copy still reads the relative-rotation region)
-        if (lane == 0) { dred[warp * 2] = d2; dred[warp * 2 + 1] = d3; }
+        if (lane == 0) { dred[warp * 3] = d2; dred[warp * 3 + 1] = d3; dred[warp * 3 + 2] = dr; }
         __syncthreads();
         if (tid == 0) {
-            d2 = 0.0; d3 = 0.0;
-            for (int w = 0; w < W; ++w) { d2 += dred[w * 2]; d3 += dred[w * 2 + 1]; }
-            finish(d2, d3);
+            d2 = 0.0; d3 = 0.0; dr = 0.0;
+            for (int w = 0; w < W; ++w) { d2 += dred[w * 3]; d3 += dred[w * 3 + 1]; dr += dred[w * 3 + 2]; }
+            finish(d2, d3, dr);
         }
     }
     CTA_CLOCK(20)
@@ -1136,10 +1198,11 @@ TileLaunch make_launch(const p2c_fused_step_t* p, const TileArgs& a) {   // a: t
     // bone-per-lane kernels of fused_fast.cu, which also copy cooperatively
     if ((t.P & 1) || (total & 1)) return t;
     if (total > (1L << 26)) return t;   // pose and joint indices are 32-bit inside the kernels
-    const void* ptrs[] = {p->pose_in, p->gt_2d, p->gt_3d, p->g_pose_in, p->rel_rot, p->abs_rot, p->abs_loc, p->proj};
+    const void* ptrs[] = {p->pose_in, p->gt_2d, p->gt_3d, p->g_pose_in, p->rel_rot, p->abs_rot, p->abs_loc, p->proj,
+                          p->gt_abs_rot};
     for (const void* q : ptrs)
         if (reinterpret_cast<uintptr_t>(q) & 15) return t;
-    if (reinterpret_cast<uintptr_t>(p->workspace) & 7) return t;   // (64-bit counter word in the header)
+    if (reinterpret_cast<uintptr_t>(p->workspace) & 15) return t;   // (64-bit counter word, float4 tile partials)
     t.PS = (t.P + 31) & ~31;
     t.slices = t.PS / 32;
     const long ntiles = (total + t.P - 1) / t.P;
@@ -1210,6 +1273,7 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     a.d6 = p->pose_in; a.ref_loc = p->ref_loc; a.ref_rot = p->ref_rot; a.ref_index = p->ref_index;
     a.world_loc = p->world_loc; a.world_rot = p->world_rot; a.cam = p->camera;
     a.gt2 = p->gt_2d; a.gt3 = p->gt_3d; a.w2 = p->weight_2d; a.w3 = p->weight_3d;
+    a.gt_rot = p->gt_abs_rot; a.wr = p->gt_abs_rot ? p->weight_rot : 0.f;
     a.rel_rot = p->rel_rot; a.abs_rot = p->abs_rot; a.abs_loc = p->abs_loc; a.proj = p->proj;
     a.proj_norm = p->proj_norm; a.g_d6 = p->g_pose_in;
     a.ticket = reinterpret_cast<unsigned int*>(p->workspace);
@@ -1241,12 +1305,19 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     // CARLA_SKELETON: compile-time tree and slices, one instance per launch shape (limb walk needs 5 warps per slice)
     const bool limb_ok = t.threads / 32 > 5 * t.slices;
     const int ki = world ? 5 : !carla ? 4 : t.count_inline ? (t.slices == 1 ? 2 : 3) : !limb_ok ? 4 : (t.slices == 1 ? 0 : 1);
-    const kern_t k = ki == 0   ? tile_kernel<26, 1, false, false>
-                     : ki == 1 ? tile_kernel<26, 2, false, false>
-                     : ki == 2 ? tile_kernel<26, 1, false, true>
-                     : ki == 3 ? tile_kernel<26, 2, false, true>
-                     : ki == 4 ? tile_kernel<0, 0, false, false>
-                               : tile_kernel<0, 0, true, false>;
+    const bool rot = p->gt_abs_rot != nullptr;
+    const kern_t k = rot ? (ki == 0   ? tile_kernel<26, 1, false, false, true>
+                            : ki == 1 ? tile_kernel<26, 2, false, false, true>
+                            : ki == 2 ? tile_kernel<26, 1, false, true, true>
+                            : ki == 3 ? tile_kernel<26, 2, false, true, true>
+                            : ki == 4 ? tile_kernel<0, 0, false, false, true>
+                                      : tile_kernel<0, 0, true, false, true>)
+                         : (ki == 0   ? tile_kernel<26, 1, false, false, false>
+                            : ki == 1 ? tile_kernel<26, 2, false, false, false>
+                            : ki == 2 ? tile_kernel<26, 1, false, true, false>
+                            : ki == 3 ? tile_kernel<26, 2, false, true, false>
+                            : ki == 4 ? tile_kernel<0, 0, false, false, false>
+                                      : tile_kernel<0, 0, true, false, false>);
     if (const int e = p2c_allow_big_smem(reinterpret_cast<const void*>(k), 227 * 1024 - 1024)) return e;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(t.grid);

@@ -74,6 +74,14 @@ __device__ __forceinline__ float2 lds64(const float* p) {
 __device__ __forceinline__ void sts64(float* p, float x, float y) {
     asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(smem_u32(p)), "f"(x), "f"(y) : "memory");
 }
+__device__ __forceinline__ float lds32(const float* p) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(smem_u32(p)) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts32(float* p, float x) {
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(smem_u32(p)), "f"(x) : "memory");
+}
 // 9-word bone record b of an AoS pose record (b is warp-uniform at every call site: the parity branch does not diverge)
 // (64-bit accesses: half the wavefronts of scalar ones; the pose stride, 117 x 8 bytes, is conflict free)
 __device__ __forceinline__ M3 lds9(const float* pose, int b) {

@@ -139,12 +139,13 @@ class ProjectionModule(nn.Module):
         }
 
     def fused_step(self, pose_inputs_6d, targets, world_loc_change_batch=None, world_rot_change_batch=None,
-                   mask_missing_joints=True, transform='hips_neck', loss_weights=None):
+                   mask_missing_joints=True, transform='hips_neck', loss_weights=None, loss_mode='loc_2d_3d'):
         """The whole pose_lifting hot path in one call: raw rotation_6d model output (N,L,B,6) -> projections,
         the module's dict, projection_2d_transformed, loc_2d / loc_3d / loc_2d_3d, with the gradient wrt the 6-D
         input attached to `loc_2d_3d` (modules/flow/pose_lifting.py:121-195 + modules/flow/base.py:440-469).
-        `targets` holds 'projection_2d_transformed' (or 'projection_2d' when transform is None) and
-        'absolute_pose_loc'."""
+        `targets` holds 'projection_2d_transformed' (or 'projection_2d' when transform is None),
+        'absolute_pose_loc' and, for the loss modes with rot_3d, 'absolute_pose_rot'.  out['loss'][loss_mode] is the
+        differentiable value of the chosen mode; loc_2d / loc_3d / rot_3d beside it are reported values."""
         n, l, b = pose_inputs_6d.shape[:3]
         device = pose_inputs_6d.device
         world_loc = world_rot = None
@@ -162,11 +163,23 @@ class ProjectionModule(nn.Module):
         gt2 = targets['projection_2d_transformed' if normalize else 'projection_2d']
         w = loss_weights or {}
         ref_loc, ref_rot = self._ref
+        # loss_mode picks the terms of the differentiable sum (loss/__init__.py:28-48); weights as in
+        # weighted_loc_2d_loc_rot_3d (missing weights are 1)
+        terms = {'loc_2d': ('loc_2d',), 'loc_3d': ('loc_3d',), 'rot_3d': ('rot_3d',), 'loc_2d_3d': ('loc_2d', 'loc_3d'),
+                 'loc_rot_3d': ('loc_3d', 'rot_3d'), 'loc_2d_loc_rot_3d': ('loc_2d', 'loc_3d', 'rot_3d'),
+                 'weighted_loc_2d_loc_rot_3d': ('loc_2d', 'loc_3d', 'rot_3d')}.get(loss_mode)
+        if terms is None:
+            raise NotImplementedError('fused_step fuses loc_2d, loc_3d, rot_3d and their sums, got loss_mode %r' % (loss_mode,))
+        weighted = loss_mode == 'weighted_loc_2d_loc_rot_3d'
+        wt = {k: (float(w.get(k, 1.0)) if weighted else 1.0) if k in terms else 0.0 for k in ('loc_2d', 'loc_3d', 'rot_3d')}
+        gt_rot = targets.get('absolute_pose_rot') if 'rot_3d' in terms else None
+        if 'rot_3d' in terms and gt_rot is None:
+            raise RuntimeError("loss mode %r needs targets['absolute_pose_rot']" % (loss_mode,))
         res = ops.fused_step(pose_inputs_6d, self._pose.tree, self._projection.camera.struct, ref_loc, ref_rot, gt2,
                              targets['absolute_pose_loc'], ref_index=self._ref_index, world_loc=world_loc,
                              world_rot=world_rot, mode=self._mode, hips=get_root_point(), neck=get_neck_point(),
                              normalize=normalize, mask_missing_joints=mask_missing_joints,
-                             weight_2d=w.get('loc_2d', 1.0), weight_3d=w.get('loc_3d', 1.0))
+                             weight_2d=wt['loc_2d'], weight_3d=wt['loc_3d'], gt_rot=gt_rot, weight_rot=wt['rot_3d'])
         if world_loc is None:
             world_loc = self._world_locations.unsqueeze(1).repeat(1, l, 1)
             world_rot = self._world_rotations.unsqueeze(1).repeat(1, l, 1, 1)
@@ -178,7 +191,7 @@ class ProjectionModule(nn.Module):
             'world_loc': world_loc,
             'world_rot': world_rot,
             'projection_2d_transformed': res.projection_2d_transformed,
-            'loss': {'loc_2d': res.loc_2d, 'loc_3d': res.loc_3d, 'loc_2d_3d': res.loc_2d_3d},
+            'loss': {'loc_2d': res.loc_2d, 'loc_3d': res.loc_3d, 'rot_3d': res.rot_3d, loss_mode: res.total},
             'loss_sums': res.losses[3:7],
         }
         return res.projection_2d, out

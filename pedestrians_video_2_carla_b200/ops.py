@@ -481,6 +481,25 @@ def renormalize(sample, dim, hips, neck, autonormalize=True, near_zero=1e-5, ref
                               None if ref_scale is None else ref_scale.detach(), ref_index)
 
 
+def draw_sparse_changes(seed, offset, n_clips, clip_len, n_bones, changes_per_frame, max_change, max_world_change=0.0,
+                        max_initial_world_change=0.0, n_types=4, device=None):
+    """The synthetic generator's random draws on the device (p2c_draw_sparse_changes; reference
+    carla_2d3d_dataset.py:157-182): Euler changes (N,L,B,3), world Euler changes (N,L,3), skeleton type (N,) int32.
+    Counter-based: (seed, offset) name the batch, nothing is kept between calls."""
+    dev = torch.device(device if device is not None else 'cuda')
+    if dev.type != 'cuda':
+        raise RuntimeError('p2c_b200: the generator draws on a CUDA device (no CPU fallback)')
+    euler = torch.empty((n_clips, clip_len, n_bones, 3), device=dev)
+    world = torch.empty((n_clips, clip_len, 3), device=dev)
+    skeleton = torch.empty((n_clips,), dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        check(_lib.load().p2c_draw_sparse_changes(int(seed) & (2 ** 64 - 1), int(offset) & (2 ** 64 - 1), n_clips, clip_len,
+                                                  n_bones, changes_per_frame, float(max_change), float(max_world_change),
+                                                  float(max_initial_world_change), n_types, ptr(euler), ptr(world),
+                                                  ptr(skeleton), stream()), 'draw_sparse_changes')
+    return euler, world, skeleton
+
+
 _WS = {}
 
 
@@ -498,7 +517,7 @@ def _workspace(dev, nfloats):
 
 class FusedStepResult(object):
     """Outputs of one fused pose_lifting step (see fused_step)."""
-    __slots__ = ('loc_2d', 'loc_3d', 'loc_2d_3d', 'losses', 'relative_pose_rot', 'absolute_pose_rot',
+    __slots__ = ('loc_2d', 'loc_3d', 'loc_2d_3d', 'rot_3d', 'total', 'losses', 'relative_pose_rot', 'absolute_pose_rot',
                  'absolute_pose_loc', 'projection_2d', 'projection_2d_transformed', 'pose_in', 'grad_pose_in')
 
     def backward(self):
@@ -546,6 +565,8 @@ class _FusedStep(torch.autograd.Function):
         N, L, B = pose_in.shape[:3]
         dev = pose_in.device
         gt2, gt3 = _gt2_records(cfg['gt_2d']), _f32c(cfg['gt_3d'], 'gt_3d')
+        gt_rot = _f32c(cfg.get('gt_rot'), 'gt_rot')
+        n_losses = 12 if gt_rot is not None else 8
         ref_index = cfg.get('ref_index')
         out = cfg.get('out') or {}
         input_6d = 1 if pose_in.shape[-1] == 6 and pose_in.dim() == 4 else 0
@@ -557,11 +578,13 @@ class _FusedStep(torch.autograd.Function):
                cfg['ref_loc'].data_ptr(), cfg['ref_rot'].data_ptr(),
                None if cfg.get('world_loc') is None else cfg['world_loc'].data_ptr(),
                None if cfg.get('world_rot') is None else cfg['world_rot'].data_ptr(), _lib.raw_stream(),
-               None if cfg.get('exchange') is None else cfg['exchange'].block)
+               None if cfg.get('exchange') is None else cfg['exchange'].block,
+               gt_rot is not None, float(cfg.get('weight_rot', 1.0)))
         plan = out.get('_plan')
         if plan is not None and plan[0] == key:
             _, a, rel_rot, abs_rot, abs_loc, proj, proj_norm, g_in, losses, keep = plan
             a.pose_in, a.gt_2d, a.gt_3d, a.ref_index = ptr(pose_in), ptr(gt2), ptr(gt3), ptr(ref_index)
+            a.gt_abs_rot = ptr(gt_rot)
             ws, ref_loc, ref_rot, world_loc, world_rot = keep[:5]
         else:
             a = _lib.FusedStep()
@@ -576,6 +599,7 @@ class _FusedStep(torch.autograd.Function):
             a.world_loc, a.world_rot, a.camera = ptr(world_loc), ptr(world_rot), cfg['camera']
             a.gt_2d, a.gt_2d_channels, a.gt_3d = ptr(gt2), gt2.shape[-1], ptr(gt3)
             a.weight_2d, a.weight_3d = float(cfg.get('weight_2d', 1.0)), float(cfg.get('weight_3d', 1.0))
+            a.gt_abs_rot, a.weight_rot = ptr(gt_rot), float(cfg.get('weight_rot', 1.0))
             if cfg.get('exchange') is not None:
                 cfg['exchange'].attach(a)
             rel_rot = out.get('rel_rot') if out.get('rel_rot') is not None else torch.empty((N, L, B, 3, 3), device=dev)
@@ -591,11 +615,14 @@ class _FusedStep(torch.autograd.Function):
             ws = out.get('workspace')
             if ws is None or ws.numel() < nws:
                 ws = _workspace(dev, int(nws))
-            losses = out.get('losses') if out.get('losses') is not None else torch.empty(8, device=dev)
+            losses = out.get('losses')
+            if losses is None or losses.numel() < n_losses:
+                losses = torch.empty(n_losses, device=dev)
             a.rel_rot, a.abs_rot, a.abs_loc, a.proj, a.proj_norm = (ptr(rel_rot), ptr(abs_rot), ptr(abs_loc),
                                                                     ptr(proj), ptr(proj_norm))
             a.g_pose_in, a.workspace, a.losses = ptr(g_in), ptr(ws), ptr(losses)
-            if all(out.get(k) is not None for k in ('rel_rot', 'abs_rot', 'abs_loc', 'proj', 'g_pose_in', 'losses')) \
+            if all(out.get(k) is not None for k in ('rel_rot', 'abs_rot', 'abs_loc', 'proj', 'g_pose_in')) \
+                    and out.get('losses') is losses \
                     and (proj_norm is None or out.get('proj_norm') is not None):
                 # `keep` pins the tensors whose pointers live in the argument block
                 out['_plan'] = (key, a, rel_rot, abs_rot, abs_loc, proj, proj_norm, g_in, losses,
@@ -669,7 +696,7 @@ class _FusedStep(torch.autograd.Function):
         return total, None
 
 
-def fused_step_buffers(n_clips, clip_len, n_bones, device, input_6d=True, transformed=False):
+def fused_step_buffers(n_clips, clip_len, n_bones, device, input_6d=True, transformed=False, rot=False):
     """Preallocated outputs for fused_step(out=...): a training loop with static shapes passes the same dict every
     step, which also lets fused_step reuse its argument block (no per-step allocations; the outputs of step i are
     overwritten by step i+1)."""
@@ -677,7 +704,7 @@ def fused_step_buffers(n_clips, clip_len, n_bones, device, input_6d=True, transf
     out = dict(rel_rot=torch.empty((n, l, b, 3, 3), device=device), abs_rot=torch.empty((n, l, b, 3, 3), device=device),
                abs_loc=torch.empty((n, l, b, 3), device=device), proj=torch.empty((n, l, b, 3), device=device),
                g_pose_in=torch.empty((n, l, b, 6) if input_6d else (n, l, b, 3, 3), device=device),
-               losses=torch.empty(8, device=device))
+               losses=torch.empty(12 if rot else 8, device=device))
     if transformed:
         out['proj_norm'] = torch.empty((n, l, b, 3), device=device)
     return out
@@ -685,21 +712,29 @@ def fused_step_buffers(n_clips, clip_len, n_bones, device, input_6d=True, transf
 
 def fused_step(pose_in, tree, camera, ref_loc, ref_rot, gt_2d, gt_3d, ref_index=None, world_loc=None, world_rot=None,
                mode=_lib.MODE_POSE_CHANGES, hips=1, neck=8, normalize=True, mask_missing_joints=True, weight_2d=1.0,
-               weight_3d=1.0, want_transformed=True, out=None, exchange=None):
+               weight_3d=1.0, want_transformed=True, out=None, exchange=None, gt_rot=None, weight_rot=1.0):
     """One pose_lifting step of the hot path in one call.  pose_in: (N,L,B,6) rotation_6d model output or
     (N,L,B,3,3) matrices.  Returns FusedStepResult; .loc_2d_3d (= weight_2d*loc_2d + weight_3d*loc_3d) and the module
     tensors (.relative_pose_rot, .absolute_pose_rot, .absolute_pose_loc, .projection_2d, .projection_2d_transformed)
     carry autograd edges back to pose_in (.loc_2d / .loc_3d are reported values).  `out` may hold preallocated
     buffers (CUDA-graph friendly; the outputs of step i are then overwritten by step i+1, so any extra loss on them
     must be back-propagated before the next call).  `exchange`: a LossExchange (exchange.py) -- the step then also
-    publishes its four loss sums to every data-parallel rank."""
+    publishes its four loss sums to every data-parallel rank.  `gt_rot` = targets['absolute_pose_rot']: rot_3d
+    (loss/rot_3d.py) is fused as well -- `.rot_3d`, and `.total` = weight_2d*loc_2d + weight_3d*loc_3d + weight_rot*rot_3d
+    carries the gradient (the loc_rot_3d / loc_2d_loc_rot_3d / weighted_loc_2d_loc_rot_3d modes of loss/__init__.py:28-48
+    are weightings of it)."""
     cfg = dict(tree=tree, camera=camera, ref_loc=ref_loc, ref_rot=ref_rot, gt_2d=gt_2d, gt_3d=gt_3d,
                ref_index=ref_index, world_loc=world_loc, world_rot=world_rot, mode=mode, hips=hips, neck=neck,
                normalize=normalize, mask_missing_joints=mask_missing_joints, weight_2d=weight_2d,
-               weight_3d=weight_3d, want_transformed=want_transformed, out=out, exchange=exchange)
+               weight_3d=weight_3d, want_transformed=want_transformed, out=out, exchange=exchange, gt_rot=gt_rot,
+               weight_rot=weight_rot)
     l2, l3, l23, rel_rot, abs_rot, abs_loc, proj, proj_norm = _FusedStep.apply(pose_in, cfg)
     res = cfg['_result']
     res.loc_2d, res.loc_3d, res.loc_2d_3d, res.pose_in = l2, l3, l23, pose_in
+    # with gt_rot (targets['absolute_pose_rot']) the differentiable sum is weight_2d*loc_2d + weight_3d*loc_3d +
+    # weight_rot*rot_3d (`total`; `loc_2d_3d` names the same tensor); rot_3d alone is a reported value
+    res.total = l23
+    res.rot_3d = res.losses[8] if gt_rot is not None else None
     res.relative_pose_rot, res.absolute_pose_rot, res.absolute_pose_loc = rel_rot, abs_rot, abs_loc
     res.projection_2d = proj
     res.projection_2d_transformed = proj_norm if (want_transformed and normalize) else None

@@ -93,7 +93,7 @@ def compare(res, grad, want, ref_grad, normalize=True, ref_grad32=None, grad_tol
 @pytest.mark.parametrize('six_d', [True, False])
 @pytest.mark.parametrize('normalize,mask', [(True, True), (False, False), (True, False)])
 def test_fused_step_carla(ops, lib, mode, six_d, normalize, mask):
-    c = make_case(12, 16, 100 + 7 * six_d + normalize + 2 * mask)
+    c = make_case(12, 16, 100 + 7 * six_d + normalize + 2 * mask, mode=mode)
     gt2, gt3 = make_targets(c, mode, normalize)
     d6 = c['d6'].clone().requires_grad_(True)
     mats = O.rotation_6d_to_matrix(d6)
@@ -130,7 +130,7 @@ def test_fused_step_kernel_variants(ops, lib, monkeypatch, request, variant, mod
     monkeypatch.setenv(variant, '1')
     lib.load().p2c_debug_reload_env()    # the switches are read once per process: re-read them for this test ...
     request.addfinalizer(lambda: (monkeypatch.undo(), lib.load().p2c_debug_reload_env()))   # ... and after it
-    c = make_case(20, 16, 4242)
+    c = make_case(20, 16, 4242, mode=mode)
     gt2, gt3 = make_targets(c, mode)
     d6 = c['d6'].clone().requires_grad_(True)
     want = oracle_step(c, O.rotation_6d_to_matrix(d6), mode, gt=(gt2, gt3))
@@ -450,3 +450,59 @@ def test_two_channel_view_targets_take_the_tile_kernel(ops, lib):
     a = ops.fused_step(cu(c['d6']), tree, cams, cu(c['loc']), cu(c['rot']), view, cu(gt3), ref_index=c['sid'].int().to(DEV))
     b = ops.fused_step(cu(c['d6']), tree, cams, cu(c['loc']), cu(c['rot']), g3, cu(gt3), ref_index=c['sid'].int().to(DEV))
     assert torch.equal(a.losses, b.losses) and torch.equal(a.grad_pose_in, b.grad_pose_in)
+
+
+def test_degenerate_normaliser_poses_stay_within_the_reference_noise(ops, lib):
+    """UNconditioned random poses (tests/_util.py::_well_conditioned off): torsos that point at the camera bring the
+    projected hips-neck distance below a pixel, the normalised coordinates into the hundreds, and every fp32
+    evaluation -- the reference's own included -- to rounding noise far above 1e-4 on those poses.  The step must stay
+    finite and within an order of magnitude of the fp32 reference's own deviation from float64, group by group."""
+    c = make_case(256, 16, 7, world=False, conditioned=False)
+    gt2, gt3 = make_targets(c)
+    d6 = c['d6'].clone().requires_grad_(True)
+    want = oracle_step(c, O.rotation_6d_to_matrix(d6), gt=(gt2, gt3))
+    want['loc_2d_3d'].backward()
+    res, grad = run_cuda(ops, lib, c, c['d6'], gt2, gt3, 'pose_changes', True, True)
+    assert bool(torch.isfinite(grad).all()) and bool(torch.isfinite(res.losses).all())
+    ref32 = oracle_grad32(c, gt2, gt3)
+    assert_close('absolute_pose_loc', res.absolute_pose_loc, want['absolute_pose_loc'])
+    assert_close('projection_2d', res.projection_2d, want['projection_2d'])
+    assert_close('loc_3d', res.loc_3d, want['loc_3d'])
+    assert_close_fp32_aware('loc_2d', res.loc_2d, want['loc_2d'], ref32.out['loc_2d'], slack=10.0)
+    assert_close_fp32_aware('grad', grad, d6.grad, ref32.grad, slack=10.0)
+
+
+@pytest.mark.parametrize('n,l,tree,w', [(12, 16, 'carla', (1.0, 1.0, 1.0)), (600, 16, 'carla', (0.5, 2.0, 3.0)),
+                                        (8, 64, 'carla', (0.0, 0.0, 1.0)), (7, 5, 'carla', (1.0, 1.0, 0.7)),
+                                        (6, 8, 'smpl', (1.0, 1.0, 1.0))])
+def test_rot_3d_fused_in_the_step(ops, lib, n, l, tree, w):
+    """weight_2d*loc_2d + weight_3d*loc_3d + weight_rot*rot_3d from one fused step (rot_3d: loss/rot_3d.py:9-37) --
+    values and gradient against the float64 oracle: one tile per CTA, many tiles, two-slice clips, a shape the tile
+    kernel declines (35 poses: generic composite with the 9-channel reduction), a non-CARLA tree."""
+    c = make_case(n, l, 700 + n + l, par=None if tree == 'carla' else smpl_parents(), world=False)
+    gt2, gt3 = make_targets(c)
+    with torch.no_grad():
+        gt_rot = oracle_step(c, O.rotation_6d_to_matrix(c['d6_gt']))['absolute_pose_rot']
+    w2, w3, wr = w
+
+    def oracle(case, dtype):
+        x = case['d6'].to(dtype).clone().requires_grad_(True)
+        out = oracle_step(case, O.rotation_6d_to_matrix(x), gt=(gt2.to(dtype), gt3.to(dtype)))
+        out['rot_3d'] = O.loss_rot_3d(out['absolute_pose_rot'], gt_rot.to(dtype))
+        out['total'] = w2 * out['loc_2d'] + w3 * out['loc_3d'] + wr * out['rot_3d']
+        out['total'].backward()
+        return x.grad, out
+    g64, want = oracle(c, torch.float64)
+    g32, _ = oracle(cast_case(c, torch.float32), torch.float32)
+    cam = c['cam']
+    x = cu(c['d6']).requires_grad_(True)
+    res = ops.fused_step(x, lib.make_tree(c['par']), lib.make_camera(cam.R.tolist(), cam.T.tolist(), cam.f, cam.px, cam.py),
+                         cu(c['loc']), cu(c['rot']), cu(gt2), cu(gt3), ref_index=c['sid'].int().to(DEV), hips=c['hips'],
+                         neck=c['neck'], weight_2d=w2, weight_3d=w3, gt_rot=cu(gt_rot), weight_rot=wr)
+    res.total.backward()
+    assert_close('rot_3d', res.rot_3d, want['rot_3d'])
+    assert_close('loc_2d', res.loc_2d, want['loc_2d'])
+    assert_close('loc_3d', res.loc_3d, want['loc_3d'])
+    assert_close('total', res.total, want['total'])
+    assert float(res.losses[10]) == n * l * c['b'] * 9
+    assert_close_fp32_aware('grad', x.grad, g64, g32)

@@ -137,7 +137,7 @@ def test_world_from_changes(api):
 def test_projection_module_and_losses_against_oracle(api, mode):
     """ProjectionModule.forward -> Normalizer -> LossModes (the reference's unfused call sequence,
     modules/flow/pose_lifting.py:121-195 + base.py:440-469) with autograd back to the 6-D model output."""
-    c = make_case(6, 8, 21)
+    c = make_case(6, 8, 21, mode=mode)
     gt2, gt3 = make_targets(c, mode)
     d6 = c['d6'].clone().requires_grad_(True)
     want = oracle_step(c, O.rotation_6d_to_matrix(d6), mode, gt=(gt2, gt3))

@@ -3,7 +3,7 @@ import pytest
 import torch
 
 import oracle as O
-from _util import assert_close, carla, make_case, random_rotations, smpl_parents
+from _util import assert_close, assert_close_fp32_aware, carla, make_case, random_rotations, smpl_parents
 
 pytestmark = pytest.mark.gpu
 
@@ -269,7 +269,7 @@ def _fk_reference(c, mats, mode, ups):
     ins = [t.clone().requires_grad_(True) for t in (mats,)]
     ref_loc, ref_rot = c['loc'][c['sid']], c['rot'][c['sid']]
     n, l = c['n'], c['l']
-    wl, wr = O.calculate_world_from_changes((n, l), c['wl'], c['wr'], dtype=torch.float64)
+    wl, wr = O.calculate_world_from_changes((n, l), c['wl'], c['wr'], dtype=mats.dtype)
     if mode == 'pose_changes':
         rl, rr, al, ar = O.abs_from_pose_changes(ins[0], ref_loc, ref_rot, c['par'])
     else:
@@ -302,6 +302,7 @@ def test_fk_module_api_kernels(ops, lib, request, monkeypatch, tile, mode, n, l,
     b = c['b']
     spread = 0.02 if l > 32 else 0.1      # (products of 100 non-rotations: keep them from exploding)
     mats = O.rotation_6d_to_matrix(c['d6']) + torch.randn((n, l, b, 3, 3), generator=g, dtype=torch.float64) * spread
+    mats = mats.float().double()     # the oracle gets exactly the fp32 matrices the kernels get
     shapes = ((n, l, b, 3, 3), (n, l, b, 3, 3), (n, l, b, 3), (n, l, b, 3))
     ups = [torch.randn(s, generator=g, dtype=torch.float64) for s in shapes]
     ref = _fk_reference(c, mats, mode, ups)
@@ -317,7 +318,11 @@ def test_fk_module_api_kernels(ops, lib, request, monkeypatch, tile, mode, n, l,
     closs.backward()
     assert_close('abs_rot', car, ref['ar'])
     assert_close('abs_loc', cal, ref['al'])
-    assert_close('proj', cproj, ref['proj'])
+    # pixel coordinates: joints near the image centre are small differences of numbers ~400, where the reference's own
+    # fp32 evaluation is as far from float64 as the kernel's
+    c32 = dict(c, loc=c['loc'].float(), rot=c['rot'].float(), wl=c['wl'].float(), wr=c['wr'].float())
+    ref32 = _fk_reference(c32, mats.float(), mode, [u.float() for u in ups])
+    assert_close_fp32_aware('proj', cproj, ref['proj'], ref32['proj'], slack=5.0)
     assert_close('g_pose_in', x.grad, ref['grad'])
 
 

@@ -88,6 +88,32 @@ def test_extra_losses_against_reference_golden(api, gold):
         assert_close('grad_d6_' + ours, d6.grad, gold['loss/grad_d6_' + theirs], 2e-4)
 
 
+def test_rotation_losses_fused_in_the_step_against_reference_golden(api, gold):
+    """rot_3d / loc_rot_3d / loc_2d_loc_rot_3d / weighted_loc_2d_loc_rot_3d through ProjectionModule.fused_step (ONE
+    launch: rot_3d is formed where abs_rot sits in shared memory, its gradient joins the torque pass) against the values
+    and d/d(6-D) the reference's own code produced (tests/golden/reference_widen.npz)."""
+    sid = gold['skeleton_id']
+    n, l = gold['loss/d6'].shape[:2]
+    pm = api['ProjectionModule'](api['MovementsModelOutputType'].pose_changes)
+    pm.on_batch_start((torch.zeros((n, l, 26, 2), device=DEV), None, _meta(sid)), 0)
+    targets = {'projection_2d_transformed': gold['loss/gt_projection_2d_transformed'].to(DEV),
+               'absolute_pose_loc': gold['loss/gt_absolute_pose_loc'].to(DEV),
+               'absolute_pose_rot': gold['loss/gt_absolute_pose_rot'].to(DEV)}
+    w = dict(zip(('loc_2d', 'loc_3d', 'rot_3d'), gold['loss/weights'].tolist()))
+    for mode, theirs in (('rot_3d', 'rot_3d'), ('loc_rot_3d', 'loc_rot_3d'), ('loc_2d_loc_rot_3d', 'loc_2d_loc_rot_3d'),
+                         ('weighted_loc_2d_loc_rot_3d', 'weighted')):
+        d6 = gold['loss/d6'].to(DEV).requires_grad_(True)
+        proj, out = pm.fused_step(d6, targets, loss_weights=w, loss_mode=mode)
+        assert_close(mode, out['loss'][mode], gold['loss/' + theirs])
+        assert_close('rot_3d', out['loss']['rot_3d'], gold['loss/rot_3d'])
+        assert_close('absolute_pose_rot', out['absolute_pose_rot'], gold['loss/absolute_pose_rot'])
+        if 'loss/grad_d6_' + theirs in gold:
+            out['loss'][mode].backward()
+            assert_close('grad_d6_' + mode, d6.grad, gold['loss/grad_d6_' + theirs], 2e-4)
+    with pytest.raises(NotImplementedError):
+        pm.fused_step(gold['loss/d6'].to(DEV), targets, loss_mode='cum_pose_changes')
+
+
 def test_missing_targets_give_none(api):
     L = api['LossModes']
     x = torch.zeros((1, 2, 26, 3, 3), device=DEV)
@@ -384,6 +410,14 @@ def test_device_target_generator(api):
     x, t, meta = ds.generate_batch()
     assert x.shape == (12, 9, 26, 2) and len(meta['age']) == 12
     e = t['euler_pose_changes']
+    # the draws themselves: ONE kernel, restated bit for bit by the oracle (counter-based Philox stream)
+    we, ww, ws = O.draw_sparse_changes(22742, 0, 12, 9, 26, 3, np.float32(np.deg2rad(5)), np.float32(np.deg2rad(2)),
+                                       np.float32(np.deg2rad(30)))
+    assert np.array_equal(e.cpu().numpy(), we)
+    assert np.array_equal(meta['skeleton_index'].cpu().numpy(), ws)
+    yaw = torch.atan2(t['world_rot_changes'][..., 1, 0], t['world_rot_changes'][..., 0, 0]).cpu().numpy()
+    assert np.allclose(yaw, ww[..., 2], atol=1e-6)
+    assert [TYPES[i] for i in ws.tolist()] == list(zip(meta['age'], meta['gender']))
     changed = (e.abs().sum(-1) > 0).sum(-1)
     assert int(changed.min()) == 3 and int(changed.max()) == 3           # exactly 3 distinct bones per frame
     assert float(e.abs().max()) <= np.deg2rad(5) + 1e-7
@@ -407,5 +441,10 @@ def test_device_target_generator(api):
     ds2 = Carla2D3DIterableDataset(batch_size=12, clip_length=9, max_world_rot_change_in_deg=2,
                                    max_initial_world_rot_change_in_deg=30, transform='hips_neck', device=DEV, seed=22742)
     assert torch.equal(ds2.generate_batch()[0], x)
+    second = ds2.generate_batch()
+    assert not torch.equal(second[0], x)      # the batch counter advances the stream
+    we2, _, _ = O.draw_sparse_changes(22742, 1, 12, 9, 26, 3, np.float32(np.deg2rad(5)), np.float32(np.deg2rad(2)),
+                                      np.float32(np.deg2rad(30)))
+    assert np.array_equal(second[1]['euler_pose_changes'].cpu().numpy(), we2)
     item = next(iter(ds2))
     assert item[0].shape == (9, 26, 2) and item[1]['absolute_pose_loc'].shape == (9, 26, 3)

@@ -144,3 +144,24 @@ def test_oracle_gradient_finite_differences():
         xm[i] -= h
         fd = (f(xp) - f(xm)) / (2 * h)
         assert abs(float(fd) - float(x.grad[i])) <= 1e-6 * max(1.0, abs(float(fd)))
+
+
+def test_generator_stream_known_answers():
+    """The device generator's stream is Philox4x32-10 (Salmon et al., Random123): its published known-answer vectors
+    pin the oracle's restatement, which in turn pins the kernel bit for bit (tests/test_gpu_widen.py)."""
+    import numpy as np
+    kat = (((0, 0, 0, 0), (0, 0), (0x6627e8d5, 0xe169c58d, 0xbc57ac4c, 0x9b00dbd8)),
+           ((0xffffffff,) * 4, (0xffffffff,) * 2, (0x408f276d, 0x41c83b0e, 0xa20bc7c6, 0x6d5451fd)),
+           ((0x243f6a88, 0x85a308d3, 0x13198a2e, 0x03707344), (0xa4093822, 0x299f31d0),
+            (0xd16cfe09, 0x94fdcceb, 0x5001e420, 0x24126ea1)))
+    for ctr, key, want in kat:
+        got = O.philox4x32_10(*[[c] for c in ctr], *key)
+        assert tuple(int(g[0]) for g in got) == want
+    e, w, s = O.draw_sparse_changes(22742, 3, 40, 7, 26, 3, 0.0873, 0.03, 0.5)
+    assert ((np.abs(e).sum(-1) > 0).sum(-1) == 3).all()            # exactly 3 distinct bones per frame
+    assert float(np.abs(e).max()) <= 0.0873 and (w[..., :2] == 0).all()
+    assert float(np.abs(w[:, 1:, 2]).max()) <= 0.03 and float(np.abs(w[:, 0, 2]).max()) <= 0.5
+    assert set(s.tolist()) <= {0, 1, 2, 3} and len(set(s.tolist())) == 4
+    # every bone gets chosen, about uniformly (40*7*3 = 840 picks over 26 bones)
+    counts = (np.abs(e).sum(-1) > 0).sum((0, 1))
+    assert counts.min() > 10 and counts.max() < 60

@@ -15,7 +15,10 @@ def main():
     for spec in sys.argv[1:]:
         name, defs = spec.split('=', 1)
         out = os.path.join(_build.PKG_DIR, 'libp2c_%s.so' % name)
-        print(_build.build(force=True, defines=[d for d in defs.split(',') if d], out=out))
+        # NAME=DEF1,DEF2 : extra -D flags;  NAME=file.cu:/path/to/other_version.cu : swap one source file
+        overrides = {d.split(':', 1)[0]: d.split(':', 1)[1] for d in defs.split(',') if ':' in d}
+        print(_build.build(force=True, defines=[d for d in defs.split(',') if d and ':' not in d], out=out,
+                           overrides=overrides))
 
 
 if __name__ == '__main__':
