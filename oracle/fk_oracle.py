@@ -267,7 +267,17 @@ def reference_camera():
 
 def project(x, loc, rot, cam):
     """p3d_pose_projection.py:115-152 with PerspectiveCameras(in_ndc=False).transform_points_screen
-    of pytorch3d 0.6.0 reduced to closed form: u = px - f X/Z, v = py - f Y/Z, out_z = 1/Z."""
+    of pytorch3d 0.6.0 reduced to closed form: u = px - f X/Z, v = py - f Y/Z, out_z = 1/Z.
+
+    PARITY UNPINNED (pytorch3d is not installable here; the reference pins `pytorch3d==0.6.0`, Dockerfile:16,98-99 /
+    environment.yml:225 -- the v0.6.0 release tag; no commit hash is recorded by the reference).  Read from that
+    release's renderer/cameras.py + renderer/utils semantics: for a camera defined in screen space (in_ndc=False)
+    `transform_points_screen` composes  view (R, T)  ->  the screen-space projection  x_s = f X/Z + px  ->
+    screen-to-NDC WITHOUT the axis flip  x_n = (x_s - cx) / s  ->  NDC-to-screen WITH the flip (+X left, +Y up in
+    NDC)  u = cx - s x_n = 2 cx - (f X/Z + px),  cx = W/2, and hands back 1/Z in the third channel.  The reference's
+    principal point IS the image centre (px = W/2, p3d_pose_projection.py:55-63), so  u = px - f X/Z.  The one open
+    point: a pytorch3d release that centres NDC at (W-1)/2 would shift raw `projection_2d` by exactly ONE PIXEL in u and
+    v; the hips/neck-normalised projection, every loss and every gradient on this path are invariant to that shift."""
     n = x.shape[0]
     dt = x.dtype
     p3d_2_world = torch.tensor(((0., -1., 0.), (1., 0., 0.), (0., 0., 1.)), dtype=dt).expand(n, -1, -1)

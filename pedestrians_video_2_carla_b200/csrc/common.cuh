@@ -178,12 +178,21 @@ __device__ __forceinline__ void exchange_publish(const XchgArgs x, float s0, flo
     const unsigned long long* table = reinterpret_cast<const unsigned long long*>(x.block);
     const size_t off = XCHG_HEADER_WORDS + ((size_t)(seq % XCHG_DEPTH) * XCHG_MAX_RANKS + x.rank) * XCHG_ENTRY_WORDS;
     const float v[4] = {s0, s1, s2, s3};
-    for (int r = 0; r < x.world; ++r) {
-        float* slot = reinterpret_cast<float*>(__ldcg(table + r)) + off;
+    // every peer pointer is requested before the first store goes out: ONE L2 round trip for the whole table instead
+    // of one per rank in front of its stores (measured at 8 ranks: 2 us of the finishing thread, on the step's tail)
+    unsigned long long peer[XCHG_MAX_RANKS];
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
-            asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1, %2};" ::"l"(slot + 2 * k), "r"(__float_as_uint(v[k])), "r"(seq)
-                         : "memory");
+    for (int r = 0; r < XCHG_MAX_RANKS; ++r) peer[r] = r < x.world ? __ldcg(table + r) : 0ull;
+#pragma unroll
+    for (int r = 0; r < XCHG_MAX_RANKS; ++r) {
+        if (r < x.world) {
+            float* slot = reinterpret_cast<float*>(peer[r]) + off;
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1, %2};" ::"l"(slot + 2 * k), "r"(__float_as_uint(v[k])),
+                             "r"(seq)
+                             : "memory");
+        }
     }
 }
 

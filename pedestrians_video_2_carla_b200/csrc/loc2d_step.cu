@@ -43,6 +43,7 @@ __global__ void __launch_bounds__(LT, 1) loc2d_step_kernel(const Loc2dArgs a) {
     const int pairs = nj >> 1;
     const float4* p4 = reinterpret_cast<const float4*>(a.pred + j0 * 2);
     float4* e4 = reinterpret_cast<float4*>(esm);
+#pragma unroll 4   // (the loads of four trips in flight together: a CTA per SM needs ~64 KB outstanding to stream)
     for (int q = tid; q < pairs; q += LT) {
         const float4 p = __ldcs(p4 + q);   // streaming: read once
         float g0x, g0y, g1x, g1y;
@@ -125,6 +126,7 @@ __global__ void __launch_bounds__(LT, 1) loc2d_step_kernel(const Loc2dArgs a) {
     __syncthreads();
     const float k = k_shared;
     float4* o4 = reinterpret_cast<float4*>(a.g_pred + j0 * 2);
+#pragma unroll 4
     for (int q = tid; q < pairs; q += LT) {
         const float4 e = e4[q];
         __stcs(o4 + q, make_float4(k * e.x, k * e.y, k * e.z, k * e.w));

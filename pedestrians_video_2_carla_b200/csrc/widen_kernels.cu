@@ -736,6 +736,12 @@ int renorm_args(Renorm& a, int64_t m, int32_t j, int32_t c, int32_t dim, int32_t
 
 }  // namespace
 
+// pose-per-lane variants (lane_kernels.cu): 1 = launched, 0 = declined, -1 = launch error
+extern "C" int p2c_renorm_lane(const float* in, const float* g_out, float* out, int64_t m, int32_t j, int32_t dim,
+                               int32_t hips, int32_t neck, int32_t autonormalize, const float* ref_shift,
+                               const float* ref_scale, const int32_t* ref_index, int32_t clip_len, int backward,
+                               void* stream);
+
 extern "C" int p2c_cum_changes_fwd(const float* changes, float* cumulative, int32_t n_clips, int32_t clip_len,
                                    int32_t n_bones, void* stream) {
     if (n_clips < 0 || clip_len < 1 || n_bones < 1) return P2C_E_BADARG;
@@ -792,7 +798,7 @@ extern "C" int p2c_renormalize_fwd(const float* sample, float* out, int64_t m, i
     if (rc) return rc;
     if (m == 0) return 0;
     if (!sample || !out) return P2C_E_NULL;
-    if (c == dim) {   // no carried channel: the chunked float4 variant
+    if (c == dim) {   // no carried channel: the chunked float4 variant (the pose-per-lane forward measured the same)
         if (dim == 2)
             renorm_flat_fwd_kernel<2><<<chunk_grid(m), RTH, 0, (cudaStream_t)stream>>>(sample, out, a);
         else
@@ -819,6 +825,12 @@ extern "C" int p2c_renormalize_bwd(const float* sample, const float* g_out, floa
     if (rc) return rc;
     if (m == 0) return 0;
     if (!sample || !g_out || !g_sample) return P2C_E_NULL;
+    if (c == dim) {
+        const int took = p2c_renorm_lane(sample, g_out, g_sample, m, j, dim, hips, neck, autonormalize, nullptr, ref_scale,
+                                         ref_index, clip_len, 1, stream);
+        if (took > 0) return 0;
+        if (took < 0) return (int)cudaErrorLaunchFailure;
+    }
     if (c == dim && (size_t)2 * RP * j * dim * sizeof(float) <= 40 * 1024) {   // else: the warp-per-pose kernels
         a.ref_shift = nullptr;   // the shift does not enter the gradient
         if (dim == 2)

@@ -128,6 +128,7 @@ class _FkClip(torch.autograd.Function):
         check(_lib.load().p2c_fk_fwd(a, stream()), 'fk_fwd')
         ctx.save_for_backward(pose_in, ref_loc, ref_rot, ref_index, world_loc, world_rot, rel_rot, abs_rot, abs_loc)
         ctx.tree, ctx.camera, ctx.mode, ctx.want_proj = tree, camera, mode, want_proj
+        ctx.set_materialize_grads(False)   # outputs nobody differentiates stay None (no zero tensors for the kernel to read)
         if rel_rot is None:
             rel_rot = pose_in.new_empty(0)
         if proj is None:

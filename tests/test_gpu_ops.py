@@ -323,7 +323,8 @@ def test_fk_module_api_kernels(ops, lib, request, monkeypatch, tile, mode, n, l,
     c32 = dict(c, loc=c['loc'].float(), rot=c['rot'].float(), wl=c['wl'].float(), wr=c['wr'].float())
     ref32 = _fk_reference(c32, mats.float(), mode, [u.float() for u in ups])
     assert_close_fp32_aware('proj', cproj, ref['proj'], ref32['proj'], slack=5.0)
-    assert_close('g_pose_in', x.grad, ref['grad'])
+    # (16 - 100 chained products of NON-rotations: the chain rule multiplies rounding like the values themselves)
+    assert_close_fp32_aware('g_pose_in', x.grad, ref['grad'], ref32['grad'], slack=5.0)
 
 
 def test_fk_tile_partial_upstream_and_no_projection(ops, lib):
