@@ -593,6 +593,7 @@ def main():
         # every rank's steps are complete (timed_region ends with synchronize + barrier): read what the peers' kernels
         # stored into THIS rank's block for the last step
         import torch.distributed as dist
+        exchange.flush()              # (a step's sums leave at the start of the next step's kernel: send the last ones)
         torch.cuda.synchronize()
         dist.barrier()
         got = exchange.read().cpu().tolist()

@@ -230,6 +230,11 @@ int p2c_exchange_close(void* peer_block);
 int p2c_exchange_destroy(void* block);
 int p2c_exchange_set_peers(void* block, void* const* peer_blocks, int32_t world);
 int p2c_exchange_read(const void* block, int32_t world, uint32_t seq, float* out, void* stream);
+/* The step kernels on the latency-critical path (p2c_fused_step's tile kernel, p2c_loc2d_step) leave their sums in the
+ * rank's own block and SEND them at the start of the next step's kernel (remote stores on a kernel's tail delay its
+ * completion by an NVLink round trip).  p2c_exchange_flush sends what is still waiting: enqueue it behind the last
+ * step, before the synchronisation point that precedes p2c_exchange_read.                                           */
+int p2c_exchange_flush(void* block, int32_t rank, int32_t world, void* stream);
 
 /* ---- pytorch3d 0.6.0 quaternion_to_matrix (real part first, not normalised first): the quaternion entry the
  *      north star names next to euler_angles_to_matrix (walker_control/p3d_pose.py:54) and rotation_6d_to_matrix

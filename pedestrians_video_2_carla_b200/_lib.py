@@ -85,6 +85,7 @@ _SIGS = {
     'p2c_exchange_destroy': (C.c_int, [_P]),
     'p2c_exchange_set_peers': (C.c_int, [_P, C.POINTER(_P), C.c_int32]),
     'p2c_exchange_read': (C.c_int, [_P, C.c_int32, C.c_uint32, _P, _P]),
+    'p2c_exchange_flush': (C.c_int, [_P, C.c_int32, C.c_int32, _P]),
     'p2c_quaternion_to_matrix_fwd': (C.c_int, [_P, _P, C.c_int64, _P]),
     'p2c_quaternion_to_matrix_bwd': (C.c_int, [_P, _P, _P, C.c_int64, _P]),
     'p2c_cum_changes_fwd': (C.c_int, [_P, _P, C.c_int32, C.c_int32, C.c_int32, _P]),

@@ -150,12 +150,13 @@ __device__ __forceinline__ void m3_to(float* s, const M3& a) {
 }
 
 // ---- loss-sum exchange block (include/p2c_b200.h, p2c_exchange_*): the path's only cross-GPU step, done by the step
-//      kernel itself.  Layout of a rank's block (bytes): [0,128) 16 peer-mapped base pointers, one per rank (slot r =
-//      rank r's block as THIS rank addresses it); [128,132) sequence number of the last step this rank published;
-//      [256, ...) DEPTH x 16 entries of 8 words: {sum_sq_2d, seq, count_2d, seq, sum_sq_3d, seq, count_3d, seq}, entry
-//      [seq % DEPTH][r] = rank r's sums of its step number `seq`.  Every value travels with the sequence number in ONE
-//      aligned 8-byte store (single-copy atomic): an entry whose four sequence words equal `seq` is complete, whatever
-//      order the stores land in -- no release fence, so the publishing thread never waits for a peer's acknowledgement.
+//      kernels themselves.  Layout of a rank's block (32-bit words): [0,32) 16 peer-mapped base pointers, one per rank
+//      (slot r = rank r's block as THIS rank addresses it); [32] number of steps this rank has finished; [33] number of
+//      steps it has sent; [36,40) / [40,44) the sums of the last two finished steps (slot = step & 1), waiting to be
+//      sent; [64, ...) DEPTH x 16 entries of 8 words {sum_sq_2d, seq, count_2d, seq, sum_sq_3d, seq, count_3d, seq},
+//      entry [seq % DEPTH][r] = rank r's sums of its step number `seq`.  Every value travels with the sequence number
+//      in ONE aligned 8-byte store (single-copy atomic): an entry whose four sequence words equal `seq` is complete,
+//      whatever order the stores land in -- no release fence, the sending thread never waits for an acknowledgement.
 constexpr int XCHG_DEPTH = 16;
 constexpr int XCHG_MAX_RANKS = 16;
 constexpr int XCHG_HEADER_WORDS = 64;
@@ -167,33 +168,52 @@ struct XchgArgs {   // by value in the kernel arguments; block == nullptr: no ex
     int rank, world;
 };
 
-// One thread (the one that finishes the step's loss sums) stores this rank's four sums into entry [seq][rank] of EVERY
-// rank's block: four relaxed 8-byte (value, seq) stores per rank, over NVLink for the peers.  Fire and forget: nothing
-// waits for a peer.  The step counter lives in the block, so CUDA-graph replays keep counting.
-__device__ __forceinline__ void exchange_publish(const XchgArgs x, float s0, float s1, float s2, float s3) {
+// The thread that finishes a step's loss sums leaves them in the rank's OWN block (two plain local stores): nothing
+// crosses NVLink on the step's tail.
+__device__ __forceinline__ void exchange_stash(const XchgArgs x, float s0, float s1, float s2, float s3) {
     if (!x.block) return;
-    unsigned* counter = reinterpret_cast<unsigned*>(x.block) + 32;
-    const unsigned seq = __ldcg(counter) + 1u;   // (only the finishing thread of this stream's steps writes it)
-    *counter = seq;
+    unsigned* hdr = reinterpret_cast<unsigned*>(x.block);
+    const unsigned seq = __ldcg(hdr + 32) + 1u;   // (only the finishing thread of this stream's steps writes it)
+    *reinterpret_cast<float4*>(x.block + 36 + 4 * (seq & 1u)) = make_float4(s0, s1, s2, s3);
+    hdr[32] = seq;
+}
+// Sends what is waiting (the sums of the step before) into entry [seq][rank] of EVERY rank's block: four relaxed 8-byte
+// (value, seq) stores per rank, over NVLink for the peers.  Called by one thread at the START of the next step's kernel
+// -- the stores then have the whole step to land (issued on the tail they cost 1.2 us per 14 us step: a kernel is
+// not complete before its remote writes are acknowledged) -- and by p2c_exchange_flush behind the last step.
+__device__ __forceinline__ void exchange_send_pending(const XchgArgs x) {
+    if (!x.block) return;
+    unsigned* hdr = reinterpret_cast<unsigned*>(x.block);
+    const unsigned last = __ldcg(hdr + 32), sent = __ldcg(hdr + 33);
+    if (last == sent) return;
     const unsigned long long* table = reinterpret_cast<const unsigned long long*>(x.block);
-    const size_t off = XCHG_HEADER_WORDS + ((size_t)(seq % XCHG_DEPTH) * XCHG_MAX_RANKS + x.rank) * XCHG_ENTRY_WORDS;
-    const float v[4] = {s0, s1, s2, s3};
-    // every peer pointer is requested before the first store goes out: ONE L2 round trip for the whole table instead
-    // of one per rank in front of its stores (measured at 8 ranks: 2 us of the finishing thread, on the step's tail)
-    unsigned long long peer[XCHG_MAX_RANKS];
+    unsigned long long peer[XCHG_MAX_RANKS];   // every peer pointer requested before the first store goes out
 #pragma unroll
     for (int r = 0; r < XCHG_MAX_RANKS; ++r) peer[r] = r < x.world ? __ldcg(table + r) : 0ull;
+    // (the block keeps the last TWO finished steps: a stashing kernel followed by one that publishes at once loses nothing)
+    for (unsigned seq = (last - sent > 1u) ? last - 1u : last;; ++seq) {
+        const float4 v4 = __ldcg(reinterpret_cast<const float4*>(x.block + 36 + 4 * (seq & 1u)));
+        const size_t off = XCHG_HEADER_WORDS + ((size_t)(seq % XCHG_DEPTH) * XCHG_MAX_RANKS + x.rank) * XCHG_ENTRY_WORDS;
+        const float v[4] = {v4.x, v4.y, v4.z, v4.w};
 #pragma unroll
-    for (int r = 0; r < XCHG_MAX_RANKS; ++r) {
-        if (r < x.world) {
-            float* slot = reinterpret_cast<float*>(peer[r]) + off;
+        for (int r = 0; r < XCHG_MAX_RANKS; ++r) {
+            if (r < x.world) {
+                float* slot = reinterpret_cast<float*>(peer[r]) + off;
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-                asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1, %2};" ::"l"(slot + 2 * k), "r"(__float_as_uint(v[k])),
-                             "r"(seq)
-                             : "memory");
+                for (int k = 0; k < 4; ++k)
+                    asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1, %2};" ::"l"(slot + 2 * k),
+                                 "r"(__float_as_uint(v[k])), "r"(seq)
+                                 : "memory");
+            }
         }
+        if (seq == last) break;
     }
+    hdr[33] = last;
+}
+// (kernels that are not on the latency-critical path publish at once)
+__device__ __forceinline__ void exchange_publish(const XchgArgs x, float s0, float s1, float s2, float s3) {
+    exchange_stash(x, s0, s1, s2, s3);
+    exchange_send_pending(x);
 }
 
 // Host-side tree preprocessing shared by the launchers.

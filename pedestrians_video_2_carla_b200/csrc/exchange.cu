@@ -44,7 +44,17 @@ __global__ void exchange_read_kernel(const float* __restrict__ block, int world,
     }
 }
 
+__global__ void exchange_flush_kernel(const XchgArgs x) { exchange_send_pending(x); }
+
 }  // namespace
+
+extern "C" int p2c_exchange_flush(void* block, int32_t rank, int32_t world, void* stream) {
+    if (!block) return P2C_E_NULL;
+    if (world < 1 || world > XCHG_MAX_RANKS || rank < 0 || rank >= world) return P2C_E_BADARG;
+    exchange_flush_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(XchgArgs{reinterpret_cast<float*>(block), rank, world});
+    P2C_LAUNCH_CHECK();
+    return 0;
+}
 
 extern "C" int64_t p2c_exchange_block_bytes(void) { return (int64_t)XCHG_BLOCK_BYTES; }
 extern "C" int32_t p2c_exchange_max_ranks(void) { return XCHG_MAX_RANKS; }

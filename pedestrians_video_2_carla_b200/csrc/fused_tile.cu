@@ -314,7 +314,7 @@ __device__ __noinline__ void finish_losses(const FoldArgs a, double d2, double d
     a.losses[0] = l2; a.losses[1] = l3; a.losses[2] = total;
     a.losses[3] = (float)d2; a.losses[4] = (float)c2; a.losses[5] = (float)d3; a.losses[6] = (float)a.count3;
     a.losses[7] = 0.f;
-    exchange_publish(a.xchg, (float)d2, (float)c2, (float)d3, (float)a.count3);
+    exchange_stash(a.xchg, (float)d2, (float)c2, (float)d3, (float)a.count3);   // (sent by the next step's kernel)
     a.header[0] = 0u;   // self-resetting workspace header: ready for the next launch
     a.header[2] = 0u;
     a.header[3] = 0u;
@@ -410,6 +410,9 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         // (one tile per CTA) let the next kernel's CTAs take the SMs as this grid's CTAs retire
         if (a.count_inline) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     }
+    // data-parallel ranks: the sums the previous step left in this rank's exchange block go out to the peers now, so
+    // that their NVLink round trip is over long before this kernel's own tail
+    if (blockIdx.x == 0 && tid == (W - 2) * 32) exchange_send_pending(a.xchg);
     if (tma) {
         if ((int)blockIdx.x < ntiles) {
             load_d6(blockIdx.x);

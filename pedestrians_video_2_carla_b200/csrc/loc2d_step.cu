@@ -36,6 +36,7 @@ __device__ __forceinline__ bool kept2(float gx, float gy, int j, int hips) {
 __global__ void __launch_bounds__(LT, 1) loc2d_step_kernel(const Loc2dArgs a) {
     extern __shared__ __align__(16) float esm[];   // masked errors of this CTA's joints, (x, y) pairs
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (blockIdx.x == 0 && tid == LT - 32) exchange_send_pending(a.xchg);   // the previous step's sums, off the tail
     const long j0 = (long)blockIdx.x * a.per_cta;   // (per_cta is even: pairs never straddle CTAs)
     long left = a.joints - j0;
     const int nj = left <= 0 ? 0 : (left < a.per_cta ? (int)left : a.per_cta);
@@ -115,7 +116,7 @@ __global__ void __launch_bounds__(LT, 1) loc2d_step_kernel(const Loc2dArgs a) {
             k_shared = (float)((double)a.upstream * 2.0 / dc);   // count 0: inf / NaN like nn.MSELoss on an empty selection
             if (blockIdx.x == 0) {
                 a.out[0] = (float)(ds / dc); a.out[1] = (float)ds; a.out[2] = (float)dc; a.out[3] = 0.f;
-                exchange_publish(a.xchg, (float)ds, (float)dc, 0.f, 0.f);
+                exchange_stash(a.xchg, (float)ds, (float)dc, 0.f, 0.f);   // (sent by the next step's kernel)
             }
             // the last CTA to leave resets the barrier words for the next launch
             unsigned gone;

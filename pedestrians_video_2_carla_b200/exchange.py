@@ -81,11 +81,16 @@ class LossExchange(object):
         args.exchange_rank, args.exchange_world = self.rank, self.world
         return args
 
+    def flush(self):
+        """Send the sums of the last step (the step kernels send a step's sums at the start of the NEXT step's kernel,
+        off their own tail).  Enqueue on the steps' stream before the synchronisation point that precedes read()."""
+        check(_lib.load().p2c_exchange_flush(C.c_void_p(self.block), self.rank, self.world, _lib.stream()), 'exchange_flush')
+
     def read(self, seq=0, out=None):
         """(8,) device tensor {sum_sq_2d, count_2d, sum_sq_3d, count_3d, ranks arrived, global loc_2d, global loc_3d,
         seq} of step `seq` (1-based; 0 = the last step this rank published).  Enqueued on the current stream; never
-        waits for a peer -- order it behind the peers' steps (e.g. after the barrier that ends an epoch or a logging
-        interval) and check [4] == world."""
+        waits for a peer -- every rank calls flush(), synchronises and meets the others (the barrier that ends an epoch
+        or a logging interval) before anyone reads; check [4] == world."""
         if out is None:
             out = torch.empty(8, device='cuda')
         check(_lib.load().p2c_exchange_read(C.c_void_p(self.block), self.world, int(seq) & 0xffffffff, _lib.ptr(out),

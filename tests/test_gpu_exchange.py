@@ -37,6 +37,8 @@ def test_emulated_ranks_sum_to_the_unsharded_losses(n, l, world):
         for rep in range(3):   # three steps: the sequence numbers advance
             for r in range(world):
                 _step(ops, _lib, c, gt2, gt3, bounds[r], bounds[r + 1], dev, xs[r])
+        for r in range(world):
+            xs[r].flush()             # a step's sums are sent by the next step's kernel: send the last ones
         torch.cuda.synchronize()
         for r in range(world):
             assert xs[r].steps == 3
@@ -90,6 +92,7 @@ def _rank_main(rank, world, port, n, l, seed, queue):
     lo, hi = n * rank // world, n * (rank + 1) // world
     for _ in range(2):
         _step(ops, _lib, c, gt2, gt3, lo, hi, dev, x)
+    x.flush()
     torch.cuda.synchronize()
     dist.barrier()            # the peers' steps are complete: their stores are in this rank's block
     queue.put((rank, x.read().cpu().tolist()))
