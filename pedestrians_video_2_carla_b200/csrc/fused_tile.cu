@@ -477,7 +477,8 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         // the reference rotations that start the scan of this thread's first (clip, bone, column) item: asked for now,
         // used after phase A (an L2 round trip on the SMs far from the table's slice)
         float q0 = 0.f, q1 = 0.f, q2 = 0.f;
-        if (a.scan && tid < tile_clips * B3) {
+        const bool split_scan = slices == 2 && np > 32;   // a clip over two slices: its halves are scanned side by side
+        if (a.scan && tid < tile_clips * B3) {   // (first-half items only when the scan is split: tile_clips == 1)
             const int cl = tid / B3, rem = tid - cl * B3;
             const float* rr = a.ref_rot + (size_t)row[cl * L] * B9 + (rem / 3) * 9 + rem % 3;
             q0 = __ldg(rr); q1 = __ldg(rr + 3); q2 = __ldg(rr + 6);
@@ -506,24 +507,33 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         // ---- phase B: R[t] = C[t] . R[t-1] (p3d_pose.py:98-114 looped by layers/projection.py:190-193); one thread
         //      per (clip, bone, column of R), serial over the frames of the clip
         if (a.scan) {
-            const int items = tile_clips * B3;
+            // A clip over two slices (33..64 frames; the tile is that ONE clip): the two halves are scanned side by side --
+            // frames 0..31 from the reference rotation, frames 32.. from the identity (a column of the prefix product only
+            // needs the same column of its predecessor) -- and the second half is multiplied by R[31] afterwards, one
+            // bone per warp task: 32 dependent steps instead of 64.
+            const int items = (split_scan ? 2 : tile_clips) * B3;
 #pragma unroll 1
             for (int idx = tid; idx < items; idx += NT) {
                 const int cl = idx / B3, rem = idx - cl * B3, b = rem / 3, j = rem - b * 3;
+                const bool second = split_scan && cl == 1;
+                const int f0 = split_scan ? cl * 32 : cl * L;            // first frame (lane column) of this item
+                const int nf = split_scan ? (cl ? np - 32 : 32) : L;     // frames it runs over
                 float p0 = q0, p1 = q1, p2 = q2;
-                if (idx != tid) {
-                    const float* rr = a.ref_rot + ((size_t)row[cl * L] * B + b) * 9 + j;
+                if (second) {
+                    p0 = j == 0 ? 1.f : 0.f; p1 = j == 1 ? 1.f : 0.f; p2 = j == 2 ? 1.f : 0.f;
+                } else if (idx != tid) {
+                    const float* rr = a.ref_rot + ((size_t)row[f0] * B + b) * 9 + j;
                     p0 = __ldg(rr); p1 = __ldg(rr + 3); p2 = __ldg(rr + 6);
                 }
-                const float* src = A + (cl * L) * B9 + b * 9;
-                float* dst = R + (cl * L) * B9 + b * 9 + j;
+                const float* src = A + f0 * B9 + b * 9;
+                float* dst = R + f0 * B9 + b * 9 + j;
                 // two frames per trip; the records of the next two frames are in flight while these products run
                 float c[9], e[9];
 #pragma unroll
                 for (int i = 0; i < 9; ++i) c[i] = src[i];
                 int f = 0;
 #pragma unroll 1
-                for (; f + 2 <= L; f += 2) {
+                for (; f + 2 <= nf; f += 2) {
 #pragma unroll
                     for (int i = 0; i < 9; ++i) e[i] = src[B9 + i];
                     const float n0 = fmaf(c[2], p2, fmaf(c[1], p1, c[0] * p0));
@@ -531,7 +541,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                     const float n2 = fmaf(c[8], p2, fmaf(c[7], p1, c[6] * p0));
                     dst[0] = n0; dst[3] = n1; dst[6] = n2;
                     src += 2 * B9;
-                    if (f + 2 < L) {
+                    if (f + 2 < nf) {
 #pragma unroll
                         for (int i = 0; i < 9; ++i) c[i] = src[i];
                     }
@@ -541,7 +551,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                     dst[B9] = p0; dst[B9 + 3] = p1; dst[B9 + 6] = p2;
                     dst += 2 * B9;
                 }
-                if (f < L) {   // odd clip length: the last frame
+                if (f < nf) {   // odd frame count: the last frame
                     dst[0] = fmaf(c[2], p2, fmaf(c[1], p1, c[0] * p0));
                     dst[3] = fmaf(c[5], p2, fmaf(c[4], p1, c[3] * p0));
                     dst[6] = fmaf(c[8], p2, fmaf(c[7], p1, c[6] * p0));
@@ -578,6 +588,17 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                     if (ci == 0)
                         atomicAdd(reinterpret_cast<unsigned long long*>(a.count2),
                                   (1ull << 32) | (unsigned long long)(unsigned)cta_count);
+                }
+            }
+        }
+        if (a.scan && split_scan) {
+            __syncthreads();   // #2b: both halves of the clip are in R
+#pragma unroll 1
+            for (int b = warp; b < B; b += W) {   // R[t] = (C[t] .. C[32]) . R[31] for the second half, one bone per task
+                const int col = 32 + lane;
+                if (col < np) {
+                    const M3 Q = lds9(R + col * B9, b), P31 = lds9(R + 31 * B9, b);
+                    sts9(R + col * B9, b, m3_mul(Q, P31));
                 }
             }
         }

@@ -13,7 +13,10 @@
 
 namespace {
 
-constexpr int LT = 512;
+#ifndef P2C_LOC2D_THREADS
+#define P2C_LOC2D_THREADS 1024
+#endif
+constexpr int LT = P2C_LOC2D_THREADS;
 constexpr int MAX_CTAS = 1024;
 
 struct Loc2dArgs {
