@@ -32,6 +32,7 @@ extern "C" {
 #define P2C_E_BONES (-2)   /* n_bones outside 1..32 or parent[] not in DFS order */
 #define P2C_E_NULL (-3)    /* a required pointer is NULL */
 #define P2C_E_UNSUPPORTED (-4)
+#define P2C_E_TOO_LARGE (-5)   /* beyond the stated maximum of an entry point with built-in scratch (p2c_loc2d_step_static) */
 
 /* Bone tree: walker_control/pose.py:29-47 (structure.yaml walked depth-first). */
 typedef struct {
@@ -156,6 +157,20 @@ int p2c_loc2d_step_supported(int64_t m, int32_t j, int32_t c_gt);
 int p2c_loc2d_step(const float* pred, const float* gt, int64_t m, int32_t j, int32_t c_gt, int32_t mask_hips,
                    float upstream, float* g_pred, float* workspace, float* out, float* exchange,
                    int32_t exchange_rank, int32_t exchange_world, void* stream);
+
+/* ---- p2c_loc2d_step without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ *      for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ *      that forbid it).  Same kernel, arguments and results as p2c_loc2d_step (no workspace, no exchange); the scratch
+ *      (barrier words + per-CTA partial sums, 8704 bytes) is a file-scope device array that every GPU loading the library
+ *      holds until exit.  Calls no cudaMalloc / cudaFree / allocating routine.
+ *      Limit: m*j <= p2c_loc2d_step_static_max_joints() = 3 788 800 joints (145 723 poses of 26 joints: what one B200
+ *      keeps on chip); beyond it, or on a GPU too small for the batch, returns P2C_E_TOO_LARGE and launches nothing.
+ *      All calls on a device SHARE the scratch: calls that overlap on the GPU (different streams, no ordering) race;
+ *      calls on one stream, or ordered by events, are safe (the barrier words are cleared on the stream before every
+ *      launch, the partial sums are overwritten before they are read).                                              */
+int64_t p2c_loc2d_step_static_max_joints(void);
+int p2c_loc2d_step_static(const float* pred, const float* gt, int64_t m, int32_t j, int32_t c_gt, int32_t mask_hips,
+                          float upstream, float* g_pred, float* out, void* stream);
 
 /* ---- One pose_lifting step of the hot path, fused: ProjectionModule.forward
  *      (modules/layers/projection.py:73-123) -> Normalizer (modules/flow/pose_lifting.py:167-170) ->

@@ -74,6 +74,8 @@ _SIGS = {
     'p2c_loc2d_step_supported': (C.c_int, [C.c_int64, C.c_int32, C.c_int32]),
     'p2c_loc2d_step': (C.c_int, [_P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_float, _P, _P, _P, _P,
                                  C.c_int32, C.c_int32, _P]),
+    'p2c_loc2d_step_static_max_joints': (C.c_int64, []),
+    'p2c_loc2d_step_static': (C.c_int, [_P, _P, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_float, _P, _P, _P]),
     'p2c_fused_step_workspace_floats': (C.c_int64, [C.c_int64, C.c_int32, C.c_int32]),
     'p2c_fused_step': (C.c_int, [C.POINTER(FusedStep), _P]),
     'p2c_fused_step_launches': (C.c_int, [C.POINTER(FusedStep)]),
@@ -141,6 +143,8 @@ def exported_symbols():
 def check(rc, what):
     if rc != 0:
         kind = 'bad argument' if rc < 0 else 'CUDA error'
+        if rc == -5:
+            kind = 'size beyond the maximum of this entry point (P2C_E_TOO_LARGE)'
         raise RuntimeError('p2c_b200.%s failed: %s %d' % (what, kind, rc))
 
 

@@ -8,6 +8,8 @@
 // read once, gradient written once (624 B per 26-joint pose).  Run-to-run bitwise deterministic (fixed grid, fixed order).
 // Batches too large for the errors to stay on chip (> ~145 k poses of 26 joints) take the two-pass kernels of
 // loss_kernels.cu (the wrapper in ops.py picks).
+#include <mutex>
+
 #include "common.cuh"
 #include "host_util.h"
 
@@ -200,6 +202,82 @@ extern "C" int p2c_loc2d_step(const float* pred, const float* gt, int64_t m, int
     cfg.stream = (cudaStream_t)stream;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeCooperative;   // the CTAs wait for each other: all resident at once or no launch
+    attr[0].val.cooperative = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    const cudaError_t le = cudaLaunchKernelEx(&cfg, loc2d_step_kernel, a);
+    if (le != cudaSuccess) return (int)le;
+    P2C_LAUNCH_CHECK();
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------ no-allocation entry
+// p2c_loc2d_step_static: the same kernel with its scratch (barrier words + per-CTA partial sums) in a file-scope device
+// array instead of a caller-allocated workspace, for callers that cannot allocate (CUDA graph capture, serving loops).
+// Every GPU that loads the library holds the array until exit; every call on a device shares it.
+namespace {
+
+constexpr int STATIC_SCRATCH_FLOATS = 2176;   // 16 barrier words + 2 x MAX_CTAS partials = 2064, padded to 8704 bytes
+static_assert(STATIC_SCRATCH_FLOATS >= 16 + 2 * MAX_CTAS, "scratch too small for the largest grid");
+constexpr long STATIC_MAX_JOINTS = 148L * 25600L;   // 3 788 800: what one B200 keeps on chip (148 CTAs x 200 KB of errors)
+
+static __device__ __align__(256) float g_loc2d_scratch[STATIC_SCRATCH_FLOATS];
+
+constexpr int STATIC_MAX_DEVICES = 64;
+float* g_scratch_ptr[STATIC_MAX_DEVICES];   // device address of g_loc2d_scratch, per device (each device has its own copy)
+std::mutex g_scratch_mutex;
+
+// In host code g_loc2d_scratch is only a handle: the device address comes from cudaGetSymbolAddress, asked once per
+// device with that device current.
+int static_scratch(float** out) {
+    const int dev = p2c_current_device();
+    if (dev >= STATIC_MAX_DEVICES) return P2C_E_UNSUPPORTED;
+    std::lock_guard<std::mutex> lock(g_scratch_mutex);
+    if (!g_scratch_ptr[dev]) {
+        float* ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_loc2d_scratch);
+        if (e != cudaSuccess) return (int)e;
+        if (!ptr) return P2C_E_NULL;
+        g_scratch_ptr[dev] = ptr;
+    }
+    *out = g_scratch_ptr[dev];
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int64_t p2c_loc2d_step_static_max_joints(void) { return STATIC_MAX_JOINTS; }
+
+extern "C" int p2c_loc2d_step_static(const float* pred, const float* gt, int64_t m, int32_t j, int32_t c_gt,
+                                     int32_t mask_hips, float upstream, float* g_pred, float* out, void* stream) {
+    if (m < 0 || j < 1 || (c_gt != 2 && c_gt != 3) || mask_hips >= j) return P2C_E_BADARG;
+    if (m == 0) return 0;
+    if (!pred || !gt || !g_pred || !out) return P2C_E_NULL;
+    if (m > STATIC_MAX_JOINTS || (long)m * j > STATIC_MAX_JOINTS) return P2C_E_TOO_LARGE;
+    if ((reinterpret_cast<uintptr_t>(pred) | reinterpret_cast<uintptr_t>(g_pred)) & 15) return P2C_E_UNSUPPORTED;
+    if (reinterpret_cast<uintptr_t>(gt) & (c_gt == 2 ? 15 : 7)) return P2C_E_UNSUPPORTED;
+    const Loc2dPlan pl = loc2d_plan(m, j);
+    if (!pl.ok) return P2C_E_TOO_LARGE;   // (a GPU with fewer SMs than a B200 keeps fewer errors on chip)
+    if (16 + 2 * pl.grid > STATIC_SCRATCH_FLOATS) return P2C_E_TOO_LARGE;
+    float* scratch = nullptr;
+    if (const int e = static_scratch(&scratch)) return e;
+    // the array keeps the last call's contents: the barrier words must start at zero (a launch that failed half way
+    // would leave them set); the partials are overwritten before they are read
+    const cudaError_t me = cudaMemsetAsync(scratch, 0, 16 * sizeof(float), (cudaStream_t)stream);
+    if (me != cudaSuccess) return (int)me;
+    Loc2dArgs a{};
+    a.pred = pred; a.gt = gt; a.g_pred = g_pred; a.joints = (long)m * j; a.J = j; a.c_gt = c_gt; a.mask_hips = mask_hips;
+    a.per_cta = pl.per_cta; a.upstream = upstream;
+    a.sync = reinterpret_cast<unsigned*>(scratch); a.partials = scratch + 16; a.out = out;
+    a.xchg = XchgArgs{nullptr, 0, 1};
+    if (const int e = p2c_allow_big_smem(reinterpret_cast<const void*>(loc2d_step_kernel), 200 * 1024)) return e;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(pl.grid);
+    cfg.blockDim = dim3(LT);
+    cfg.dynamicSmemBytes = pl.smem;
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeCooperative;
     attr[0].val.cooperative = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
