@@ -444,6 +444,9 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     auto fold_if_last = [&]() { warp_fold_if_last(fold_args(), ntiles, my_ticket); };
     auto take_ticket = [&]() { my_ticket = ticket_release(a.ticket); };
     constexpr bool lone_sums = BT == 26 && LONE && SL == 1, lone_sums_early = lone_sums;
+    // (even, odd) bone pairs per warp in the element-wise passes where the warps have two or more tasks each: the record
+    // accessors then know the parity of their bone at compile time (tile_common.cuh)
+    constexpr bool PAIRS = BT == 26 && !LONE;
     const float k3 = a.w3 * 2.0f / (float)a.count3;
     const float kr = a.wr * 2.0f / (float)(a.count3 * 3.0);   // rot_3d: mean over 9 entries per bone
     __shared__ float red_r[32];
@@ -451,6 +454,10 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     CTA_CLOCK(17)
     const int clips_full = a.P / L;
     const int lane_frame = lane % L;   // (one slice: whole clips side by side in the lanes)
+    const int lane_clip = lane / L;
+    const bool whole_clips = clips_full * L == a.P;   // pose_changes mode; relative_rot tiles are 32 free poses
+    __shared__ signed char par_s[P2C_MAX_BONES];      // parents (a shared-memory read per task instead of arithmetic)
+    if (tid < B) par_s[tid] = (signed char)(BT == 26 ? carla_parent(tid) : a.parent[tid]);
 
     // tiles beyond the first come from a grid-wide counter (SMs do not run at one speed: up to a quarter between the
     // fastest and the slowest CTA under a static split); the ticket is drawn at the top of a tile and first needed
@@ -458,8 +465,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     int nxt = ntiles;
     for (int tile = blockIdx.x; tile < ntiles; tile = nxt, ++it) {
         const int m0 = tile * a.P;
-        unsigned drawn = 0;
-        if (tma && a.dynamic) drawn = atomicAdd(a.next, 1u);
+        unsigned drawn = 0;   // (the next tile of this CTA: drawn after the forward walk, see barrier #4)
         if (ROT && tma) {   // the tile's rot_3d target records on their way into L2 while the forward phases run
             const uint32_t bytes = (uint32_t)(min(a.P, total - m0) * B9) * 4u;
             asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.gt_rot + (size_t)m0 * B9), "r"(bytes) : "memory");
@@ -486,20 +492,19 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         // ---- phase A: 6-D -> C[t] (rotation_6d_to_matrix), one bone per task
         {
             float* dst = a.scan ? A : R;
-            const int nt = slices * B;
-#pragma unroll 1
-            for (int task = warp; task < nt; task += W) {
+            bone_tasks<PAIRS>(warp, W, slices * B, [&](int task, auto par) {
+                constexpr int PAR = decltype(par)::value;
                 const int slice = task >= B ? 1 : 0, b = task - slice * B;
                 const int col = slice * 32 + lane, pl = min(col, np - 1);
                 float d[6];
-                lds6(D + pl * B6, b, d);
+                lds6<PAR>(D + pl * B6, b, d);
                 const GS r = gram_schmidt(d);
                 M3 C;
                 C.m[0] = r.b1.x; C.m[1] = r.b1.y; C.m[2] = r.b1.z;
                 C.m[3] = r.b2.x; C.m[4] = r.b2.y; C.m[5] = r.b2.z;
                 C.m[6] = r.b3.x; C.m[7] = r.b3.y; C.m[8] = r.b3.z;
-                if (col < np) sts9(dst + pl * B9, b, C);
-            }
+                if (col < np) sts9<PAR>(dst + pl * B9, b, C);
+            });
         }
         if (!a.scan) fence_async_smem();
         __syncthreads();   // #2
@@ -550,6 +555,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                     p2 = fmaf(e[8], n2, fmaf(e[7], n1, e[6] * n0));
                     dst[B9] = p0; dst[B9 + 3] = p1; dst[B9 + 6] = p2;
                     dst += 2 * B9;
+                    DEBUG_CLOCK(if (a.clocks && (int)blockIdx.x == a.clock_cta && (int)it == a.clocks - 1 && tid == 0 && f < 32) g_tile_clocks[40 + (f >> 1)] = clock64();)
                 }
                 if (f < nf) {   // odd frame count: the last frame
                     dst[0] = fmaf(c[2], p2, fmaf(c[1], p1, c[0] * p0));
@@ -561,7 +567,22 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         // bone offsets of the skeleton of every clip the tile touches, one 3B-word record per clip, in the upper half of
         // the scratch region: the forward walk reads them from there (lanes of one clip read one address: a broadcast)
         // instead of going to the table in global memory
-        const int clip0 = m0 / L, nclip = (m0 + np - 1) / L - clip0 + 1;
+        // (tiles of whole clips start at a clip boundary: no division by the run-time clip length per tile)
+        int clip0, last_clip;
+        if (whole_clips) {
+            clip0 = tile * clips_full;
+            last_clip = np == a.P ? clips_full - 1 : (np - 1) / L;
+        } else {
+            clip0 = m0 / L;
+            last_clip = (m0 + np - 1) / L - clip0;
+        }
+        const int nclip = last_clip + 1;
+        // clip (counted from the tile's first) of the pose in column col = slot pl (columns past the tile repeat its last)
+        auto clip_of = [&](int col, int pl) {
+            (void)col;
+            if (!whole_clips) return (m0 + pl) / L - clip0;
+            return slices == 1 ? min(lane_clip, last_clip) : 0;
+        };
         {
             const int busy = (a.scan && tile_clips * B3 <= 160 && NT >= 256) ? 160 : 0;   // threads that ran the scan
             for (int i = tid - busy; i >= 0 && i < nclip * B3; i += NT - busy) {
@@ -593,14 +614,15 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         }
         if (a.scan && split_scan) {
             __syncthreads();   // #2b: both halves of the clip are in R
-#pragma unroll 1
-            for (int b = warp; b < B; b += W) {   // R[t] = (C[t] .. C[32]) . R[31] for the second half, one bone per task
+            // R[t] = (C[t] .. C[32]) . R[31] for the second half, one bone per task
+            bone_tasks<PAIRS>(warp, W, B, [&](int b, auto par) {
+                constexpr int PAR = decltype(par)::value;
                 const int col = 32 + lane;
                 if (col < np) {
-                    const M3 Q = lds9(R + col * B9, b), P31 = lds9(R + 31 * B9, b);
-                    sts9(R + col * B9, b, m3_mul(Q, P31));
+                    const M3 Q = lds9<PAR>(R + col * B9, b), P31 = lds9<PAR>(R + 31 * B9, b);
+                    sts9<PAR>(R + col * B9, b, m3_mul(Q, P31));
                 }
-            }
+            });
         }
         fence_async_smem();
         __syncthreads();   // #3
@@ -609,7 +631,6 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             bulk_s2g(a.rel_rot + (size_t)m0 * B9, R, (uint32_t)(np * B9) * 4u);
             bulk_commit();
         }
-        if (tma) next_s[it & 1] = a.dynamic ? (int)min(drawn + gridDim.x, (unsigned)ntiles) : ntiles;
 
         // ---- phase C: FK (p3d_pose.py:116-184): A_b = R_b . A_parent, t_b = loc_b . A_parent + t_parent.
         //      The phase is bound by shared-memory wavefronts, so every record is read once: with the CARLA tree (known at
@@ -627,7 +648,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             const bool valid = col < np;
             const float* rb = R + pl * B9;
             float* ab = A + pl * B9;
-            const float* lc = GV + ((m0 + pl) / L - clip0) * B3;   // this pose's skeleton offsets
+            const float* lc = GV + clip_of(col, pl) * B3;   // this pose's skeleton offsets
             float P[9], tp[3];   // A and t of the previous bone of the run
             auto rec_ld = [&](const float* base, int b, float* x) {   // 9-word record b of an even-word pose record
                 const float* q = base + 9 * b;
@@ -678,8 +699,11 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 if (valid) rec_st(ab, b, n);
                 TS[(3 * b) * PS + col] = tp[0]; TS[(3 * b + 1) * PS + col] = tp[1]; TS[(3 * b + 2) * PS + col] = tp[2];
             };
-#define P2C_RUN(B0, B1) \
-    _Pragma("unroll") for (int b = B0; b < B1; ++b) bone(b, carla_parent(b), b == B0);
+#define P2C_RUN(B0, B1)                                                                   \
+    _Pragma("unroll") for (int b = B0; b < B1; ++b) {                                      \
+        bone(b, carla_parent(b), b == B0);                                                 \
+        DEBUG_CLOCK(if (B0 < 8 && a.clocks && (int)blockIdx.x == a.clock_cta && (int)it == a.clocks - 1 && tid == 0) g_tile_clocks[32 + b] = clock64();) \
+    }
             if (grp == 0) {
                 P2C_RUN(0, 2)
                 named_arrive(3, 3 * slices * 32);   // hips
@@ -708,7 +732,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             const bool valid = col < np;
             const float* rb = R + pl * B9;
             float* ab = A + pl * B9 + jc;
-            const float* lc = GV + ((m0 + pl) / L - clip0) * B3;   // this pose's skeleton offsets
+            const float* lc = GV + clip_of(col, pl) * B3;   // this pose's skeleton offsets
             float* tr = TS + jc * PS + col;
             float c0 = 0.f, c1 = 0.f, c2 = 0.f, ct = 0.f;   // column jc of A_{b-1}, component jc of t_{b-1}
             // two bones per trip (B is even); the inputs of the next bone (its rel_rot record, its offset, its parent)
@@ -750,6 +774,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     _Pragma("unroll") for (int b = B0; b < B1; ++b) {     \
         fetch(u, b);                                      \
         bone(u, b, carla_parent(b));                      \
+        DEBUG_CLOCK(if (B0 < 8 && a.clocks && (int)blockIdx.x == a.clock_cta && (int)it == a.clocks - 1 && tid == 0) g_tile_clocks[32 + b] = clock64();) \
     }
                 if (!lone_limbs) {
                     P2C_RUNC(0, 26)
@@ -800,7 +825,10 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             DEBUG_CLOCK(if (a.clocks && (int)blockIdx.x == a.clock_cta) g_tile_clocks[22] = clock64();)
         }
         __syncthreads();   // #4
-        nxt = next_s[it & 1];
+        // The CTA's next tile comes from the grid-wide counter as LATE as its first use allows (after the loss pass:
+        // barrier #5): a tile that has been drawn is out of every other CTA's reach until its owner gets to it, and
+        // the slowest owners set the length of the kernel's tail.
+        if (tma && a.dynamic) drawn = atomicAdd(a.next, 1u);
         TILE_CLOCK(5)
         if (tma && a.abs_rot) {
             bulk_s2g(a.abs_rot + (size_t)m0 * B9, A, (uint32_t)(np * B9) * 4u);
@@ -834,9 +862,8 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         // ---- projection, normaliser, loss terms, dL/d abs_loc; one bone per task; abs_loc and projection records are
         //      written over the target records they were compared with
         {
-            const int nt = slices * B;
-#pragma unroll 1
-            for (int task = warp; task < nt; task += W) {
+            bone_tasks<PAIRS>(warp, W, slices * B, [&](int task, auto par) {
+                constexpr int PAR = decltype(par)::value;
                 const int slice = task >= B ? 1 : 0, b = task - slice * B;
                 const int col = slice * 32 + lane, pl = min(col, np - 1);
                 const bool valid = col < np;
@@ -854,8 +881,8 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 const V3 g = bone_loss<WORLD>(a, b, t, g2.x, g2.y, g3, m, valid, cx, p, n);
                 s2 = cx.s2; s3 = cx.s3;
                 if (valid) {
-                    sts3(G3 + pl * B3, b, t);
-                    sts3(G2 + pl * B3, b, p);
+                    sts3<PAR>(G3 + pl * B3, b, t);
+                    sts3<PAR>(G2 + pl * B3, b, p);
                     if (a.proj_norm && a.normalize) {   // off the benchmark path: straight to global
                         float* o = a.proj_norm + ((size_t)m * B + b) * 3;
                         o[0] = n.x; o[1] = n.y; o[2] = n.z;
@@ -867,14 +894,18 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                     PART[(b * 3 + 1) * PS + col] = cx.sgy;
                     PART[(b * 3 + 2) * PS + col] = cx.sgn;
                 }
-            }
+            });
         }
         s2 = warp_sum(s2);
         s3 = warp_sum(s3);
         if (lane == 0) { red[warp * 2] = s2; red[warp * 2 + 1] = s3; }
         fence_async_smem();
-        if (tma) bulk_wait_read_all();   // rel_rot / abs_rot stores have read R and A
+        if (tma) {
+            bulk_wait_read_all();   // rel_rot / abs_rot stores have read R and A
+            next_s[it & 1] = a.dynamic ? (int)min(drawn + gridDim.x, (unsigned)ntiles) : ntiles;
+        }
         __syncthreads();   // #5
+        nxt = next_s[it & 1];
         TILE_CLOCK(7)
         auto store_partial = [&]() {
             // the tile's loss partial (a fixed shuffle tree over the per-warp sums: W <= 32); on this CTA's last tile
@@ -917,9 +948,8 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         // ---- own parts of the subtree sums, one bone per task: g_b x t_b -> rows XR (the former partial-sum rows)
         float* XR = PART;
         {
-            const int nt = slices * B;
-#pragma unroll 1
-            for (int task = warp; task < nt; task += W) {
+            bone_tasks<PAIRS && ROT>(warp, W, slices * B, [&](int task, auto par) {
+                constexpr int PAR = decltype(par)::value;
                 const int slice = task >= B ? 1 : 0, b = task - slice * B;
                 const int col = slice * 32 + lane;
                 const V3 t{TS[(b * 3) * PS + col], TS[(b * 3 + 1) * PS + col], TS[(b * 3 + 2) * PS + col]};
@@ -945,7 +975,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                     // which joins the own part of the subtree sums.  The target record comes straight from global
                     // memory (prefetched into L2 at the top of the tile; 36 bytes per lane, L1 keeps the lines).
                     const int pl = min(col, np - 1);
-                    const M3 A_ = lds9(A + pl * B9, b);
+                    const M3 A_ = lds9<PAR>(A + pl * B9, b);
                     const float* gq = a.gt_rot + ((size_t)(m0 + pl) * B + b) * 9;
                     float q[9];
 #pragma unroll
@@ -969,7 +999,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 XR[(b * 3) * PS + col] = x.x;
                 XR[(b * 3 + 1) * PS + col] = x.y;
                 XR[(b * 3 + 2) * PS + col] = x.z;
-            }
+            });
         }
         if (ROT) {
             sr = warp_sum(sr);
@@ -1086,7 +1116,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
 #pragma unroll 1
             for (int task = warp; task < nt; task += W) {
                 const int sl = task >= B ? 1 : 0, b = task - sl * B;
-                const int par = BT == 26 ? carla_parent(b) : a.parent[b];   // (arithmetic: no cold constant-bank read)
+                const int par = par_s[b];
                 const int col = sl * 32 + lane, pl = min(col, np - 1);
                 const V3 sx{XR[(b * 3) * PS + col], XR[(b * 3 + 1) * PS + col], XR[(b * 3 + 2) * PS + col]};
                 const V3 sg{GV[(b * 3) * PS + col], GV[(b * 3 + 1) * PS + col], GV[(b * 3 + 2) * PS + col]};
@@ -1107,8 +1137,9 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         //      shuffles),  omega = R[t] z[t],  tangent-form Gram-Schmidt backward -> gradient records over the 6-D
         //      records (which now live in the two target regions)
         {
-#pragma unroll 1
-            for (int b = warp; b < B; b += W) {
+            // (a clip over two slices: one bone per warp, both slices in turn -- no pairs, the warps have one task each)
+            bone_tasks<PAIRS && SL == 1>(warp, W, B, [&](int b, auto par) {
+                constexpr int PAR = decltype(par)::value;
                 V3 later{0.f, 0.f, 0.f};   // sum over the later slice of the same clip (clips longer than 32 frames)
 #pragma unroll 1
                 for (int sl = slices - 1; sl >= 0; --sl) {
@@ -1131,12 +1162,12 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                         }
                     }
                     float d[6], o[6];
-                    lds6(G3 + pl * B6, b, d);
-                    const V3 om = v3_mul_mt(z, lds9(R + pl * B9, b));
+                    lds6<PAR>(G3 + pl * B6, b, d);
+                    const V3 om = v3_mul_mt(z, lds9<PAR>(R + pl * B9, b));
                     gram_schmidt_bwd_tangent(gram_schmidt(d), om, o);
-                    if (valid) sts6(G3 + pl * B6, b, o);
+                    if (valid) sts6<PAR>(G3 + pl * B6, b, o);
                 }
-            }
+            });
         }
         fence_async_smem();
         __syncthreads();   // #8

@@ -84,10 +84,16 @@ __device__ __forceinline__ void sts32(float* p, float x) {
 }
 // 9-word bone record b of an AoS pose record (b is warp-uniform at every call site: the parity branch does not diverge)
 // (64-bit accesses: half the wavefronts of scalar ones; the pose stride, 117 x 8 bytes, is conflict free)
+// PAR: the parity of b when the caller knows it at compile time (0 / 1), -1 = look at b.  A run-time parity is compiled
+// as BOTH access sequences under predicates plus the moves that merge their registers (17 issue slots for a 5-access
+// record load): the task loops of the kernels therefore hand out bones in (even, odd) pairs where they can.
+template <int PAR>
+__device__ __forceinline__ bool odd_record(int b) { return PAR < 0 ? (b & 1) != 0 : PAR != 0; }
+template <int PAR = -1>
 __device__ __forceinline__ M3 lds9(const float* pose, int b) {
     const float* p = pose + 9 * b;
     M3 r;
-    if (b & 1) {
+    if (odd_record<PAR>(b)) {
         r.m[0] = p[0];
         const float2 v0 = lds64(p + 1), v1 = lds64(p + 3), v2 = lds64(p + 5), v3 = lds64(p + 7);
         r.m[1] = v0.x; r.m[2] = v0.y; r.m[3] = v1.x; r.m[4] = v1.y; r.m[5] = v2.x; r.m[6] = v2.y; r.m[7] = v3.x; r.m[8] = v3.y;
@@ -98,9 +104,10 @@ __device__ __forceinline__ M3 lds9(const float* pose, int b) {
     }
     return r;
 }
+template <int PAR = -1>
 __device__ __forceinline__ void sts9(float* pose, int b, const M3& a) {
     float* p = pose + 9 * b;
-    if (b & 1) {
+    if (odd_record<PAR>(b)) {
         p[0] = a.m[0];
         sts64(p + 1, a.m[1], a.m[2]); sts64(p + 3, a.m[3], a.m[4]);
         sts64(p + 5, a.m[5], a.m[6]); sts64(p + 7, a.m[7], a.m[8]);
@@ -167,9 +174,10 @@ __device__ __forceinline__ void sts128(float* p, float x, float y, float z, floa
     asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(smem_u32(p)), "f"(x), "f"(y), "f"(z), "f"(w) : "memory");
 }
 // 6-word bone record b of a 16-byte aligned AoS pose record (6-D / gradient records): 128 + 64 bits, order by parity
+template <int PAR = -1>
 __device__ __forceinline__ void lds6(const float* pose, int b, float* d) {
     const float* p = pose + 6 * b;
-    if (b & 1) {
+    if (odd_record<PAR>(b)) {
         const float2 u = lds64(p);
         const float4 v = lds128(p + 2);
         d[0] = u.x; d[1] = u.y; d[2] = v.x; d[3] = v.y; d[4] = v.z; d[5] = v.w;
@@ -179,9 +187,10 @@ __device__ __forceinline__ void lds6(const float* pose, int b, float* d) {
         d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w; d[4] = u.x; d[5] = u.y;
     }
 }
+template <int PAR = -1>
 __device__ __forceinline__ void sts6(float* pose, int b, const float* d) {
     float* p = pose + 6 * b;
-    if (b & 1) {
+    if (odd_record<PAR>(b)) {
         sts64(p, d[0], d[1]);
         sts128(p + 2, d[2], d[3], d[4], d[5]);
     } else {
@@ -194,9 +203,10 @@ __device__ __forceinline__ V3 lds3(const float* pose, int b) {
     const float* p = pose + 3 * b;
     return V3{p[0], p[1], p[2]};
 }
+template <int PAR = -1>
 __device__ __forceinline__ void sts3(float* pose, int b, const V3& v) {
     float* p = pose + 3 * b;
-    if (b & 1) {
+    if (odd_record<PAR>(b)) {
         p[0] = v.x;
         sts64(p + 1, v.y, v.z);
     } else {
@@ -206,3 +216,24 @@ __device__ __forceinline__ void sts3(float* pose, int b, const V3& v) {
 }
 
 }  // namespace
+
+// Bone tasks of the element-wise passes: task t of nt goes to warp t mod W (one bone per task), or -- PAIRS -- tasks
+// (2u, 2u + 1) go to warp u mod W, so that every call of the body knows the parity of its bone at compile time (nt and
+// the bone count are even: the parity of a task is the parity of its bone).  The body is f(task, Parity<..>{}).
+template <int PAR>
+struct Parity {
+    static constexpr int value = PAR;
+};
+template <bool PAIRS, typename F>
+__device__ __forceinline__ void bone_tasks(int warp, int W, int nt, F f) {
+    if (PAIRS) {
+#pragma unroll 1
+        for (int t = 2 * warp; t < nt; t += 2 * W) {
+            f(t, Parity<0>{});
+            f(t + 1, Parity<1>{});
+        }
+    } else {
+#pragma unroll 1
+        for (int t = warp; t < nt; t += W) f(t, Parity<-1>{});
+    }
+}

@@ -29,6 +29,10 @@ if w[16]:
         w[17] - w[16], w[18] - w[17], w[19] - w[18], w[20] - w[19]))
 if w[21]:
     print('forward walk done %d, count poll done %d cycles after barrier 3' % (w[21] - w[4], w[22] - w[4]))
+if w[32]:
+    print('trunk walk, cycles after barrier 3 per bone:', [int(w[32 + b] - w[4]) for b in range(8)])
+if w[40]:
+    print('scan (thread 0), cycles after barrier 2 per two-frame trip:', [int(w[40 + k] - w[3]) for k in range(16) if w[40 + k]])
 ct = (ctypes.c_ulonglong * 2048)()
 lib.p2c_debug_cta_times.argtypes = [ctypes.c_void_p]
 assert lib.p2c_debug_cta_times(ct) == 0
