@@ -36,6 +36,12 @@
 #include "host_util.h"
 #include "tile_common.cuh"
 
+#ifndef P2C_LONE_TASKS
+// one-bone-per-warp passes (the one-tile-per-CTA kernels): 2 = the body compiled once per parity behind a warp-uniform
+// branch, 0 = parity looked at inside the accessors (measured: 14.20 -> 14.02 us at 256 x 16)
+#define P2C_LONE_TASKS 2
+#endif
+
 namespace {
 
 constexpr int MAX_THREADS = 832;
@@ -446,7 +452,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     constexpr bool lone_sums = BT == 26 && LONE && SL == 1, lone_sums_early = lone_sums;
     // (even, odd) bone pairs per warp in the element-wise passes where the warps have two or more tasks each: the record
     // accessors then know the parity of their bone at compile time (tile_common.cuh)
-    constexpr bool PAIRS = BT == 26 && !LONE;
+    constexpr int PAIRS = BT == 26 ? (LONE ? P2C_LONE_TASKS : 1) : 0;
     const float k3 = a.w3 * 2.0f / (float)a.count3;
     const float kr = a.wr * 2.0f / (float)(a.count3 * 3.0);   // rot_3d: mean over 9 entries per bone
     __shared__ float red_r[32];
@@ -615,7 +621,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         if (a.scan && split_scan) {
             __syncthreads();   // #2b: both halves of the clip are in R
             // R[t] = (C[t] .. C[32]) . R[31] for the second half, one bone per task
-            bone_tasks<PAIRS>(warp, W, B, [&](int b, auto par) {
+            bone_tasks<(PAIRS == 1 && SL != 1) ? P2C_LONE_TASKS : PAIRS>(warp, W, B, [&](int b, auto par) {
                 constexpr int PAR = decltype(par)::value;
                 const int col = 32 + lane;
                 if (col < np) {
@@ -948,7 +954,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         // ---- own parts of the subtree sums, one bone per task: g_b x t_b -> rows XR (the former partial-sum rows)
         float* XR = PART;
         {
-            bone_tasks<PAIRS && ROT>(warp, W, slices * B, [&](int task, auto par) {
+            bone_tasks<ROT ? PAIRS : 0>(warp, W, slices * B, [&](int task, auto par) {
                 constexpr int PAR = decltype(par)::value;
                 const int slice = task >= B ? 1 : 0, b = task - slice * B;
                 const int col = slice * 32 + lane;
@@ -1124,7 +1130,14 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 const V3 mv{sx.x - (sg.y * t.z - sg.z * t.y), sx.y - (sg.z * t.x - sg.x * t.z),
                             sx.z - (sg.x * t.y - sg.y * t.x)};
                 V3 y = mv;
+#ifndef P2C_NO_Y_BRANCH   // (the parent's parity is a run-time value: two access sequences behind a branch)
+                if (par >= 0) {
+                    if (par & 1) y = v3_mul_mt(mv, lds9<1>(A + pl * B9, par));
+                    else y = v3_mul_mt(mv, lds9<0>(A + pl * B9, par));
+                }
+#else
                 if (par >= 0) y = v3_mul_mt(mv, lds9(A + pl * B9, par));
+#endif
                 if (col >= np) y = V3{0.f, 0.f, 0.f};
                 XR[(b * 3) * PS + col] = y.x; XR[(b * 3 + 1) * PS + col] = y.y; XR[(b * 3 + 2) * PS + col] = y.z;
             }
@@ -1138,7 +1151,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         //      records (which now live in the two target regions)
         {
             // (a clip over two slices: one bone per warp, both slices in turn -- no pairs, the warps have one task each)
-            bone_tasks<PAIRS && SL == 1>(warp, W, B, [&](int b, auto par) {
+            bone_tasks<(PAIRS == 1 && SL != 1) ? P2C_LONE_TASKS : PAIRS>(warp, W, B, [&](int b, auto par) {
                 constexpr int PAR = decltype(par)::value;
                 V3 later{0.f, 0.f, 0.f};   // sum over the later slice of the same clip (clips longer than 32 frames)
 #pragma unroll 1

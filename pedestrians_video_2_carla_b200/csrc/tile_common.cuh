@@ -224,13 +224,21 @@ template <int PAR>
 struct Parity {
     static constexpr int value = PAR;
 };
-template <bool PAIRS, typename F>
+// MODE 0: one task per trip, parity looked at inside the accessors; 1: pairs; 2: one task per trip, the body compiled
+// twice and picked by a (warp-uniform) branch on the task's parity
+template <int MODE, typename F>
 __device__ __forceinline__ void bone_tasks(int warp, int W, int nt, F f) {
-    if (PAIRS) {
+    if (MODE == 1) {
 #pragma unroll 1
         for (int t = 2 * warp; t < nt; t += 2 * W) {
             f(t, Parity<0>{});
             f(t + 1, Parity<1>{});
+        }
+    } else if (MODE == 2) {
+#pragma unroll 1
+        for (int t = warp; t < nt; t += W) {
+            if (t & 1) f(t, Parity<1>{});
+            else f(t, Parity<0>{});
         }
     } else {
 #pragma unroll 1
