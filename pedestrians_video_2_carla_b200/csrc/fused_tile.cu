@@ -80,6 +80,11 @@ struct TileArgs {
     float* losses;
     double count3;
     XchgArgs xchg;         // data-parallel ranks: where the finishing thread publishes the four loss sums
+    // per-launch constants worked out by the launcher: read from the constant bank where they are used instead of
+    // being computed at the top of the kernel and held in registers across the tile loop (the kernel runs at its
+    // register cap: every long-lived value is a spill somewhere else)
+    int total, ntiles, clips_full, whole_clips;
+    float k2_all, k3, kr;
 };
 
 struct GS {
@@ -354,10 +359,23 @@ __device__ __noinline__ void warp_fold_if_last(const FoldArgs a, int ntiles, uns
 // the code, and a kernel that runs every phase once per launch pays for its size in instruction fetches); ROT: rot_3d is
 // fused (targets['absolute_pose_rot'] given) -- its own instances, so the plain step carries neither its code nor its
 // registers (measured: +6 % on every size when the term was a run-time branch)
+// threads per CTA: one bone per warp and slice when the launch has at most one tile per CTA (latency), else two
+__host__ __device__ constexpr int tile_threads(int bones, int slices, bool lone) {
+    return ((lone ? bones : bones / 2) * slices < 4 ? 4
+            : (lone ? bones : bones / 2) * slices > MAX_THREADS / 32 ? MAX_THREADS / 32
+                                                                      : (lone ? bones : bones / 2) * slices) * 32;
+}
+
 template <int BT, int SL, bool WORLD, bool LONE, bool ROT>
 __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) {
     extern __shared__ __align__(16) float smem[];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, NT = blockDim.x, W = NT >> 5;
+    // (CARLA instances: the CTA size is part of the instance -- tile_threads() -- so warp counts and loop strides fold)
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+#ifdef P2C_RUNTIME_NT
+    const int NT = (int)blockDim.x, W = NT >> 5;
+#else
+    const int NT = BT == 26 ? tile_threads(BT, SL, LONE) : (int)blockDim.x, W = NT >> 5;
+#endif
     const int B = BT ? BT : a.B, slices = SL ? SL : a.slices;
     const int B3 = B * 3, B6 = B * 6, B9 = B * 9, PS = 32 * slices, L = a.L;
     const TilePlan sm = tile_plan(PS, B);
@@ -376,8 +394,8 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     float* TS = D;               // SoA scratch rows [0, 3B): t_b, later subtree sums of g x t
     float* GV = D + B3 * PS;     // SoA scratch rows [3B, 6B): g_b, later subtree sums of g
     const bool tma = tid == (W - 1) * 32;   // the thread that issues every bulk copy (a warp without tree work)
-    const int total = a.N * L;              // (the launcher keeps N*L*B*9 below 2^31 elements... offsets are size_t)
-    const int ntiles = (total + a.P - 1) / a.P;
+    const int total = a.total;              // (the launcher keeps N*L*B*9 below 2^31 elements... offsets are size_t)
+    const int ntiles = a.ntiles;
 
     auto load_d6 = [&](int tile) {
         const int m0 = tile * a.P;
@@ -431,7 +449,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     if (tid == 0) cta_count = 0;
     __syncthreads();
 
-    float k2 = a.w2 * 2.0f / ((float)total * (float)(B * 2));   // (mask on: replaced below once the count is known)
+    float k2 = a.k2_all;   // (mask on: replaced below once the count is known)
     // ---- loss sums: one partial pair per TILE (fixed order inside the tile), so the totals do not depend on which
     //      CTA ran which tile; the last CTA to take a ticket folds them in tile order at the end of the kernel
     __shared__ int next_s[2];
@@ -453,15 +471,31 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
     // (even, odd) bone pairs per warp in the element-wise passes where the warps have two or more tasks each: the record
     // accessors then know the parity of their bone at compile time (tile_common.cuh)
     constexpr int PAIRS = BT == 26 ? (LONE ? P2C_LONE_TASKS : 1) : 0;
-    const float k3 = a.w3 * 2.0f / (float)a.count3;
-    const float kr = a.wr * 2.0f / (float)(a.count3 * 3.0);   // rot_3d: mean over 9 entries per bone
+    const float k3 = a.k3;
+    const float kr = a.kr;   // rot_3d: mean over 9 entries per bone
     __shared__ float red_r[32];
     unsigned it = 0;
     CTA_CLOCK(17)
-    const int clips_full = a.P / L;
-    const int lane_frame = lane % L;   // (one slice: whole clips side by side in the lanes)
-    const int lane_clip = lane / L;
-    const bool whole_clips = clips_full * L == a.P;   // pose_changes mode; relative_rot tiles are 32 free poses
+    const int clips_full = a.clips_full;
+    // suffix scan over the frames of a clip (phase E): bit k of scan_ok<slice> = "the lane 2^k to the right holds a later
+    // frame of MY clip" -- a function of the lane alone, so the rounds of the scan test one bit instead of comparing
+    // (kept in shared memory: two more live registers cost more in spills than a read per task)
+    __shared__ unsigned scan_ok_s[64];
+    if (warp == 0) {
+        const int lane_clip = lane / L, lane_frame = lane - lane_clip * L;   // (one slice: whole clips side by side)
+        unsigned ok0 = (unsigned)lane_clip << 8, ok1 = 0u;   // (bits 8..: the lane's clip within a one-slice tile)
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            const int off = 1 << k;
+            if (lane + off < 32) {
+                if ((slices == 1 ? lane_frame : lane) + off < L) ok0 |= 1u << k;
+                if (32 + lane + off < L) ok1 |= 1u << k;
+            }
+        }
+        scan_ok_s[lane] = ok0;
+        scan_ok_s[32 + lane] = ok1;
+    }
+    const bool whole_clips = a.whole_clips != 0;   // pose_changes mode; relative_rot tiles are 32 free poses
     __shared__ signed char par_s[P2C_MAX_BONES];      // parents (a shared-memory read per task instead of arithmetic)
     if (tid < B) par_s[tid] = (signed char)(BT == 26 ? carla_parent(tid) : a.parent[tid]);
 
@@ -587,7 +621,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         auto clip_of = [&](int col, int pl) {
             (void)col;
             if (!whole_clips) return (m0 + pl) / L - clip0;
-            return slices == 1 ? min(lane_clip, last_clip) : 0;
+            return slices == 1 ? min((int)(scan_ok_s[lane] >> 8), last_clip) : 0;
         };
         {
             const int busy = (a.scan && tile_clips * B3 <= 160 && NT >= 256) ? 160 : 0;   // threads that ran the scan
@@ -1160,13 +1194,14 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                     const bool valid = col < np;
                     V3 z{XR[(b * 3) * PS + col], XR[(b * 3 + 1) * PS + col], XR[(b * 3 + 2) * PS + col]};
                     if (a.scan) {
-                        const int fr = slices == 1 ? lane_frame : col;   // frame of this lane within its clip
+                        const unsigned ok = scan_ok_s[sl * 32 + lane];
 #pragma unroll
-                        for (int off = 1; off < 32; off <<= 1) {
+                        for (int k = 0; k < 5; ++k) {
+                            const int off = 1 << k;
                             if (off >= L) break;
                             const float vx = __shfl_down_sync(FULL_MASK, z.x, off), vy = __shfl_down_sync(FULL_MASK, z.y, off),
                                         vz = __shfl_down_sync(FULL_MASK, z.z, off);
-                            if (lane + off < 32 && fr + off < L) { z.x += vx; z.y += vy; z.z += vz; }
+                            if (ok & (1u << k)) { z.x += vx; z.y += vy; z.z += vz; }
                         }
                         if (slices > 1) {
                             z.x += later.x; z.y += later.y; z.z += later.z;
@@ -1277,10 +1312,8 @@ TileLaunch make_launch(const p2c_fused_step_t* p, const TileArgs& a) {   // a: t
     // many tiles: two bones per warp and two CTAs per SM; at most one tile per SM (the 256 x 16 step): one bone per
     // warp, which halves the latency of the element-wise passes
     const bool lone = ntiles <= sm_count();
-    int warps = (lone ? B : B / 2) * t.slices;
-    if (warps < 4) warps = 4;
-    if (warps > MAX_THREADS / 32) warps = MAX_THREADS / 32;
-    t.threads = warps * 32;
+    t.threads = tile_threads(B, t.slices, lone);
+    const int warps = t.threads / 32;
     if (warps < 6 * t.slices) return t;   // the subtree-sum walks take six warps per slice (tiny trees: other kernels)
     t.smem = (size_t)tile_plan(t.PS, B).total * sizeof(float);
     const size_t cap = 227 * 1024;
@@ -1358,6 +1391,13 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     a.xchg = XchgArgs{p->exchange, p->exchange_rank, p->exchange_world};
     const long total = (long)p->n_clips * p->clip_len;
     a.count3 = (double)total * B * 3;
+    a.total = (int)total;
+    a.ntiles = (int)((total + t.P - 1) / t.P);
+    a.clips_full = t.P / p->clip_len;
+    a.whole_clips = a.clips_full * p->clip_len == t.P ? 1 : 0;
+    a.k2_all = p->weight_2d * 2.0f / ((float)total * (float)(B * 2));
+    a.k3 = p->weight_3d * 2.0f / (float)a.count3;
+    a.kr = a.wr * 2.0f / (float)(a.count3 * 3.0);
     cudaStream_t st = (cudaStream_t)stream;
     if (a.mask && !a.count_inline) {
         long blocks = (total * B / 4 + 511) / 512;   // two 48-byte groups per thread and trip

@@ -1,0 +1,10 @@
+#!/bin/bash
+mkdir -p gpurun_out
+{
+for rep in 1 2; do
+P2C_LIB=pedestrians_video_2_carla_b200/libp2c_base.so timeout 300 python tools/quick_bench.py base
+timeout 300 python tools/quick_bench.py new
+done
+timeout 900 python -m pytest tests/test_gpu_fused_step.py tests/test_gpu_module_api.py -x -q -m gpu 2>&1 | tail -3
+} > gpurun_out/r28.log 2>&1
+cat gpurun_out/r28.log
