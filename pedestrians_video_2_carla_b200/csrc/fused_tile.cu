@@ -36,6 +36,9 @@
 #include "host_util.h"
 #include "tile_common.cuh"
 
+#ifndef P2C_SERVICE_WARP
+#define P2C_SERVICE_WARP 1   // 0: experiment, the loss fold stays in task warp W - 2
+#endif
 #ifndef P2C_LONE_TASKS
 // one-bone-per-warp passes (the one-tile-per-CTA kernels): 2 = the body compiled once per parity behind a warp-uniform
 // branch, 0 = parity looked at inside the accessors (measured: 14.20 -> 14.02 us at 256 x 16)
@@ -44,7 +47,8 @@
 
 namespace {
 
-constexpr int MAX_THREADS = 832;
+constexpr int MAX_THREADS = 832;                   // worker threads: at most 26 warps with bone / column tasks
+constexpr int LAUNCH_THREADS = MAX_THREADS + 32;   // + the service warp of the one-tile-per-CTA CARLA kernels
 
 struct TileArgs {
     int N, L, B, P, PS, slices, scan;   // clips, frames per clip, bones, poses per tile, P rounded up to 32, PS/32
@@ -272,6 +276,7 @@ __device__ __forceinline__ V3 bone_loss(const TileArgs& a, int b, const V3& t, f
 }
 
 __device__ long long g_tile_clocks[64];
+__device__ long long g_warp_clocks[32 * 16];   // debug: arrival of every warp at the barriers of the recorded tile
 __device__ unsigned long long g_cta_times[2 * 1024];   // debug (P2C_TILE_CLOCKS): globaltimer at entry / exit of every CTA
 #ifdef P2C_CLOCKS_BUILD
 __device__ __forceinline__ unsigned long long globaltimer() {
@@ -285,8 +290,12 @@ __device__ __forceinline__ unsigned long long globaltimer() {
 #ifndef P2C_CLOCKS_BUILD
 #define CTA_CLOCK(k)
 #define TILE_CLOCK(k)
+#define WARP_CLOCK(k)
 #define DEBUG_CLOCK(stmt)
 #else
+#define WARP_CLOCK(k)                                                                                         \
+    if (a.clocks && (int)blockIdx.x == a.clock_cta && (int)it == a.clocks - 1 && (threadIdx.x & 31) == 0)      \
+        g_warp_clocks[(threadIdx.x >> 5) * 16 + k] = clock64();
 #define DEBUG_CLOCK(stmt) stmt
 #define CTA_CLOCK(k) \
     if (a.clocks && (int)blockIdx.x == a.clock_cta && threadIdx.x == 0) g_tile_clocks[k] = clock64();
@@ -336,7 +345,9 @@ __device__ __noinline__ void finish_losses(const FoldArgs a, double d2, double d
 __device__ __noinline__ void warp_fold_if_last(const FoldArgs a, int ntiles, unsigned ticket) {
     const int lane = threadIdx.x & 31;
     if (__shfl_sync(FULL_MASK, ticket, 0) != gridDim.x - 1) return;
-    __threadfence();
+    // (acquire side of the ticket chain: the partials are read with ld.cg, past L1 -- no need for the sequentially
+    // consistent fence + L1 invalidate of __threadfence())
+    asm volatile("fence.acq_rel.gpu;" ::: "memory");
     double d2 = 0.0, d3 = 0.0, dr = 0.0;
     for (int i = lane; i < ntiles; i += 32) {
         const float4 v = __ldcg(reinterpret_cast<const float4*>(a.partials) + i);
@@ -367,15 +378,23 @@ __host__ __device__ constexpr int tile_threads(int bones, int slices, bool lone)
 }
 
 template <int BT, int SL, bool WORLD, bool LONE, bool ROT>
-__global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) {
+__global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs a) {
     extern __shared__ __align__(16) float smem[];
     // (CARLA instances: the CTA size is part of the instance -- tile_threads() -- so warp counts and loop strides fold)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-#ifdef P2C_RUNTIME_NT
-    const int NT = (int)blockDim.x, W = NT >> 5;
-#else
-    const int NT = BT == 26 ? tile_threads(BT, SL, LONE) : (int)blockDim.x, W = NT >> 5;
-#endif
+    // SERVICE (one tile per CTA, CARLA): one more warp than there are task warps.  It stores the tile's loss partial,
+    // draws the CTA's ticket and, in the grid's last CTA, folds the partials -- a chain of L2 round trips (store
+    // acknowledged -> ticket -> partials -> totals stored: ~5 k cycles) that sat in a task warp and made the folding CTA,
+    // and with it the step, ~2 us longer than the others.  The service warp takes no part in the barriers after the loss
+    // pass (the task warps meet at a named barrier of their own), so the chain runs beside the backward phases.
+    constexpr bool SERVICE = BT == 26 && LONE && P2C_SERVICE_WARP;
+    const int WT = BT == 26 ? tile_threads(BT, SL, LONE) : (int)blockDim.x;   // threads with bone / column tasks
+    const int W = WT >> 5, NT = WT + (SERVICE ? 32 : 0);
+    const int svc = SERVICE ? W : W - 2;   // the warp that stores the partial, draws the ticket and folds
+    auto sync_tasks = [&]() {              // barrier of the task warps once the service warp has left
+        if (SERVICE) named_barrier(7, W * 32);
+        else __syncthreads();
+    };
     const int B = BT ? BT : a.B, slices = SL ? SL : a.slices;
     const int B3 = B * 3, B6 = B * 6, B9 = B * 9, PS = 32 * slices, L = a.L;
     const TilePlan sm = tile_plan(PS, B);
@@ -517,6 +536,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         TILE_CLOCK(0)
         while (!mbar_try_wait(bars, it & 1u)) {}
         TILE_CLOCK(1)
+        WARP_CLOCK(1)
         __syncthreads();   // #1 (first tile: the row table; later tiles: ordered by the barriers of the previous tile)
 
         TILE_CLOCK(2)
@@ -547,6 +567,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             });
         }
         if (!a.scan) fence_async_smem();
+        WARP_CLOCK(2)
         __syncthreads();   // #2
         TILE_CLOCK(3)
         // ---- phase B: R[t] = C[t] . R[t-1] (p3d_pose.py:98-114 looped by layers/projection.py:190-193); one thread
@@ -646,9 +667,11 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                     c = __reduce_add_sync(FULL_MASK, c);
                     if (lane == 0 && c) atomicAdd(&cta_count, c);
                     named_barrier(1, nc);
+#ifndef P2C_EXP_LATECOUNT
                     if (ci == 0)
                         atomicAdd(reinterpret_cast<unsigned long long*>(a.count2),
                                   (1ull << 32) | (unsigned long long)(unsigned)cta_count);
+#endif
                 }
             }
         }
@@ -665,6 +688,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             });
         }
         fence_async_smem();
+        WARP_CLOCK(3)
         __syncthreads();   // #3
         TILE_CLOCK(4)
         if (tma && a.rel_rot) {
@@ -858,12 +882,18 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             // one lane of a warp without a column polls until every CTA of the grid has sent its count (all CTAs are
             // resident: one tile each, at most one CTA per SM)
             unsigned long long v;
+#ifdef P2C_EXP_LATECOUNT
+            // (sent HERE, by a thread whose next proxy fence is two phases away: a thread that fences right after a
+            // global atomic waits for the atomic's round trip, and with it the whole CTA at the next barrier)
+            atomicAdd(reinterpret_cast<unsigned long long*>(a.count2), (1ull << 32) | (unsigned long long)(unsigned)cta_count);
+#endif
             do {
                 v = *reinterpret_cast<volatile unsigned long long*>(a.count2);
             } while ((unsigned)(v >> 32) < gridDim.x);
             k2_shared = a.w2 * 2.0f / (float)(unsigned)(v & 0xffffffffull);
             DEBUG_CLOCK(if (a.clocks && (int)blockIdx.x == a.clock_cta) g_tile_clocks[22] = clock64();)
         }
+        WARP_CLOCK(4)
         __syncthreads();   // #4
         // The CTA's next tile comes from the grid-wide counter as LATE as its first use allows (after the loss pass:
         // barrier #5): a tile that has been drawn is out of every other CTA's reach until its owner gets to it, and
@@ -891,6 +921,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             NRM[5 * PS + col] = (scale > 0.f && scale <= 3.402823466e38f) ? 1.f : 0.f;
         }
         while (!mbar_try_wait(bars + 1, it & 1u)) {}
+        WARP_CLOCK(5)
         __syncthreads();   // #4b
         if (a.mask && a.count_inline) k2 = k2_shared;
         if (a.mask && !a.count_inline && it == 0) {
@@ -944,6 +975,7 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             bulk_wait_read_all();   // rel_rot / abs_rot stores have read R and A
             next_s[it & 1] = a.dynamic ? (int)min(drawn + gridDim.x, (unsigned)ntiles) : ntiles;
         }
+        WARP_CLOCK(6)
         __syncthreads();   // #5
         nxt = next_s[it & 1];
         TILE_CLOCK(7)
@@ -960,7 +992,14 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 if (nxt >= ntiles) take_ticket();
             }
         };
-        if (!ROT && warp == W - 2) store_partial();   // (rot_3d fused: its sum is formed in the next pass)
+        if (SERVICE && warp == svc) {
+            // (rot_3d fused: its sum is formed in the next pass -- the task warps arrive at barrier 6 when it is there)
+            if (ROT) named_barrier(6, (W + 1) * 32);
+            store_partial();
+            if (a.warp_fold) fold_if_last();
+            break;   // one tile per CTA: nothing else for this warp (the kernel's tail waits for it)
+        }
+        if (!SERVICE && !ROT && warp == svc) store_partial();   // (rot_3d fused: its sum is formed in the next pass)
         if (tma) {
             if (a.abs_loc) bulk_s2g(a.abs_loc + (size_t)m0 * B3, G3, (uint32_t)(np * B3) * 4u);
             if (a.proj) bulk_s2g(a.proj + (size_t)m0 * B3, G2, (uint32_t)(np * B3) * 4u);
@@ -983,7 +1022,9 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 }
                 NRM[(6 + k) * PS + col] = s0_ + s1_;   // (B is even)
             }
-            __syncthreads();   // #5a
+            WARP_CLOCK(7)
+            sync_tasks();   // #5a
+            TILE_CLOCK(10)
         }
         // ---- own parts of the subtree sums, one bone per task: g_b x t_b -> rows XR (the former partial-sum rows)
         float* XR = PART;
@@ -1045,13 +1086,16 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             sr = warp_sum(sr);
             if (lane == 0) red_r[warp] = sr;
         }
-        __syncthreads();   // #5b
-        if (ROT && warp == W - 2) store_partial();
+        WARP_CLOCK(8)
+        if (SERVICE && ROT) named_arrive(6, (W + 1) * 32);   // (red_r is complete: the service warp may go on)
+        sync_tasks();   // #5b
+        TILE_CLOCK(11)
+        if (!SERVICE && ROT && warp == svc) store_partial();
         // few tiles: the warp that drew this CTA's ticket folds the grid's partials if it was the last -- NOW, when it has
         // no part in the subtree walks below, so that the fold (an L2 round trip, and with data-parallel ranks the peer
         // stores of the exchange, an NVLink round trip) sits behind the rest of the backward pass of this CTA
         const bool fold_early = W - 2 >= (lone_sums_early ? 15 : 6 * slices);
-        if (fold_early && nxt >= ntiles && a.warp_fold && warp == W - 2) fold_if_last();
+        if (!SERVICE && fold_early && nxt >= ntiles && a.warp_fold && warp == svc) fold_if_last();
 
         // ---- subtree sums, leaves first (the bone order has parents before children, so a walk in reverse bone order
         //      meets every child before its parent):  Sx_b = sum_{d in subtree(b)} g_d x t_d (rows XR), Sg_b = sum g_d
@@ -1144,9 +1188,10 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
         }
         // (two warps without a column when W >= 6 slices + 2: both jobs wait on global memory, off the critical path)
         if (nxt < ntiles && warp == W - 1) fill_rows(nxt, (it + 1) & 1);
-        if (!fold_early && nxt >= ntiles && a.warp_fold && warp == W - 2) fold_if_last();   // (the ticket was drawn after the loss pass)
+        if (!SERVICE && !fold_early && nxt >= ntiles && a.warp_fold && warp == svc) fold_if_last();   // (the ticket was drawn after the loss pass)
         while (!mbar_try_wait(bars + 2, it & 1u)) {}
-        __syncthreads();   // #6
+        WARP_CLOCK(9)
+        sync_tasks();   // #6
         TILE_CLOCK(8)
         // ---- per bone, all independent:  m_b = Sx_b - Sg_b x t_b,  y_b = A_parent m_b  (in place over Sx_b).  After this
         //      pass the scratch rows (t, Sg) and the abs_rot records are dead, so the next tile's 6-D records can start
@@ -1176,8 +1221,11 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
                 XR[(b * 3) * PS + col] = y.x; XR[(b * 3 + 1) * PS + col] = y.y; XR[(b * 3 + 2) * PS + col] = y.z;
             }
         }
-        fence_async_smem();   // (the scratch rows are about to be overwritten by TMA)
-        __syncthreads();   // #7
+        // (the scratch rows are about to be overwritten by TMA -- when a tile follows; on the CTA's last tile the fence
+        // would only make the thread that folded the grid's loss sums wait for its global stores: 3 k cycles)
+        if (nxt < ntiles) fence_async_smem();
+        WARP_CLOCK(10)
+        sync_tasks();   // #7
         TILE_CLOCK(9)
         if (tma && nxt < ntiles) load_d6(nxt);
         // ---- z[t] = sum_{s >= t} y[s] over the frames of the clip (lanes are frames: a segmented suffix scan over
@@ -1218,7 +1266,8 @@ __global__ void __launch_bounds__(MAX_THREADS, 1) tile_kernel(const TileArgs a) 
             });
         }
         fence_async_smem();
-        __syncthreads();   // #8
+        WARP_CLOCK(11)
+        sync_tasks();   // #8
         TILE_CLOCK(12)
         if (tma) {
             bulk_s2g(a.g_d6 + (size_t)m0 * B6, G3, (uint32_t)(np * B6) * 4u);
@@ -1350,6 +1399,9 @@ extern "C" int p2c_fused_tile_supported(const p2c_fused_step_t* p) {
 extern "C" int p2c_debug_cta_times(unsigned long long* out) {
     return (int)cudaMemcpyFromSymbol(out, g_cta_times, sizeof(unsigned long long) * 2048);
 }
+extern "C" int p2c_debug_warp_clocks(long long* out) {
+    return (int)cudaMemcpyFromSymbol(out, g_warp_clocks, sizeof(long long) * 512);
+}
 extern "C" int p2c_debug_tile_clocks(long long* out) {
     return (int)cudaMemcpyFromSymbol(out, g_tile_clocks, sizeof(long long) * 64);
 }
@@ -1414,6 +1466,7 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     const bool limb_ok = t.threads / 32 > 5 * t.slices;
     const int ki = world ? 5 : !carla ? 4 : t.count_inline ? (t.slices == 1 ? 2 : 3) : !limb_ok ? 4 : (t.slices == 1 ? 0 : 1);
     const bool rot = p->gt_abs_rot != nullptr;
+    const int threads = t.threads + ((P2C_SERVICE_WARP && (ki == 2 || ki == 3)) ? 32 : 0);   // + the service warp
     const kern_t k = rot ? (ki == 0   ? tile_kernel<26, 1, false, false, true>
                             : ki == 1 ? tile_kernel<26, 2, false, false, true>
                             : ki == 2 ? tile_kernel<26, 1, false, true, true>
@@ -1429,7 +1482,7 @@ extern "C" int p2c_fused_tile(const p2c_fused_step_t* p, void* stream) {
     if (const int e = p2c_allow_big_smem(reinterpret_cast<const void*>(k), 227 * 1024 - 1024)) return e;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(t.grid);
-    cfg.blockDim = dim3(t.threads);
+    cfg.blockDim = dim3(threads);
     cfg.dynamicSmemBytes = t.smem;
     cfg.stream = st;
     cudaLaunchAttribute attr[2];

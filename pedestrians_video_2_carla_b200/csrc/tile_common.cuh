@@ -228,6 +228,7 @@ struct Parity {
 // twice and picked by a (warp-uniform) branch on the task's parity
 template <int MODE, typename F>
 __device__ __forceinline__ void bone_tasks(int warp, int W, int nt, F f) {
+    if (warp >= W) return;   // (a warp beyond the W task warps -- the service warp of fused_tile.cu -- has no tasks)
     if (MODE == 1) {
 #pragma unroll 1
         for (int t = 2 * warp; t < nt; t += 2 * W) {

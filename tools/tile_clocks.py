@@ -23,6 +23,8 @@ v = v[:10] + [v[12]]
 for i in range(1, 11):
     print('%-30s +%6d cycles' % (names[i], v[i] - v[i - 1]))
 print('tile total %d cycles' % (v[10] - v[0]))
+if buf[10] and buf[11]:
+    print('  inside norm bwd + subtree sums: sums over bones(bar5a) +%d, own parts(bar5b) +%d, subtree walks +%d' % (buf[10] - buf[7], buf[11] - buf[10], buf[8] - buf[11]))
 w = list(buf)
 if w[16]:
     print('CTA 0: entry -> tile loop %d, tile loop %d, store drain %d, loss fold + ticket %d cycles' % (
@@ -33,6 +35,24 @@ if w[32]:
     print('trunk walk, cycles after barrier 3 per bone:', [int(w[32 + b] - w[4]) for b in range(8)])
 if w[40]:
     print('scan (thread 0), cycles after barrier 2 per two-frame trip:', [int(w[40 + k] - w[3]) for k in range(16) if w[40 + k]])
+if os.environ.get('P2C_WARP_CLOCKS'):
+    wc = (ctypes.c_longlong * 512)()
+    lib.p2c_debug_warp_clocks.argtypes = [ctypes.c_void_p]
+    assert lib.p2c_debug_warp_clocks(wc) == 0
+    tags = ['', '#1', '#2', '#3', '#4', '#4b', '#5', '#5a', '#5b', '#6', '#7', '#8']
+    arr = [[wc[wp * 16 + k] for k in range(16)] for wp in range(32)]
+    nw = max(wp for wp in range(32) if arr[wp][2]) + 1
+    prev = None
+    for k in range(1, 12):
+        t = [arr[wp][k] for wp in range(nw)]
+        if not all(t):
+            continue
+        rel = max(t)
+        late = sorted(range(nw), key=lambda wp: -t[wp])[:4]
+        early = sorted(t)[nw // 2]
+        print('barrier %-3s released %6d after the previous one; median warp arrived %5d before the release; last warps: %s' % (
+            tags[k], rel - prev if prev else 0, rel - early, ', '.join('w%d (-%d)' % (wp, rel - t[wp]) for wp in late)))
+        prev = rel
 ct = (ctypes.c_ulonglong * 2048)()
 lib.p2c_debug_cta_times.argtypes = [ctypes.c_void_p]
 assert lib.p2c_debug_cta_times(ct) == 0
@@ -45,6 +65,9 @@ tiles = None
 print('%d CTAs: start us min %.1f med %.1f max %.1f | end us min %.1f med %.1f max %.1f | life us min %.1f med %.1f max %.1f' % (
     len(t), st.min(), np.median(st), st.max(), en.min(), np.median(en), en.max(), (en - st).min(), np.median(en - st), (en - st).max()))
 life = en - st
+if os.environ.get('P2C_CLOCKS_ALL'):
+    print('life by CTA (us):', ' '.join('%.1f' % x for x in life))
+    print('start by CTA (us):', ' '.join('%.1f' % x for x in st))
 order = np.argsort(life)
 print('shortest-lived CTAs', order[:6].tolist(), 'longest-lived', order[-6:].tolist())
 tt = np.array(list(ct), dtype=np.int64).reshape(-1, 2)
