@@ -444,6 +444,33 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
         mbar_init(bars + 2, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    // Set-up that touches no global memory comes BEFORE the wait for the previous kernel of the stream: the CTAs of a
+    // chained step are resident (and idle in that wait) before the step in front of them has finished.
+    // suffix scan over the frames of a clip (phase E): bit k of scan_ok<slice> = "the lane 2^k to the right holds a later
+    // frame of MY clip" -- a function of the lane alone, so the rounds of the scan test one bit instead of comparing
+    // (kept in shared memory: two more live registers cost more in spills than a read per task)
+    __shared__ unsigned scan_ok_s[64];
+    if (warp == 0) {
+        const int lane_clip = lane / L, lane_frame = lane - lane_clip * L;   // (one slice: whole clips side by side)
+        unsigned ok0 = (unsigned)lane_clip << 8, ok1 = 0u;   // (bits 8..: the lane's clip within a one-slice tile)
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            const int off = 1 << k;
+            if (lane + off < 32) {
+                if ((slices == 1 ? lane_frame : lane) + off < L) ok0 |= 1u << k;
+                if (32 + lane + off < L) ok1 |= 1u << k;
+            }
+        }
+        scan_ok_s[lane] = ok0;
+        scan_ok_s[32 + lane] = ok1;
+    }
+    __shared__ signed char par_s[P2C_MAX_BONES];      // parents (a shared-memory read per task instead of arithmetic)
+    if (tid < B) par_s[tid] = (signed char)(BT == 26 ? carla_parent(tid) : a.parent[tid]);
+    __shared__ int cta_count;
+    __shared__ float k2_shared;
+    __shared__ int last_s;
+    if (tid == 0) { cta_count = 0; last_s = 0; }
+    __syncthreads();   // (mbarriers initialised, tables and counters in place)
     if (a.count_inline || !a.mask) {
         // No count pre-pass in front of this launch (one tile per CTA, or the mask is off): the kernel is launched with
         // programmatic stream serialization, so the previous kernel of the stream may still be running (a one-tile-
@@ -462,18 +489,13 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
             load_targets(blockIdx.x);
         }
     }
+    // (the first tile's row table: visible to the other warps after barrier #1)
     if (warp == 0 && (int)blockIdx.x < ntiles) fill_rows(blockIdx.x, 0);
-    __shared__ int cta_count;
-    __shared__ float k2_shared;
-    if (tid == 0) cta_count = 0;
-    __syncthreads();
 
     float k2 = a.k2_all;   // (mask on: replaced below once the count is known)
     // ---- loss sums: one partial pair per TILE (fixed order inside the tile), so the totals do not depend on which
     //      CTA ran which tile; the last CTA to take a ticket folds them in tile order at the end of the kernel
     __shared__ int next_s[2];
-    __shared__ int last_s;
-    if (tid == 0) last_s = 0;
     unsigned my_ticket = 0xffffffffu;   // (drawn by one lane after this CTA's last partial store, looked at later)
     auto fold_args = [&]() {
         FoldArgs f;
@@ -496,27 +518,7 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
     unsigned it = 0;
     CTA_CLOCK(17)
     const int clips_full = a.clips_full;
-    // suffix scan over the frames of a clip (phase E): bit k of scan_ok<slice> = "the lane 2^k to the right holds a later
-    // frame of MY clip" -- a function of the lane alone, so the rounds of the scan test one bit instead of comparing
-    // (kept in shared memory: two more live registers cost more in spills than a read per task)
-    __shared__ unsigned scan_ok_s[64];
-    if (warp == 0) {
-        const int lane_clip = lane / L, lane_frame = lane - lane_clip * L;   // (one slice: whole clips side by side)
-        unsigned ok0 = (unsigned)lane_clip << 8, ok1 = 0u;   // (bits 8..: the lane's clip within a one-slice tile)
-#pragma unroll
-        for (int k = 0; k < 5; ++k) {
-            const int off = 1 << k;
-            if (lane + off < 32) {
-                if ((slices == 1 ? lane_frame : lane) + off < L) ok0 |= 1u << k;
-                if (32 + lane + off < L) ok1 |= 1u << k;
-            }
-        }
-        scan_ok_s[lane] = ok0;
-        scan_ok_s[32 + lane] = ok1;
-    }
     const bool whole_clips = a.whole_clips != 0;   // pose_changes mode; relative_rot tiles are 32 free poses
-    __shared__ signed char par_s[P2C_MAX_BONES];      // parents (a shared-memory read per task instead of arithmetic)
-    if (tid < B) par_s[tid] = (signed char)(BT == 26 ? carla_parent(tid) : a.parent[tid]);
 
     // tiles beyond the first come from a grid-wide counter (SMs do not run at one speed: up to a quarter between the
     // fastest and the slowest CTA under a static split); the ticket is drawn at the top of a tile and first needed
