@@ -572,6 +572,11 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
         WARP_CLOCK(2)
         __syncthreads();   // #2
         TILE_CLOCK(3)
+        // (Measured alternatives for the one-tile kernels, all slower than the column mapping below -- a warp issues an
+        // FFMA every 2 cycles at best, so what counts is the instruction count on the busiest scheduler, not the length
+        // of the dependency chain: a thread per ELEMENT (three neighbouring lanes per column, 3 reads + 3 shuffles + 3
+        // FMAs + 1 store per frame, 16 warps): 3.1 k cycles against 2.8 k; a LANE PER BONE forming the full 3x3 product
+        // (two warps, every word read once): 3.75 k.)
         // ---- phase B: R[t] = C[t] . R[t-1] (p3d_pose.py:98-114 looped by layers/projection.py:190-193); one thread
         //      per (clip, bone, column of R), serial over the frames of the clip
         if (a.scan) {
