@@ -41,6 +41,11 @@ __device__ __forceinline__ bool kept2(float gx, float gy, int j, int hips) {
 __global__ void __launch_bounds__(LT, 1) loc2d_step_kernel(const Loc2dArgs a) {
     extern __shared__ __align__(16) float esm[];   // masked errors of this CTA's joints, (x, y) pairs
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // Launched with programmatic stream serialization (p2c_loc2d_step): the previous kernel of the stream may still be
+    // running.  Everything in global memory may come from it (predictions, the self-resetting barrier words): wait until
+    // it is complete and flushed, then let the NEXT kernel's launch overlap this one.  (A no-op in a plain launch.)
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     if (blockIdx.x == 0 && tid == LT - 32) exchange_send_pending(a.xchg);   // the previous step's sums, off the tail
     const long j0 = (long)blockIdx.x * a.per_cta;   // (per_cta is even: pairs never straddle CTAs)
     long left = a.joints - j0;
@@ -200,12 +205,19 @@ extern "C" int p2c_loc2d_step(const float* pred, const float* gt, int64_t m, int
     cfg.blockDim = dim3(LT);
     cfg.dynamicSmemBytes = pl.smem;
     cfg.stream = (cudaStream_t)stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeCooperative;   // the CTAs wait for each other: all resident at once or no launch
     attr[0].val.cooperative = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;   // chained steps: see the top of the kernel
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
-    const cudaError_t le = cudaLaunchKernelEx(&cfg, loc2d_step_kernel, a);
+    cfg.numAttrs = 2;
+    cudaError_t le = cudaLaunchKernelEx(&cfg, loc2d_step_kernel, a);
+    if (le != cudaSuccess) {   // (the two attributes together are refused: cooperative only)
+        (void)cudaGetLastError();
+        cfg.numAttrs = 1;
+        le = cudaLaunchKernelEx(&cfg, loc2d_step_kernel, a);
+    }
     if (le != cudaSuccess) return (int)le;
     P2C_LAUNCH_CHECK();
     return 0;
