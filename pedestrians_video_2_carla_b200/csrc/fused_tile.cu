@@ -1010,11 +1010,7 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
         if (tma) {
             if (a.abs_loc) bulk_s2g(a.abs_loc + (size_t)m0 * B3, G3, (uint32_t)(np * B3) * 4u);
             if (a.proj) bulk_s2g(a.proj + (size_t)m0 * B3, G2, (uint32_t)(np * B3) * 4u);
-            bulk_commit();
-            bulk_wait_read_all();
-            // the 6-D records come back (L2 hot) over the two target regions; phase E waits for them
-            mbar_expect_tx(bars + 2, (uint32_t)(np * B6) * 4u);
-            bulk_g2s(G3, a.d6 + (size_t)m0 * B6, (uint32_t)(np * B6) * 4u, bars + 2);
+            bulk_commit();   // (the regions are free again once these stores have read them: see after barrier #5b)
         }
         // ---- normaliser backward through shift (hips) and scale (|neck - hips|): it needs the sums over all bones
         //      (three warps per slice, one per sum), and lands on g_hips and g_neck before the subtree sums are formed
@@ -1022,10 +1018,23 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
             if (warp < 3 * slices) {
                 const int k = warp % 3, col = (warp / 3) * 32 + lane;
                 float s0_ = 0.f, s1_ = 0.f;
+                if (BT == 26) {
+                    // every read in flight before the first addition (the additions keep their order): three warps
+                    // hold up the whole CTA here, and a read-add-read-add chain cost 1.2 - 2.4 k cycles per tile
+                    float v[26];
+#pragma unroll
+                    for (int q = 0; q < 26; ++q) v[q] = PART[(q * 3 + k) * PS + col];
+#pragma unroll
+                    for (int q = 0; q < 26; q += 2) {
+                        s0_ += v[q];
+                        s1_ += v[q + 1];
+                    }
+                } else {
 #pragma unroll 1
-                for (int q = 0; q + 1 < B; q += 2) {
-                    s0_ += PART[(q * 3 + k) * PS + col];
-                    s1_ += PART[(q * 3 + 3 + k) * PS + col];
+                    for (int q = 0; q + 1 < B; q += 2) {
+                        s0_ += PART[(q * 3 + k) * PS + col];
+                        s1_ += PART[(q * 3 + 3 + k) * PS + col];
+                    }
                 }
                 NRM[(6 + k) * PS + col] = s0_ + s1_;   // (B is even)
             }
@@ -1096,6 +1105,14 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
         WARP_CLOCK(8)
         if (SERVICE && ROT) named_arrive(6, (W + 1) * 32);   // (red_r is complete: the service warp may go on)
         sync_tasks();   // #5b
+        if (tma) {
+            // the 6-D records come back (L2 hot) over the two target regions, as soon as the stores of abs_loc and
+            // projection have read them: asked for HERE, where the issuing thread's warp has no part in the subtree
+            // walks (the wait for the stores used to hold the whole CTA at barrier #5a); phase E waits for the records
+            bulk_wait_read_all();
+            mbar_expect_tx(bars + 2, (uint32_t)(np * B6) * 4u);
+            bulk_g2s(G3, a.d6 + (size_t)m0 * B6, (uint32_t)(np * B6) * 4u, bars + 2);
+        }
         TILE_CLOCK(11)
         if (!SERVICE && ROT && warp == svc) store_partial();
         // few tiles: the warp that drew this CTA's ticket folds the grid's partials if it was the last -- NOW, when it has
@@ -1196,7 +1213,6 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
         // (two warps without a column when W >= 6 slices + 2: both jobs wait on global memory, off the critical path)
         if (nxt < ntiles && warp == W - 1) fill_rows(nxt, (it + 1) & 1);
         if (!SERVICE && !fold_early && nxt >= ntiles && a.warp_fold && warp == svc) fold_if_last();   // (the ticket was drawn after the loss pass)
-        while (!mbar_try_wait(bars + 2, it & 1u)) {}
         WARP_CLOCK(9)
         sync_tasks();   // #6
         TILE_CLOCK(8)
@@ -1235,6 +1251,7 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
         sync_tasks();   // #7
         TILE_CLOCK(9)
         if (tma && nxt < ntiles) load_d6(nxt);
+        while (!mbar_try_wait(bars + 2, it & 1u)) {}   // the 6-D records are back
         // ---- z[t] = sum_{s >= t} y[s] over the frames of the clip (lanes are frames: a segmented suffix scan over
         //      shuffles),  omega = R[t] z[t],  tangent-form Gram-Schmidt backward -> gradient records over the 6-D
         //      records (which now live in the two target regions)
