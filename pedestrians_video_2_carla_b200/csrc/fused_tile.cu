@@ -36,6 +36,9 @@
 #include "host_util.h"
 #include "tile_common.cuh"
 
+#ifndef P2C_ENTRY_PREFETCH
+#define P2C_ENTRY_PREFETCH 1   // 0: experiment, no L2 prefetch of the first tile ahead of the dependency wait
+#endif
 #ifndef P2C_SERVICE_WARP
 #define P2C_SERVICE_WARP 1   // 0: experiment, the loss fold stays in task warp W - 2
 #endif
@@ -446,6 +449,18 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
     }
     // Set-up that touches no global memory comes BEFORE the wait for the previous kernel of the stream: the CTAs of a
     // chained step are resident (and idle in that wait) before the step in front of them has finished.
+#if P2C_ENTRY_PREFETCH
+    // ... and so do L2 PREFETCHES of the first tile's records: they return no data (L2 is the point of coherence: if
+    // the previous kernel still writes these lines, the loads after the wait see its writes), they only start the trip
+    // from HBM early, so that the TMA loads issued after the wait find the records in L2.
+    if (tma && (int)blockIdx.x < ntiles) {
+        const int m0 = blockIdx.x * a.P, np0 = min(a.P, total - m0);
+        const uint32_t b6 = (uint32_t)(np0 * B6) * 4u, b3 = (uint32_t)(np0 * B3) * 4u;
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.d6 + (size_t)m0 * B6), "r"(b6) : "memory");
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.gt3 + (size_t)m0 * B3), "r"(b3) : "memory");
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.gt2 + (size_t)m0 * B3), "r"(b3) : "memory");
+    }
+#endif
     // suffix scan over the frames of a clip (phase E): bit k of scan_ok<slice> = "the lane 2^k to the right holds a later
     // frame of MY clip" -- a function of the lane alone, so the rounds of the scan test one bit instead of comparing
     // (kept in shared memory: two more live registers cost more in spills than a read per task)

@@ -44,6 +44,18 @@ __global__ void __launch_bounds__(LT, 1) loc2d_step_kernel(const Loc2dArgs a) {
     // Launched with programmatic stream serialization (p2c_loc2d_step): the previous kernel of the stream may still be
     // running.  Everything in global memory may come from it (predictions, the self-resetting barrier words): wait until
     // it is complete and flushed, then let the NEXT kernel's launch overlap this one.  (A no-op in a plain launch.)
+    // (ahead of the wait: L2 prefetches of this CTA's slice -- they return no data, L2 is the point of coherence, they
+    // only start the trip from HBM while the previous kernel drains)
+    if (tid == 0) {
+        const long pj0 = (long)blockIdx.x * a.per_cta, pleft = a.joints - pj0;
+        const long pn = pleft <= 0 ? 0 : (pleft < a.per_cta ? pleft : a.per_cta);
+        const unsigned bytes = (unsigned)((pn * 2 * sizeof(float)) & ~15ul);
+        if (bytes) {
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.pred + pj0 * 2), "r"(bytes) : "memory");
+            if (a.c_gt == 2)
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.gt + pj0 * 2), "r"(bytes) : "memory");
+        }
+    }
     asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     if (blockIdx.x == 0 && tid == LT - 32) exchange_send_pending(a.xchg);   // the previous step's sums, off the tail
