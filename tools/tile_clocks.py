@@ -53,6 +53,9 @@ if os.environ.get('P2C_WARP_CLOCKS'):
         print('barrier %-3s released %6d after the previous one; median warp arrived %5d before the release; last warps: %s' % (
             tags[k], rel - prev if prev else 0, rel - early, ', '.join('w%d (-%d)' % (wp, rel - t[wp]) for wp in late)))
         prev = rel
+if w[50] and w[54]:
+    print('fold (service warp of the last CTA): partial stored + ticket known +%d, fence + partials read +%d, shuffles +%d, totals stored +%d => %d cycles after its barrier 5' % (
+        w[51] - w[50], w[52] - w[51], w[53] - w[52], w[54] - w[53], w[54] - w[50]))
 ct = (ctypes.c_ulonglong * 2048)()
 lib.p2c_debug_cta_times.argtypes = [ctypes.c_void_p]
 assert lib.p2c_debug_cta_times(ct) == 0
