@@ -42,6 +42,9 @@
 #ifndef P2C_POLL_FOLD
 #define P2C_POLL_FOLD 1   // 0: experiment, the service warp of the LAST CTA folds (ticket scheme)
 #endif
+#ifndef P2C_EARLY_NORM
+#define P2C_EARLY_NORM 1   // 0: experiment, shift / scale after the forward walk
+#endif
 #ifndef P2C_SERVICE_WARP
 #define P2C_SERVICE_WARP 1   // 0: experiment, the loss fold stays in task warp W - 2
 #endif
@@ -759,6 +762,10 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
         //      column of the parent), each walking the whole tree in bone order.
         constexpr bool limbs = BT == 26 && !LONE;
         constexpr bool lone_limbs = BT == 26 && LONE && SL == 1;   // limb groups of three column warps each
+        // (one tile per CTA) hips and neck come early in the walk (trunk, first bone of the head group): a warp without
+        // a column forms the normaliser's shift and scale from them WHILE the limbs are still walked -- one phase and
+        // one barrier (#4b) less on the CTA's critical path
+        const bool early_norm = P2C_EARLY_NORM && lone_limbs && a.normalize && a.neck == 8 && a.hips <= 3;
         const int fk_warps = limbs ? 5 * slices : lone_limbs ? 15 : 3 * slices;
         if (limbs && warp < fk_warps) {
             const int grp = warp / slices, col = (warp - grp * slices) * 32 + lane, pl = min(col, np - 1);
@@ -903,7 +910,9 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
                     P2C_RUNC(4, 8)
                 } else if (cgrp == 1) {
                     named_barrier(4, 9 * 32);
-                    P2C_RUNC(8, 12)
+                    P2C_RUNC(8, 9)
+                    if (early_norm) named_arrive(8, 4 * 32);   // neck (and, through barrier 4, hips) are in place
+                    P2C_RUNC(9, 12)
                 } else if (cgrp == 2) {
                     named_barrier(4, 9 * 32);
                     P2C_RUNC(12, 16)
@@ -931,6 +940,20 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
                 }
             }
             fence_async_smem();
+        } else if (early_norm && warp == fk_warps + 1) {
+            named_barrier(8, 4 * 32);
+            const int col = lane, m = m0 + min(col, np - 1);
+            const V3 th{TS[(a.hips * 3) * PS + col], TS[(a.hips * 3 + 1) * PS + col], TS[(a.hips * 3 + 2) * PS + col]};
+            const V3 tn{TS[(a.neck * 3) * PS + col], TS[(a.neck * 3 + 1) * PS + col], TS[(a.neck * 3 + 2) * PS + col]};
+            const Proj ph = project<WORLD>(a, th, m), pn = project<WORLD>(a, tn, m);
+            const float dx = pn.p.x - ph.p.x, dy = pn.p.y - ph.p.y;
+            const float scale = fsqrt(fmaf(dx, dx, dy * dy));
+            NRM[col] = ph.p.x;
+            NRM[PS + col] = ph.p.y;
+            NRM[2 * PS + col] = dx;
+            NRM[3 * PS + col] = dy;
+            NRM[4 * PS + col] = frcp(scale);
+            NRM[5 * PS + col] = (scale > 0.f && scale <= 3.402823466e38f) ? 1.f : 0.f;
         } else if (a.mask && a.count_inline && tid == fk_warps * 32) {
             // one lane of a warp without a column polls until every CTA of the grid has sent its count (all CTAs are
             // resident: one tile each, at most one CTA per SM)
@@ -959,7 +982,7 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
             bulk_commit();
         }
         // hips/neck shift and scale of every pose (extractor.py:23-36, hips_neck_extractor.py:6-13)
-        if (a.normalize && warp < slices) {
+        if (a.normalize && !early_norm && warp < slices) {
             const int col = warp * 32 + lane;
             const int m = m0 + min(col, np - 1);
             const V3 th{TS[(a.hips * 3) * PS + col], TS[(a.hips * 3 + 1) * PS + col], TS[(a.hips * 3 + 2) * PS + col]};
@@ -976,7 +999,7 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
         }
         while (!mbar_try_wait(bars + 1, it & 1u)) {}
         WARP_CLOCK(5)
-        __syncthreads();   // #4b
+        if (!early_norm) __syncthreads();   // #4b (shift / scale in place; early_norm: they were before barrier #4)
         if (a.mask && a.count_inline) k2 = k2_shared;
         if (a.mask && !a.count_inline && it == 0) {
             asm volatile("griddepcontrol.wait;" ::: "memory");   // the count pre-pass (launched just before) is complete
