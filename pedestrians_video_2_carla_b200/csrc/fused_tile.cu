@@ -45,6 +45,9 @@
 #ifndef P2C_EARLY_NORM
 #define P2C_EARLY_NORM 1   // 0: experiment, shift / scale after the forward walk
 #endif
+#ifndef P2C_EARLY_NORM_MANY
+#define P2C_EARLY_NORM_MANY 1   // 0: experiment, early shift / scale only in the one-tile kernels
+#endif
 #ifndef P2C_SERVICE_WARP
 #define P2C_SERVICE_WARP 1   // 0: experiment, the loss fold stays in task warp W - 2
 #endif
@@ -765,7 +768,8 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
         // (one tile per CTA) hips and neck come early in the walk (trunk, first bone of the head group): a warp without
         // a column forms the normaliser's shift and scale from them WHILE the limbs are still walked -- one phase and
         // one barrier (#4b) less on the CTA's critical path
-        const bool early_norm = P2C_EARLY_NORM && lone_limbs && a.normalize && a.neck == 8 && a.hips <= 3;
+        const bool early_norm = P2C_EARLY_NORM && (lone_limbs || (limbs && P2C_EARLY_NORM_MANY)) && a.normalize &&
+                                a.neck == 8 && a.hips <= 3;
         const int fk_warps = limbs ? 5 * slices : lone_limbs ? 15 : 3 * slices;
         if (limbs && warp < fk_warps) {
             const int grp = warp / slices, col = (warp - grp * slices) * 32 + lane, pl = min(col, np - 1);
@@ -836,7 +840,9 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
                 P2C_RUN(4, 8)               // left arm
             } else if (grp == 1) {
                 named_barrier(4, 3 * slices * 32);
-                P2C_RUN(8, 12)              // neck, head, eyes
+                P2C_RUN(8, 9)               // neck
+                if (early_norm) named_arrive(8 + (warp - grp * slices), 2 * 32);   // (per slice: this warp + the spare one)
+                P2C_RUN(9, 12)              // head, eyes
             } else if (grp == 2) {
                 named_barrier(4, 3 * slices * 32);
                 P2C_RUN(12, 16)             // right arm
@@ -940,9 +946,13 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
                 }
             }
             fence_async_smem();
-        } else if (early_norm && warp == fk_warps + 1) {
-            named_barrier(8, 4 * 32);
-            const int col = lane, m = m0 + min(col, np - 1);
+        } else if (early_norm && (lone_limbs ? warp == fk_warps + 1 : warp < fk_warps + slices)) {
+            // (many tiles: warps fk_warps .. fk_warps + slices - 1, one per slice; one tile per CTA: the warp behind the
+            // lane that polls the grid's count)
+            const int sl = lone_limbs ? 0 : warp - fk_warps;
+            if (lone_limbs) named_barrier(8, 4 * 32);
+            else named_barrier(8 + sl, 2 * 32);
+            const int col = sl * 32 + lane, m = m0 + min(col, np - 1);
             const V3 th{TS[(a.hips * 3) * PS + col], TS[(a.hips * 3 + 1) * PS + col], TS[(a.hips * 3 + 2) * PS + col]};
             const V3 tn{TS[(a.neck * 3) * PS + col], TS[(a.neck * 3 + 1) * PS + col], TS[(a.neck * 3 + 2) * PS + col]};
             const Proj ph = project<WORLD>(a, th, m), pn = project<WORLD>(a, tn, m);
