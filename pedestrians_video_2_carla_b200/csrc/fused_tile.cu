@@ -48,6 +48,9 @@
 #ifndef P2C_EARLY_NORM_MANY
 #define P2C_EARLY_NORM_MANY 1   // 0: experiment, early shift / scale only in the one-tile kernels
 #endif
+#ifndef P2C_MERGE_YE
+#define P2C_MERGE_YE 1   // 0: experiment, y in a pass of its own in the one-tile kernels too
+#endif
 #ifndef P2C_SERVICE_WARP
 #define P2C_SERVICE_WARP 1   // 0: experiment, the loss fold stays in task warp W - 2
 #endif
@@ -1349,7 +1352,25 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
         // ---- per bone, all independent:  m_b = Sx_b - Sg_b x t_b,  y_b = A_parent m_b  (in place over Sx_b).  After this
         //      pass the scratch rows (t, Sg) and the abs_rot records are dead, so the next tile's 6-D records can start
         //      their way in while the gradient pass runs.
-        {
+        // (one tile per CTA, one slice: bone b's y and its gradient pass run in the SAME warp -- y stays in registers, no
+        // pass of its own, no barrier #7: MERGE_YE)
+        constexpr bool MERGE_YE = BT == 26 && LONE && SL == 1 && P2C_MERGE_YE;
+        auto y_of = [&](int b, int col, int pl) {
+            const int par = par_s[b];
+            const V3 sx{XR[(b * 3) * PS + col], XR[(b * 3 + 1) * PS + col], XR[(b * 3 + 2) * PS + col]};
+            const V3 sg{GV[(b * 3) * PS + col], GV[(b * 3 + 1) * PS + col], GV[(b * 3 + 2) * PS + col]};
+            const V3 t{TS[(b * 3) * PS + col], TS[(b * 3 + 1) * PS + col], TS[(b * 3 + 2) * PS + col]};
+            const V3 mv{sx.x - (sg.y * t.z - sg.z * t.y), sx.y - (sg.z * t.x - sg.x * t.z),
+                        sx.z - (sg.x * t.y - sg.y * t.x)};
+            V3 y = mv;
+            if (par >= 0) {   // (the parent's parity is a run-time value: two access sequences behind a branch)
+                if (par & 1) y = v3_mul_mt(mv, lds9<1>(A + pl * B9, par));
+                else y = v3_mul_mt(mv, lds9<0>(A + pl * B9, par));
+            }
+            if (col >= np) y = V3{0.f, 0.f, 0.f};
+            return y;
+        };
+        if (!MERGE_YE) {
             const int nt = slices * B;
 #pragma unroll 1
             for (int task = warp; task < nt; task += W) {
@@ -1378,7 +1399,7 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
         // would only make the thread that folded the grid's loss sums wait for its global stores: 3 k cycles)
         if (nxt < ntiles) fence_async_smem();
         WARP_CLOCK(10)
-        sync_tasks();   // #7
+        if (!MERGE_YE) sync_tasks();   // #7
         TILE_CLOCK(9)
         if (tma && nxt < ntiles) load_d6(nxt);
         while (!mbar_try_wait(bars + 2, it & 1u)) {}   // the 6-D records are back
@@ -1394,7 +1415,8 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
                 for (int sl = slices - 1; sl >= 0; --sl) {
                     const int col = sl * 32 + lane, pl = min(col, np - 1);
                     const bool valid = col < np;
-                    V3 z{XR[(b * 3) * PS + col], XR[(b * 3 + 1) * PS + col], XR[(b * 3 + 2) * PS + col]};
+                    V3 z = MERGE_YE ? y_of(b, col, pl)
+                                    : V3{XR[(b * 3) * PS + col], XR[(b * 3 + 1) * PS + col], XR[(b * 3 + 2) * PS + col]};
                     if (a.scan) {
                         const unsigned ok = scan_ok_s[sl * 32 + lane];
 #pragma unroll
