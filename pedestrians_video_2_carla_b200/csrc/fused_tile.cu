@@ -483,6 +483,7 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
         asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.d6 + (size_t)m0 * B6), "r"(b6) : "memory");
         asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.gt3 + (size_t)m0 * B3), "r"(b3) : "memory");
         asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a.gt2 + (size_t)m0 * B3), "r"(b3) : "memory");
+        if (a.ref_index) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.ref_index + m0 / L) : "memory");   // (row table)
     }
 #endif
     // suffix scan over the frames of a clip (phase E): bit k of scan_ok<slice> = "the lane 2^k to the right holds a later
@@ -517,6 +518,7 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
         // per-CTA step triggers its dependents at its very top).  Everything in global memory -- the inputs, the
         // self-resetting workspace header -- may come from it: wait until it is complete and flushed.
         asm volatile("griddepcontrol.wait;" ::: "memory");
+        CTA_CLOCK(23)
         // (one tile per CTA) let the next kernel's CTAs take the SMs as this grid's CTAs retire
         if (a.count_inline) asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     }

@@ -29,6 +29,8 @@ w = list(buf)
 if w[16]:
     print('CTA 0: entry -> tile loop %d, tile loop %d, store drain %d, loss fold + ticket %d cycles' % (
         w[17] - w[16], w[18] - w[17], w[19] - w[18], w[20] - w[19]))
+if w[23]:
+    print('entry: top -> dependency wait over %d, -> tile loop %d, -> first 6-D records landed %d cycles' % (w[23] - w[16], w[17] - w[23], v[1] - w[17]))
 if w[21]:
     print('forward walk done %d, count poll done %d cycles after barrier 3' % (w[21] - w[4], w[22] - w[4]))
 if w[32]:
