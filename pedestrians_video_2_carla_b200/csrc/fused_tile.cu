@@ -537,7 +537,9 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
     }
     // data-parallel ranks: the sums the previous step left in this rank's exchange block go out to the peers now, so
     // that their NVLink round trip is over long before this kernel's own tail
-    if (blockIdx.x == 0 && tid == (W - 2) * 32) exchange_send_pending(a.xchg);
+    // (by the service warp where there is one: a task warp's next proxy fence would wait for the peer stores' NVLink
+    // round trip, and with it CTA 0 at its next barrier -- 0.5 us per step at N > 1)
+    if (blockIdx.x == 0 && tid == svc * 32) exchange_send_pending(a.xchg);
     if (tma) {
         if ((int)blockIdx.x < ntiles) {
             load_d6(blockIdx.x);
