@@ -205,8 +205,10 @@ typedef struct {
     float* proj_norm;            /* out (N,L,B,3) normalised projection or NULL                      */
     float* g_pose_in;            /* out, same shape as pose_in                                       */
     float* workspace;            /* p2c_fused_step_workspace_floats(N*L, B, input_6d) floats; its first 16 floats
-                                    are self-resetting counters: zero them ONCE before the first call, every call
-                                    leaves them zero again; do not share one workspace between concurrent streams */
+                                    are counters the kernels maintain themselves: zero them ONCE before the first
+                                    call and leave them alone afterwards (every call leaves its counters zero again;
+                                    word 5 is a launch sequence that keeps counting); do not share one workspace
+                                    between concurrent streams                                                    */
     float* losses;               /* out, 8 floats (12 with gt_abs_rot, see below)                    */
     /* data-parallel ranks (one process per GPU, clips sharded by batch): when `exchange` is a block made by
        p2c_exchange_create + p2c_exchange_set_peers, the kernel that finishes the loss sums also stores this rank's
