@@ -1128,6 +1128,13 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
                         d3 += __shfl_xor_sync(FULL_MASK, d3, o);
                         dr += __shfl_xor_sync(FULL_MASK, dr, o);
                     }
+                    // the entries are spent: no later launch may take them for its own, whatever the caller does to
+                    // the header in between (a header zeroed again restarts the sequence)
+                    for (int i = lane; i < ntiles; i += 32) {
+#pragma unroll
+                        for (int k = 0; k < (ROT ? 3 : 2); ++k)
+                            asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(ent + 4 * (size_t)i + k), "l"(0ull) : "memory");
+                    }
                     if (lane == 0) {
                         FoldArgs f = fold_args();
                         f.count_known = a.mask ? count_s : -1;

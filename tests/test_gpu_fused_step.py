@@ -506,3 +506,25 @@ def test_rot_3d_fused_in_the_step(ops, lib, n, l, tree, w):
     assert_close('total', res.total, want['total'])
     assert float(res.losses[10]) == n * l * c['b'] * 9
     assert_close_fp32_aware('grad', x.grad, g64, g32)
+
+
+def test_one_workspace_through_shape_changes_and_a_zeroed_header(ops, lib):
+    """The step's loss totals go through the caller's workspace: per-tile partials behind a ticket (many tiles) or as
+    self-validating (value, launch sequence) entries folded by CTA 0 (one tile per CTA).  One workspace is taken
+    through a one-tile launch, a many-tile launch, one-tile launches again, and a header that the caller zeroes in
+    between (which restarts the launch sequence): every step's totals must be the ones of its own inputs."""
+    from pedestrians_video_2_carla_b200 import ops as _ops
+    cases = []
+    for n, l, seed in ((8, 16, 3), (400, 16, 4), (8, 16, 5), (6, 16, 6), (8, 16, 7)):
+        c = make_case(n, l, seed, world=False)
+        gt2, gt3 = make_targets(c)
+        want = oracle_step(c, O.rotation_6d_to_matrix(c['d6']), gt=(gt2, gt3))
+        cases.append((c, gt2, gt3, want))
+    for k, (c, gt2, gt3, want) in enumerate(cases):
+        if k == 3:   # the caller zeroes the 16 header words again (and only them)
+            for ws in _ops._WS.values():
+                ws[:16].zero_()
+        for _ in range(2):
+            res, _grad = run_cuda(ops, lib, c, c['d6'], gt2, gt3, 'pose_changes', True, True)
+            assert_close('loc_2d', res.loc_2d, want['loc_2d'])
+            assert_close('loc_3d', res.loc_3d, want['loc_3d'])
