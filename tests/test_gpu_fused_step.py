@@ -528,3 +528,27 @@ def test_one_workspace_through_shape_changes_and_a_zeroed_header(ops, lib):
             res, _grad = run_cuda(ops, lib, c, c['d6'], gt2, gt3, 'pose_changes', True, True)
             assert_close('loc_2d', res.loc_2d, want['loc_2d'])
             assert_close('loc_3d', res.loc_3d, want['loc_3d'])
+
+
+@pytest.mark.parametrize('n,l', [(256, 16), (100, 64), (37, 8), (2048, 16)])
+def test_back_to_back_launches_are_bitwise_repeatable(n, l):
+    """Steps launched back to back overlap through programmatic dependent launch and share one workspace; inside a step
+    the warps hand shared-memory regions to each other phase by phase.  A missing barrier or an unordered reuse shows
+    up as a run-to-run difference: every output of every launch must equal the first launch's bit for bit
+    (tools/stress_determinism.py runs the same check for longer)."""
+    import bench
+    dev = torch.device('cuda', 0)
+    sh = bench.FusedShard(dev, n, l, bench.SEED, want_bytes=1, max_sets=1)
+    st = sh.sets[0]
+    names = ('losses', 'g_d6', 'rel_rot', 'abs_rot', 'abs_loc', 'proj')
+    sh.launch(0)
+    torch.cuda.synchronize()
+    ref = {a: st[a].clone() for a in names}
+    for i in range(25):
+        for a in names[1:]:
+            st[a].fill_(float('nan'))
+        for _ in range(4):
+            sh.launch(0)
+        torch.cuda.synchronize()
+        for a in names:
+            assert torch.equal(st[a], ref[a]), '%s differs from the first launch at iteration %d' % (a, i)

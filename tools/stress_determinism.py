@@ -1,0 +1,40 @@
+"""Run-to-run bitwise repeatability of the fused step under back-to-back launches (a missing barrier or an unordered
+shared-memory reuse shows up as a difference sooner or later):  python tools/stress_determinism.py [iters]"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch  # noqa: E402
+
+import bench  # noqa: E402
+
+iters = int(sys.argv[1]) if len(sys.argv) > 1 else 300
+dev = torch.device('cuda', 0)
+torch.cuda.set_device(dev)
+bad = 0
+for n, l, k in ((256, 16, iters), (100, 64, iters), (37, 8, iters), (2048, 16, iters // 3), (8192, 16, iters // 10), (1024, 64, iters // 10)):
+    sh = bench.FusedShard(dev, n, l, bench.SEED, want_bytes=1, max_sets=1)
+    st = sh.sets[0]
+    names = [a for a in ('losses', 'g_d6', 'rel_rot', 'abs_rot', 'abs_loc', 'proj') if a in st]
+    sh.launch(0)
+    torch.cuda.synchronize()
+    ref = {a: st[a].clone() for a in names}
+    diff = 0
+    for i in range(k):
+        for a in names[1:]:
+            st[a].fill_(float('nan'))      # every output must be rewritten by the launch
+        for _ in range(4):                 # back to back: launches overlap through programmatic dependent launch
+            sh.launch(0)
+        torch.cuda.synchronize()
+        for a in names:
+            if not torch.equal(st[a], ref[a]):
+                diff += 1
+                if diff <= 3:
+                    d = (st[a] != ref[a]) & ~(torch.isnan(st[a]) & torch.isnan(ref[a]))
+                    print('  %dx%d iteration %d: %s differs in %d places' % (n, l, i, a, int(d.sum())))
+    print('%dx%d: %d iterations x 4 launches, %d differing tensors' % (n, l, k, diff))
+    bad += diff
+    del sh
+    torch.cuda.empty_cache()
+print('OK' if bad == 0 else 'FAILED')
+sys.exit(1 if bad else 0)
