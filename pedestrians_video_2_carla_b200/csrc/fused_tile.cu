@@ -733,11 +733,9 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
                     c = __reduce_add_sync(FULL_MASK, c);
                     if (lane == 0 && c) atomicAdd(&cta_count, c);
                     named_barrier(1, nc);
-#ifndef P2C_EXP_LATECOUNT
                     if (ci == 0)
                         atomicAdd(reinterpret_cast<unsigned long long*>(a.count2),
                                   (1ull << 32) | (unsigned long long)(unsigned)cta_count);
-#endif
                 }
             }
         }
@@ -975,11 +973,6 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
             // one lane of a warp without a column polls until every CTA of the grid has sent its count (all CTAs are
             // resident: one tile each, at most one CTA per SM)
             unsigned long long v;
-#ifdef P2C_EXP_LATECOUNT
-            // (sent HERE, by a thread whose next proxy fence is two phases away: a thread that fences right after a
-            // global atomic waits for the atomic's round trip, and with it the whole CTA at the next barrier)
-            atomicAdd(reinterpret_cast<unsigned long long*>(a.count2), (1ull << 32) | (unsigned long long)(unsigned)cta_count);
-#endif
             do {
                 v = *reinterpret_cast<volatile unsigned long long*>(a.count2);
             } while ((unsigned)(v >> 32) < gridDim.x);
@@ -1394,14 +1387,10 @@ __global__ void __launch_bounds__(LAUNCH_THREADS, 1) tile_kernel(const TileArgs 
                 const V3 mv{sx.x - (sg.y * t.z - sg.z * t.y), sx.y - (sg.z * t.x - sg.x * t.z),
                             sx.z - (sg.x * t.y - sg.y * t.x)};
                 V3 y = mv;
-#ifndef P2C_NO_Y_BRANCH   // (the parent's parity is a run-time value: two access sequences behind a branch)
                 if (par >= 0) {
                     if (par & 1) y = v3_mul_mt(mv, lds9<1>(A + pl * B9, par));
                     else y = v3_mul_mt(mv, lds9<0>(A + pl * B9, par));
                 }
-#else
-                if (par >= 0) y = v3_mul_mt(mv, lds9(A + pl * B9, par));
-#endif
                 if (col >= np) y = V3{0.f, 0.f, 0.f};
                 XR[(b * 3) * PS + col] = y.x; XR[(b * 3 + 1) * PS + col] = y.y; XR[(b * 3 + 2) * PS + col] = y.z;
             }
