@@ -36,5 +36,34 @@ for n, l, k in ((256, 16, iters), (100, 64, iters), (37, 8, iters), (2048, 16, i
     bad += diff
     del sh
     torch.cuda.empty_cache()
+# the rot_3d instances (own template instances: barrier 6 hands the rotation sums to the service warp) and the loss
+# exchange with ranks emulated as blocks on one device, through the public API
+from pedestrians_video_2_carla_b200 import ops  # noqa: E402
+from pedestrians_video_2_carla_b200.exchange import LossExchange  # noqa: E402
+for n, l, k, with_x in ((256, 16, iters // 2, False), (100, 64, iters // 4, False), (2048, 16, iters // 6, False),
+                        (256, 16, iters // 2, True)):
+    sh = bench.FusedShard(dev, n, l, bench.SEED, want_bytes=1, max_sets=1)
+    st = sh.sets[0]
+    t = ops.fused_step(st['d6'] * 0.9, sh.tree, sh.cam, sh.loc, sh.rot, st['gt2'], st['gt3'], ref_index=st['sid'])
+    gt_rot = t.absolute_pose_rot.detach().clone()
+    xchs = LossExchange.local(2, dev) if with_x else None
+    xch = xchs[0] if with_x else None
+    ref, diff = None, 0
+    for i in range(k):
+        outs = []
+        for _ in range(3):
+            r = ops.fused_step(st['d6'], sh.tree, sh.cam, sh.loc, sh.rot, st['gt2'], st['gt3'], ref_index=st['sid'],
+                               gt_rot=gt_rot, weight_rot=0.5, exchange=xch)
+            outs.append((r.losses.clone(), r.grad_pose_in.clone(), r.absolute_pose_rot.clone(), r.projection_2d.clone()))
+        torch.cuda.synchronize()
+        if ref is None:
+            ref = outs[0]
+        for o in outs:
+            diff += sum(0 if torch.equal(a, b) else 1 for a, b in zip(o, ref))
+    print('%dx%d rot_3d%s: %d iterations x 3 launches, %d differing tensors' % (n, l, ' + exchange' if with_x else '', k, diff))
+    bad += diff
+    if xchs is not None:
+        for e in xchs:
+            e.close()
 print('OK' if bad == 0 else 'FAILED')
 sys.exit(1 if bad else 0)
