@@ -30,6 +30,15 @@
 //
 // The backward is the torque form derived in fused_fast.cu:  m_b = sum_{d in subtree(b)} g_d x (t_d - t_b),
 // y_b = A_parent m_b, z[t] = sum_{s >= t} y[s], omega = R[t] z[t], tangent-form Gram-Schmidt backward.
+//
+// Two launch shapes.  MANY tiles per CTA: 13 task warps (bones in (even, odd) pairs per warp), two CTAs
+// per SM, tiles drawn from a grid-wide counter, mask count by a pre-pass kernel, loss partials folded by the last CTA
+// to take a ticket.  At most ONE tile per CTA (the 256 x 16 step): 26 task warps (a bone each) + a service warp that
+// publishes the CTA's loss partial as self-validating entries and, in CTA 0, folds the grid's; mask count inside the
+// kernel; steps chained by programmatic dependent launch with the set-up and L2 prefetches ahead of the dependency
+// wait.  Narrow phases (frame scan: 5 warps, tree walk: 5 or 15) are as long as the instruction count of their busiest
+// warp scheduler: the shift / scale of the normaliser is formed beside the walk by a spare warp, the loss fold beside
+// the backward phases by the service warp.
 #include <stdlib.h>
 
 #include "common.cuh"
