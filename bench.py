@@ -355,7 +355,9 @@ def timed_region(shard, steps, warmup, world):
     # A fixed-length busy kernel (~0.2 ms) goes first, so that the K steps are already queued behind it when the start
     # event fires: the events bracket the DEVICE time of exactly K steps, not the host's graph-launch latency (tens of
     # microseconds, i.e. several 14 us steps, which an idle stream would otherwise spend waiting for the host).
-    torch.cuda._sleep(400000)
+    # (long enough for the host to get through the FIRST launch of the K-step graphs -- their upload grows with the
+    # node count: with a fixed 0.2 ms gate a 240-step graph's first replay read 10.5 us per step against 9.8)
+    torch.cuda._sleep(int(400000 + 6000 * steps * max(int(getattr(shard, 'launches_per_step', 1)), 1)))
     e0.record()
     shard.run_steps(steps)
     e1.record()
@@ -587,8 +589,8 @@ def main():
             'warmup': args.warmup, 'ms_per_step': round(ms_per_step, 6), 'higher_is_better': True, 'scaling': 'weak',
             'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic', 'config': config_of(args, args.gpus),
             'clocks': sampler.summary(note), 'gpu_launches': shard.launches_per_step * args.steps,
-            'timing': 'CUDA events on the launching stream around K graph-replayed steps, queued behind a 0.2 ms busy '
-                      'kernel so the events see device time only; barrier + synchronize on both sides; max over ranks'}
+            'timing': 'CUDA events on the launching stream around K graph-replayed steps, queued behind a busy '
+                      'kernel (0.2 ms + 3 us per launch: the host finishes launching first) so the events see device time only; barrier + synchronize on both sides; max over ranks'}
     if exchange is not None:
         # every rank's steps are complete (timed_region ends with synchronize + barrier): read what the peers' kernels
         # stored into THIS rank's block for the last step
