@@ -509,7 +509,7 @@ def measured_peak():
 
 # dram__bytes_read.sum + dram__bytes_write.sum of the step kernel, one launch, from the committed `ncu --set full`
 # captures (profiles/*_tile_<clips>x<len>.txt); writes still in L2 when the kernel ends are not in it
-NCU_DRAM_BYTES = {('fused', 256, 16): 5.634e6, ('fused', 8192, 16): 164.04e6 + 352.72e6,
+NCU_DRAM_BYTES = {('fused', 256, 16): 5.192e6, ('fused', 8192, 16): 164.17e6 + 352.72e6,
                   ('fused', 4096, 64): 327.82e6 + 760.78e6}   # profiles/r02f_tile_*.txt (final build of round 2)
 
 
